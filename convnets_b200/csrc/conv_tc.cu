@@ -1,0 +1,906 @@
+// conv_tc.cu — tcgen05 / TMEM / TMA implicit-GEMM convolution for sm_100a (bf16 in, fp32 accumulate).
+// Replaces aten::convolution / convolution_backward for the dense (groups == 1) layers the
+// reference builds at src/basemodel.py:974 (k = 1, 3, 5, 7; strided; dilated).
+//
+// Two kernels:
+//  * conv_fprop_tc_k : D[M = pixels, N = out-channels] = sum over (tap, channel-block) of
+//        A[128 pixels x 64 ch]  (one im2col-mode TMA load per (tap, channel block); zero-fill
+//                                gives the padding)          -> K-major SW128 smem tile
+//        B[BLOCK_N x 64 ch]     (weights, KRSC viewed as {C, R*S, K}) -> K-major SW128 smem tile
+//    accumulated by tcgen05.mma (M=128, N=BLOCK_N, K=16) into TMEM; epilogue tcgen05.ld ->
+//    (+bias, ReLU) -> bf16 -> swizzled smem -> TMA store into the NHWC output (a plain
+//    [M, K] matrix).  The same kernel computes data-grad: stride-1 dgrad is a forward conv of dy
+//    with the transposed filter; strided dgrad is decomposed by output parity class into stride-1
+//    sub-convolutions whose results are interleaved by a small scatter kernel.
+//  * conv_wgrad_tc_k : per tap, D[M = out-channels(128), N = in-channels(NT)] += dy^T x_tap with
+//    the GEMM-K dimension = output pixels; both operands are "MN-major" smem tiles
+//    ([64 pixels x 64 ch] TMA boxes), one TMEM accumulator per tap, split-K over pixel ranges
+//    into fp32 partials summed by a second (deterministic) kernel.
+//
+// Warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + single-thread MMA issuer,
+// warps 2..5 = epilogue (warp_id % 4 selects the TMEM lane quarter).  mbarrier full/empty rings
+// between producer and MMA; tcgen05.commit releases smem slots and signals the epilogue.
+#include <cuda.h>
+
+#include "common.cuh"
+#include "sm100.cuh"
+
+namespace cnb {
+using namespace sm100;
+
+constexpr int kMaxTaps = 49;
+constexpr int kTcThreads = 192;
+constexpr int TILE_M = 128;   // pixels per CTA tile (fprop) / out-channels per CTA tile (wgrad)
+constexpr int TILE_K = 64;    // bf16 elements per 128-byte swizzle row
+constexpr int A_TILE_BYTES = TILE_M * TILE_K * 2;  // 16 KB
+
+// ------------------------------------------------------------------------------------------
+// driver entry points (no link-time dependency on libcuda)
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*PFN_encodeIm2col)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                     const cuuint64_t*, const cuuint64_t*, const int*, const int*,
+                                     cuuint32_t, cuuint32_t, const cuuint32_t*,
+                                     CUtensorMapInterleave, CUtensorMapSwizzle,
+                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled g_encodeTiled = nullptr;
+static PFN_encodeIm2col g_encodeIm2col = nullptr;
+static int g_driver_version = 0;
+
+static int load_driver_fns() {
+  if (g_encodeTiled && g_encodeIm2col) return CNB_OK;
+  cudaDriverEntryPointQueryResult qres;
+  void* fn = nullptr;
+  cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+  CNB_REQUIRE(e == cudaSuccess && fn && qres == cudaDriverEntryPointSuccess, CNB_ERR_CUDA,
+              "cuTensorMapEncodeTiled not available: %s", cudaGetErrorString(e));
+  g_encodeTiled = (PFN_encodeTiled)fn;
+  fn = nullptr;
+  e = cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &fn, cudaEnableDefault, &qres);
+  CNB_REQUIRE(e == cudaSuccess && fn && qres == cudaDriverEntryPointSuccess, CNB_ERR_CUDA,
+              "cuTensorMapEncodeIm2col not available: %s", cudaGetErrorString(e));
+  g_encodeIm2col = (PFN_encodeIm2col)fn;
+  cudaDriverGetVersion(&g_driver_version);
+  return CNB_OK;
+}
+
+// 2-D / 3-D tiled bf16 map with 128B swizzle; dims/box innermost first; OOB reads give zeros.
+static int make_tiled_map(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
+                          const uint64_t* strides_bytes /* rank-1 */, const uint32_t* box,
+                          const char* what) {
+  cuuint64_t gdim[5], gstr[4];
+  cuuint32_t b[5], es[5];
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = dims[i];
+    b[i] = box[i];
+    es[i] = 1;
+  }
+  for (int i = 0; i < rank - 1; ++i) gstr[i] = strides_bytes[i];
+  CUresult r = g_encodeTiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank,
+                             const_cast<void*>(base), gdim, gstr, b, es,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CNB_REQUIRE(r == CUDA_SUCCESS, CNB_ERR_CUDA, "cuTensorMapEncodeTiled(%s) failed: CUresult %d", what,
+              (int)r);
+  return CNB_OK;
+}
+
+// im2col-mode bf16 map over an NHWC activation tensor {C, W, H, N}.
+static int make_im2col_map(CUtensorMap* m, const void* base, int N, int H, int W, int C,
+                           int lower_w, int lower_h, int upper_w, int upper_h, int trav_w,
+                           int trav_h, int pixels, const char* what) {
+  cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t gstr[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  int lower[2] = {lower_w, lower_h};
+  int upper[2] = {upper_w, upper_h};
+  cuuint32_t es[4] = {1, (cuuint32_t)trav_w, (cuuint32_t)trav_h, 1};
+  CUresult r = g_encodeIm2col(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim,
+                              gstr, lower, upper, (cuuint32_t)TILE_K, (cuuint32_t)pixels, es,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CNB_REQUIRE(r == CUDA_SUCCESS, CNB_ERR_CUDA,
+              "cuTensorMapEncodeIm2col(%s) failed: CUresult %d (N=%d H=%d W=%d C=%d lower=%d,%d "
+              "upper=%d,%d trav=%d,%d)",
+              what, (int)r, N, H, W, C, lower_w, lower_h, upper_w, upper_h, trav_w, trav_h);
+  // Driver workaround also applied by CUTLASS (cute/atom/copy_traits_sm90_im2col.hpp): for small
+  // tensors, drivers <= 13.1 set a descriptor bit that must be cleared.
+  if (g_driver_version <= 13010 && (size_t)N * H * W * C * 2 < 131072)
+    reinterpret_cast<uint64_t*>(m)[1] &= ~(1ull << 21);
+  return CNB_OK;
+}
+
+// ==========================================================================================
+// forward / data-grad kernel
+// ==========================================================================================
+struct FpropParams {
+  CUtensorMap tmA;  // activations: im2col {C,W,H,N} (box 64ch x 128 pixels) or tiled {C, M}
+  CUtensorMap tmB;  // weights {Cg, RS, Kout}, box {64, 1, BLOCK_N}
+  CUtensorMap tmD;  // output {Kout, M}, box {64, 128}
+  const float* bias;
+  int M;            // output pixels in this launch
+  int outP, outQ;   // output grid per image (pixel index -> (n, i, j))
+  int lower_h, lower_w, trav_h, trav_w;
+  int num_cblk;     // ceil(C / 64)
+  int num_taps;
+  int n_tiles;      // ceil(Kout / BLOCK_N)
+  int Kout;
+  int flags;
+  int16_t off_h[kMaxTaps], off_w[kMaxTaps];
+  uint8_t widx[kMaxTaps];
+};
+
+template <int BLOCK_N, int STAGES, bool IM2COL>
+__global__ void __launch_bounds__(kTcThreads, 1)
+conv_fprop_tc_k(const __grid_constant__ FpropParams p) {
+  constexpr int B_TILE_BYTES = BLOCK_N * TILE_K * 2;
+  constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
+  static_assert(STAGES * STAGE_BYTES >= TILE_M * BLOCK_N * 2, "output staging aliases the stages");
+  constexpr uint32_t TMEM_COLS = BLOCK_N < 32 ? 32 : BLOCK_N;
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x / 32;
+  const int lane = threadIdx.x % 32;
+  const int n_tile = blockIdx.x % p.n_tiles;
+  const int m_tile = blockIdx.x / p.n_tiles;
+  const int m0 = m_tile * TILE_M;
+  const int n0 = n_tile * BLOCK_N;
+  const int num_iters = p.num_taps * p.num_cblk;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmA);
+    tma_prefetch_desc(&p.tmB);
+    tma_prefetch_desc(&p.tmD);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_ptr, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int bn = 0, bh = 0, bw = 0;
+      if (IM2COL) {
+        int j = m0 % p.outQ;
+        int t = m0 / p.outQ;
+        int i = t % p.outP;
+        bn = t / p.outP;
+        bh = p.lower_h + i * p.trav_h;
+        bw = p.lower_w + j * p.trav_w;
+      }
+      int it = 0;
+      for (int tap = 0; tap < p.num_taps; ++tap) {
+        for (int cb = 0; cb < p.num_cblk; ++cb, ++it) {
+          const int s = it % STAGES;
+          const uint32_t use = it / STAGES;
+          mbar_wait(&empty_bar[s], (use & 1) ^ 1);
+          uint8_t* sa = smem + s * STAGE_BYTES;
+          uint8_t* sb = sa + A_TILE_BYTES;
+          mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+          if (IM2COL)
+            tma_load_im2col_4d(&p.tmA, &full_bar[s], sa, cb * TILE_K, bw, bh, bn,
+                               (uint16_t)p.off_w[tap], (uint16_t)p.off_h[tap]);
+          else
+            tma_load_2d(&p.tmA, &full_bar[s], sa, cb * TILE_K, m0);
+          tma_load_3d(&p.tmB, &full_bar[s], sb, cb * TILE_K, (int)p.widx[tap], n0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BLOCK_N, 0, 0);
+    for (int it = 0; it < num_iters; ++it) {
+      const int s = it % STAGES;
+      const uint32_t use = it / STAGES;
+      mbar_wait(&full_bar[s], use & 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t a_base = smem_u32(smem + s * STAGE_BYTES);
+        const uint32_t b_base = a_base + A_TILE_BYTES;
+#pragma unroll
+        for (int k = 0; k < TILE_K / 16; ++k) {
+          uint64_t da = make_smem_desc_sw128(a_base + k * 32, 0, 1024);
+          uint64_t db = make_smem_desc_sw128(b_base + k * 32, 0, 1024);
+          umma_bf16(tmem_base, da, db, idesc, (it | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);
+        if (it == num_iters - 1) umma_commit(tmem_full_bar);
+      }
+      __syncwarp();
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int quarter = warp % 4;
+    const int row = quarter * 32 + lane;
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    uint8_t* stage_out = smem;  // aliases the (now idle) pipeline stages
+#pragma unroll 1
+    for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0, v);
+      tmem_ld_wait();
+      uint8_t* box = stage_out + (c0 / 64) * (TILE_M * 128);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        uint32_t packed[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float f0 = __uint_as_float(v[j * 8 + e * 2 + 0]);
+          float f1 = __uint_as_float(v[j * 8 + e * 2 + 1]);
+          const int col = n0 + c0 + j * 8 + e * 2;
+          if (p.flags & CNB_CONV_BIAS) {
+            f0 += (col < p.Kout) ? p.bias[col] : 0.f;
+            f1 += (col + 1 < p.Kout) ? p.bias[col + 1] : 0.f;
+          }
+          if (p.flags & CNB_CONV_RELU) {
+            f0 = (f0 > 0.f || f0 != f0) ? f0 : 0.f;
+            f1 = (f1 > 0.f || f1 != f1) ? f1 : 0.f;
+          }
+          __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);
+          packed[e] = *reinterpret_cast<uint32_t*>(&h);
+        }
+        const int chunk = (c0 % 64) / 8 + j;
+        uint4* dst = reinterpret_cast<uint4*>(box + row * 128 + ((chunk ^ (row & 7)) * 16));
+        *dst = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+      }
+    }
+    tc_fence_before();
+    fence_proxy_async_smem();
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (warp == 2 && lane == 0) {
+      for (int b = 0; b < BLOCK_N / 64; ++b) {
+        if (n0 + b * 64 < p.Kout)
+          tma_store_2d(&p.tmD, stage_out + b * (TILE_M * 128), n0 + b * 64, m0);
+      }
+      tma_store_commit();
+      tma_store_wait0();
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ==========================================================================================
+// weight-grad kernel
+// ==========================================================================================
+struct WgradParams {
+  CUtensorMap tmDy;  // {K, M} tiled, box {64 out-ch, 64 pixels}
+  CUtensorMap tmX;   // im2col {C,W,H,N}, box 64 ch x 64 pixels (or tiled {C, M} for 1x1 s1 p0)
+  float* out;        // [splits][K][RS][Cg] partials (or dw itself when splits == 1)
+  int M;             // output pixels N*P*Q
+  int outP, outQ, lower_h, lower_w, trav_h, trav_w;
+  int K, Cg, RS;
+  int num_taps;      // all taps
+  int taps_per_cta, tap_groups;
+  int cin_tiles, cout_tiles;
+  int splits, pixblk_per_split;  // pixel blocks (64 pixels) per split
+  int16_t off_h[kMaxTaps], off_w[kMaxTaps];
+};
+
+template <int NT, int SA, int SB, bool IM2COL>
+__global__ void __launch_bounds__(kTcThreads, 1)
+conv_wgrad_tc_k(const __grid_constant__ WgradParams p) {
+  constexpr int PIX = 64;                         // GEMM-K block: pixels per TMA box
+  constexpr int DY_BYTES = 2 * PIX * 128;         // two 64-channel boxes -> 128 out-channels
+  constexpr int X_BYTES = (NT / 64) * PIX * 128;  // NT/64 boxes
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~(uintptr_t)1023);
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + SA * DY_BYTES;
+  uint64_t* fullA = reinterpret_cast<uint64_t*>(sB + SB * X_BYTES);
+  uint64_t* emptyA = fullA + SA;
+  uint64_t* fullB = emptyA + SA;
+  uint64_t* emptyB = fullB + SB;
+  uint64_t* tmem_full_bar = emptyB + SB;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x / 32;
+  const int lane = threadIdx.x % 32;
+
+  // work item decode: blockIdx.x = ((split * cout_tiles + ct) * cin_tiles + it_) * tap_groups + tg
+  int w = blockIdx.x;
+  const int tg = w % p.tap_groups; w /= p.tap_groups;
+  const int cit = w % p.cin_tiles; w /= p.cin_tiles;
+  const int ct = w % p.cout_tiles; w /= p.cout_tiles;
+  const int split = w;
+  const int tap0 = tg * p.taps_per_cta;
+  const int ntap = min(p.taps_per_cta, p.num_taps - tap0);
+  const int total_pixblk = (p.M + PIX - 1) / PIX;
+  const int pb0 = split * p.pixblk_per_split;
+  const int pb1 = min(pb0 + p.pixblk_per_split, total_pixblk);
+  const int npb = max(pb1 - pb0, 0);
+  const int cout0 = ct * TILE_M;
+  const int cin0 = cit * NT;
+
+  // TMEM columns: power of two >= taps_per_cta * NT (host guarantees <= 512)
+  uint32_t tmem_cols = 32;
+  while ((int)tmem_cols < p.taps_per_cta * NT) tmem_cols <<= 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmDy);
+    tma_prefetch_desc(&p.tmX);
+    for (int s = 0; s < SA; ++s) { mbar_init(&fullA[s], 1); mbar_init(&emptyA[s], 1); }
+    for (int s = 0; s < SB; ++s) { mbar_init(&fullB[s], 1); mbar_init(&emptyB[s], 1); }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_ptr, tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int itb = 0;
+      for (int pb = 0; pb < npb; ++pb) {
+        const int pix0 = (pb0 + pb) * PIX;
+        {  // dy tile: two 64-channel boxes
+          const int s = pb % SA;
+          const uint32_t use = pb / SA;
+          mbar_wait(&emptyA[s], (use & 1) ^ 1);
+          mbar_expect_tx(&fullA[s], DY_BYTES);
+          uint8_t* dst = sA + s * DY_BYTES;
+          tma_load_2d(&p.tmDy, &fullA[s], dst, cout0, pix0);
+          tma_load_2d(&p.tmDy, &fullA[s], dst + PIX * 128, cout0 + 64, pix0);
+        }
+        int bn = 0, bh = 0, bw = 0;
+        if (IM2COL) {
+          int j = pix0 % p.outQ;
+          int t = pix0 / p.outQ;
+          int i = t % p.outP;
+          bn = t / p.outP;
+          bh = p.lower_h + i * p.trav_h;
+          bw = p.lower_w + j * p.trav_w;
+        }
+        for (int tp = 0; tp < ntap; ++tp, ++itb) {
+          const int s = itb % SB;
+          const uint32_t use = itb / SB;
+          mbar_wait(&emptyB[s], (use & 1) ^ 1);
+          mbar_expect_tx(&fullB[s], X_BYTES);
+          uint8_t* dst = sB + s * X_BYTES;
+#pragma unroll
+          for (int b = 0; b < NT / 64; ++b) {
+            if (IM2COL)
+              tma_load_im2col_4d(&p.tmX, &fullB[s], dst + b * PIX * 128, cin0 + b * 64, bw, bh, bn,
+                                 (uint16_t)p.off_w[tap0 + tp], (uint16_t)p.off_h[tap0 + tp]);
+            else
+              tma_load_2d(&p.tmX, &fullB[s], dst + b * PIX * 128, cin0 + b * 64, pix0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = make_idesc_bf16(TILE_M, NT, 1, 1);  // both operands MN-major
+    int itb = 0;
+    for (int pb = 0; pb < npb; ++pb) {
+      const int sa = pb % SA;
+      mbar_wait(&fullA[sa], (pb / SA) & 1);
+      for (int tp = 0; tp < ntap; ++tp, ++itb) {
+        const int sb = itb % SB;
+        mbar_wait(&fullB[sb], (itb / SB) & 1);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t a_base = smem_u32(sA + sa * DY_BYTES);
+          const uint32_t b_base = smem_u32(sB + sb * X_BYTES);
+#pragma unroll
+          for (int k = 0; k < PIX / 16; ++k) {
+            // MN-major SW128: 16 pixel rows = 2 swizzle atoms of 1024 B (SBO); the next
+            // 64-channel box sits PIX*128 bytes further (LBO).
+            uint64_t da = make_smem_desc_sw128(a_base + k * 2048, PIX * 128, 1024);
+            uint64_t db = make_smem_desc_sw128(b_base + k * 2048, PIX * 128, 1024);
+            umma_bf16(tmem_base + (uint32_t)(tp * NT), da, db, idesc, (pb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&emptyB[sb]);
+          if (tp == ntap - 1) umma_commit(&emptyA[sa]);
+          if (pb == npb - 1 && tp == ntap - 1) umma_commit(tmem_full_bar);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    const int quarter = warp % 4;
+    const int row = quarter * 32 + lane;  // out-channel within the tile
+    const int ko = cout0 + row;
+    if (npb > 0) {
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+    }
+    const int64_t wsz = (int64_t)p.K * p.RS * p.Cg;
+    float* outp = p.out + (int64_t)split * wsz;
+    for (int tp = 0; tp < ntap; ++tp) {
+#pragma unroll 1
+      for (int c0 = 0; c0 < NT; c0 += 32) {
+        uint32_t v[32];
+        if (npb > 0) {
+          tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(tp * NT + c0), v);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0u;
+        }
+        if (ko < p.K) {
+          float* dst = outp + ((int64_t)ko * p.RS + (tap0 + tp)) * p.Cg + cin0 + c0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (cin0 + c0 + j < p.Cg) dst[j] = __uint_as_float(v[j]);
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, tmem_cols);
+  }
+}
+
+// ==========================================================================================
+// small helper kernels
+// ==========================================================================================
+// wt[c][rs][k] = w[k][rs][c]   (dgrad operand: the filter with in/out channels exchanged)
+__global__ void transpose_filter_k(const bf16* __restrict__ w, bf16* __restrict__ wt, int K, int RS,
+                                   int C) {
+  int64_t total = (int64_t)K * RS * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int k = (int)(i % K);
+    int64_t t = i / K;
+    int rs = (int)(t % RS);
+    int c = (int)(t / RS);
+    wt[i] = w[((int64_t)k * RS + rs) * C + c];
+  }
+}
+
+// Interleave the parity-class results of a strided dgrad into dx (zeros where no class has taps).
+struct ScatterP {
+  const bf16* src[16];  // per class compact [N, Ha, Wb, C] or nullptr
+  int Ha[16], Wb[16];
+  int N, H, W, C, sh, sw;
+};
+__global__ void dgrad_interleave_k(ScatterP p, bf16* __restrict__ dx) {
+  const int Cv = p.C / 8;
+  const int64_t total = (int64_t)p.N * p.H * p.W * Cv;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int cv = (int)(i % Cv);
+    int64_t pix = i / Cv;
+    int w = (int)(pix % p.W);
+    int64_t t = pix / p.W;
+    int h = (int)(t % p.H);
+    int n = (int)(t / p.H);
+    int a = h % p.sh, b = w % p.sw;
+    int cls = a * p.sw + b;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    const bf16* s = p.src[cls];
+    if (s) {
+      int ii = h / p.sh, jj = w / p.sw;
+      v = *reinterpret_cast<const uint4*>(
+          s + (((int64_t)n * p.Ha[cls] + ii) * p.Wb[cls] + jj) * p.C + cv * 8);
+    }
+    *reinterpret_cast<uint4*>(dx + i * 8) = v;
+  }
+}
+
+__global__ void sum_splits_tc_k(const float* __restrict__ part, float* __restrict__ out, int splits,
+                                int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    float s = 0.f;
+    for (int k = 0; k < splits; ++k) s += part[(int64_t)k * n + i];
+    out[i] = s;
+  }
+}
+
+// ==========================================================================================
+// host side
+// ==========================================================================================
+struct FpropLaunch {
+  const void* a;                 // activation tensor fed to the loads, NHWC bf16
+  int aN, aH, aW, aC;
+  int lower_h, lower_w, upper_h, upper_w, trav_h, trav_w;
+  int outP, outQ;                // output grid per image
+  int ntaps;
+  int16_t off_h[kMaxTaps], off_w[kMaxTaps];
+  uint8_t widx[kMaxTaps];
+  const void* w;                 // weights [Kout][RS][aC] bf16
+  int Kout, RS;
+  void* out;                     // [aN*outP*outQ, Kout] bf16
+  const float* bias;
+  int flags;
+  bool tiled2d;                  // pure GEMM: A is the [M, C] matrix itself
+};
+
+template <int BLOCK_N, int STAGES, bool IM2COL>
+static int launch_fprop_inst(const FpropParams& prm, int grid, cudaStream_t st) {
+  constexpr int STAGE_BYTES = A_TILE_BYTES + BLOCK_N * TILE_K * 2;
+  constexpr size_t smem = (size_t)STAGES * STAGE_BYTES + (2 * STAGES + 1) * 8 + 16 + 1024;
+  static bool attr_done = false;
+  auto kern = conv_fprop_tc_k<BLOCK_N, STAGES, IM2COL>;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cudaFuncSetAttribute(fprop): %s",
+                cudaGetErrorString(e));
+    attr_done = true;
+  }
+  kern<<<grid, kTcThreads, smem, st>>>(prm);
+  return check_launch("conv_fprop_tc");
+}
+
+static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
+  CNB_TRY(load_driver_fns());
+  FpropParams prm;
+  memset(&prm, 0, sizeof(prm));
+  const int64_t M64 = (int64_t)L.aN * L.outP * L.outQ;
+  CNB_REQUIRE(M64 < (1ll << 31) - 256, CNB_ERR_UNSUPPORTED, "conv_tc: too many output pixels");
+  const int M = (int)M64;
+  if (L.tiled2d) {
+    uint64_t dims[2] = {(uint64_t)L.aC, (uint64_t)M};
+    uint64_t str[1] = {(uint64_t)L.aC * 2};
+    uint32_t box[2] = {TILE_K, TILE_M};
+    CNB_TRY(make_tiled_map(&prm.tmA, L.a, 2, dims, str, box, "A(2d)"));
+  } else {
+    CNB_TRY(make_im2col_map(&prm.tmA, L.a, L.aN, L.aH, L.aW, L.aC, L.lower_w, L.lower_h, L.upper_w,
+                            L.upper_h, L.trav_w, L.trav_h, TILE_M, "A(im2col)"));
+  }
+  const int BLOCK_N = L.Kout <= 64 ? 64 : (L.Kout <= 128 ? 128 : 256);
+  {
+    uint64_t dims[3] = {(uint64_t)L.aC, (uint64_t)L.RS, (uint64_t)L.Kout};
+    uint64_t str[2] = {(uint64_t)L.aC * 2, (uint64_t)L.aC * L.RS * 2};
+    uint32_t box[3] = {TILE_K, 1, (uint32_t)BLOCK_N};
+    CNB_TRY(make_tiled_map(&prm.tmB, L.w, 3, dims, str, box, "B(weights)"));
+  }
+  {
+    uint64_t dims[2] = {(uint64_t)L.Kout, (uint64_t)M};
+    uint64_t str[1] = {(uint64_t)L.Kout * 2};
+    uint32_t box[2] = {64, TILE_M};
+    CNB_TRY(make_tiled_map(&prm.tmD, L.out, 2, dims, str, box, "D(output)"));
+  }
+  prm.bias = L.bias;
+  prm.M = M;
+  prm.outP = L.outP; prm.outQ = L.outQ;
+  prm.lower_h = L.lower_h; prm.lower_w = L.lower_w;
+  prm.trav_h = L.trav_h; prm.trav_w = L.trav_w;
+  prm.num_cblk = (L.aC + TILE_K - 1) / TILE_K;
+  prm.num_taps = L.ntaps;
+  prm.n_tiles = (L.Kout + BLOCK_N - 1) / BLOCK_N;
+  prm.Kout = L.Kout;
+  prm.flags = L.flags & ((L.bias ? CNB_CONV_BIAS : 0) | CNB_CONV_RELU);
+  for (int t = 0; t < L.ntaps; ++t) {
+    prm.off_h[t] = L.off_h[t];
+    prm.off_w[t] = L.off_w[t];
+    prm.widx[t] = L.widx[t];
+  }
+  const int64_t grid64 = ceil_div(M, TILE_M) * prm.n_tiles;
+  CNB_REQUIRE(grid64 < (1ll << 31), CNB_ERR_UNSUPPORTED, "conv_tc: grid too large");
+  const int grid = (int)grid64;
+  if (L.tiled2d) {
+    if (BLOCK_N == 64) return launch_fprop_inst<64, 6, false>(prm, grid, st);
+    if (BLOCK_N == 128) return launch_fprop_inst<128, 5, false>(prm, grid, st);
+    return launch_fprop_inst<256, 4, false>(prm, grid, st);
+  }
+  if (BLOCK_N == 64) return launch_fprop_inst<64, 6, true>(prm, grid, st);
+  if (BLOCK_N == 128) return launch_fprop_inst<128, 5, true>(prm, grid, st);
+  return launch_fprop_inst<256, 4, true>(prm, grid, st);
+}
+
+static bool corners_ok(int v) { return v >= -128 && v <= 127; }
+
+bool conv_tc_supported(const cnb_conv_desc& d, int direction, const char** why) {
+  static const char* dummy;
+  if (!why) why = &dummy;
+  if (d.dtype != CNB_BF16) { *why = "tcgen05 path is bf16-only (fp32-IO mode uses CUDA cores)"; return false; }
+  if (d.groups != 1) { *why = "grouped convolution"; return false; }
+  if (d.C % 8 != 0 || d.K % 8 != 0) { *why = "C and K must be multiples of 8 (16-byte TMA strides)"; return false; }
+  if (d.R * d.S > kMaxTaps) { *why = "more than 49 filter taps"; return false; }
+  int P, Q;
+  conv_out_dims(d, P, Q);
+  if (P <= 0 || Q <= 0) { *why = "empty output"; return false; }
+  const int eh = (d.R - 1) * d.dil_h, ew = (d.S - 1) * d.dil_w;
+  if (eh > 255 || ew > 255) { *why = "dilated filter extent > 255"; return false; }
+  if (!corners_ok(-d.pad_h) || !corners_ok(-d.pad_w) || !corners_ok(d.pad_h - eh) ||
+      !corners_ok(d.pad_w - ew)) { *why = "padding outside the im2col corner range"; return false; }
+  if (d.stride_h > 8 || d.stride_w > 8) { *why = "stride > 8"; return false; }
+  if (direction == CNB_DGRAD) {
+    if (d.stride_h * d.stride_w > 16) { *why = "strided dgrad with more than 16 parity classes"; return false; }
+    if (d.R > 16 || d.S > 16) { *why = "filter larger than 16 in one dimension"; return false; }
+  }
+  if ((int64_t)d.N * d.H * d.W >= (1ll << 31) - 256 || (int64_t)d.N * P * Q >= (1ll << 31) - 256) {
+    *why = "more than 2^31 pixels"; return false;
+  }
+  return true;
+}
+
+static void wgrad_geometry(const cnb_conv_desc& d, int& NT, int& taps_per_cta, int& tap_groups,
+                           int& cin_tiles, int& cout_tiles, int& splits, int& pixblk_per_split) {
+  const int Cg = d.C;
+  NT = Cg >= 256 ? 256 : (Cg >= 128 ? 128 : 64);
+  const int taps = d.R * d.S;
+  int maxt = 512 / NT;
+  tap_groups = (taps + maxt - 1) / maxt;
+  taps_per_cta = (taps + tap_groups - 1) / tap_groups;
+  tap_groups = (taps + taps_per_cta - 1) / taps_per_cta;
+  cin_tiles = (Cg + NT - 1) / NT;
+  cout_tiles = (d.K + TILE_M - 1) / TILE_M;
+  int P, Q;
+  conv_out_dims(d, P, Q);
+  const int64_t M = (int64_t)d.N * P * Q;
+  const int64_t total_pb = ceil_div(M, 64);
+  const int64_t tiles = (int64_t)tap_groups * cin_tiles * cout_tiles;
+  int64_t want = ceil_div((int64_t)sm_count() * 2, tiles);
+  int64_t maxs = ceil_div(total_pb, 8);  // at least 8 pixel blocks (512 pixels) per split
+  if (want > maxs) want = maxs;
+  if (want < 1) want = 1;
+  if (want > 512) want = 512;
+  pixblk_per_split = (int)ceil_div(total_pb, want);
+  splits = (int)ceil_div(total_pb, pixblk_per_split);
+}
+
+size_t conv_tc_workspace(const cnb_conv_desc& d, int direction) {
+  if (direction == CNB_FWD) return 0;
+  if (direction == CNB_DGRAD) {
+    size_t wt = align_up((size_t)d.K * d.R * d.S * d.C * 2, 1024);
+    size_t tmp = 0;
+    if (d.stride_h != 1 || d.stride_w != 1) {
+      // compact per-class results: each at most ceil(H/sh)*ceil(W/sw) pixels
+      int Ha = (d.H + d.stride_h - 1) / d.stride_h, Wb = (d.W + d.stride_w - 1) / d.stride_w;
+      tmp = (size_t)d.stride_h * d.stride_w * align_up((size_t)d.N * Ha * Wb * d.C * 2, 1024);
+    }
+    return wt + tmp + 1024;
+  }
+  int NT, tpc, tg, cit, cot, splits, pps;
+  wgrad_geometry(d, NT, tpc, tg, cit, cot, splits, pps);
+  return (size_t)(splits > 1 ? splits : 0) * d.K * d.R * d.S * d.C * sizeof(float) + 1024;
+}
+
+int conv_tc_fwd(const cnb_conv_desc& d, const void* x, const void* w, const float* bias, void* y,
+                void* ws, size_t ws_bytes, cudaStream_t st) {
+  (void)ws; (void)ws_bytes;
+  FpropLaunch L;
+  memset(&L, 0, sizeof(L));
+  int P, Q;
+  conv_out_dims(d, P, Q);
+  L.a = x; L.aN = d.N; L.aH = d.H; L.aW = d.W; L.aC = d.C;
+  L.lower_h = -d.pad_h; L.lower_w = -d.pad_w;
+  L.upper_h = d.pad_h - (d.R - 1) * d.dil_h;
+  L.upper_w = d.pad_w - (d.S - 1) * d.dil_w;
+  L.trav_h = d.stride_h; L.trav_w = d.stride_w;
+  L.outP = P; L.outQ = Q;
+  L.ntaps = d.R * d.S;
+  for (int r = 0; r < d.R; ++r)
+    for (int s = 0; s < d.S; ++s) {
+      int t = r * d.S + s;
+      L.off_h[t] = (int16_t)(r * d.dil_h);
+      L.off_w[t] = (int16_t)(s * d.dil_w);
+      L.widx[t] = (uint8_t)t;
+    }
+  L.w = w; L.Kout = d.K; L.RS = d.R * d.S;
+  L.out = y; L.bias = bias; L.flags = d.flags;
+  L.tiled2d = (d.R == 1 && d.S == 1 && d.stride_h == 1 && d.stride_w == 1 && d.pad_h == 0 &&
+               d.pad_w == 0);
+  return launch_fprop(L, st);
+}
+
+int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, void* dx, void* ws,
+                  size_t ws_bytes, cudaStream_t st) {
+  CNB_REQUIRE(ws && ws_bytes >= conv_tc_workspace(d, CNB_DGRAD), CNB_ERR_WORKSPACE,
+              "conv_tc_dgrad: workspace %zu < %zu", ws_bytes, conv_tc_workspace(d, CNB_DGRAD));
+  int P, Q;
+  conv_out_dims(d, P, Q);
+  const int RS = d.R * d.S;
+  // transposed filter wt[C][RS][K]
+  bf16* wt = reinterpret_cast<bf16*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
+  {
+    int64_t total = (int64_t)d.K * RS * d.C;
+    transpose_filter_k<<<grid_for(total, 256), 256, 0, st>>>((const bf16*)w, wt, d.K, RS, d.C);
+    CNB_TRY(check_launch("transpose_filter"));
+  }
+  uint8_t* tmp_base = reinterpret_cast<uint8_t*>(wt) + align_up((size_t)d.K * RS * d.C * 2, 1024);
+
+  if (d.stride_h == 1 && d.stride_w == 1) {
+    FpropLaunch L;
+    memset(&L, 0, sizeof(L));
+    L.a = dy; L.aN = d.N; L.aH = P; L.aW = Q; L.aC = d.K;
+    L.lower_h = d.pad_h - (d.R - 1) * d.dil_h;
+    L.lower_w = d.pad_w - (d.S - 1) * d.dil_w;
+    L.upper_h = L.lower_h + d.H - P;
+    L.upper_w = L.lower_w + d.W - Q;
+    CNB_REQUIRE(corners_ok(L.lower_h) && corners_ok(L.lower_w) && corners_ok(L.upper_h) &&
+                    corners_ok(L.upper_w),
+                CNB_ERR_UNSUPPORTED, "conv_tc_dgrad: corners outside the im2col range");
+    L.trav_h = 1; L.trav_w = 1;
+    L.outP = d.H; L.outQ = d.W;
+    L.ntaps = RS;
+    for (int r = 0; r < d.R; ++r)
+      for (int s = 0; s < d.S; ++s) {
+        int t = r * d.S + s;
+        L.off_h[t] = (int16_t)((d.R - 1 - r) * d.dil_h);
+        L.off_w[t] = (int16_t)((d.S - 1 - s) * d.dil_w);
+        L.widx[t] = (uint8_t)t;
+      }
+    L.w = wt; L.Kout = d.C; L.RS = RS;
+    L.out = dx; L.bias = nullptr; L.flags = 0;
+    L.tiled2d = (RS == 1 && d.pad_h == 0 && d.pad_w == 0);
+    return launch_fprop(L, st);
+  }
+
+  // ---- strided: one stride-1 sub-convolution per output parity class (a, b)
+  ScatterP sp;
+  memset(&sp, 0, sizeof(sp));
+  sp.N = d.N; sp.H = d.H; sp.W = d.W; sp.C = d.C; sp.sh = d.stride_h; sp.sw = d.stride_w;
+  const int HaMax = (d.H + d.stride_h - 1) / d.stride_h, WbMax = (d.W + d.stride_w - 1) / d.stride_w;
+  const size_t cls_bytes = align_up((size_t)d.N * HaMax * WbMax * d.C * 2, 1024);
+  for (int a = 0; a < d.stride_h; ++a)
+    for (int b = 0; b < d.stride_w; ++b) {
+      const int cls = a * d.stride_w + b;
+      const int Ha = (d.H - a + d.stride_h - 1) / d.stride_h;
+      const int Wb = (d.W - b + d.stride_w - 1) / d.stride_w;
+      sp.Ha[cls] = Ha; sp.Wb[cls] = Wb; sp.src[cls] = nullptr;
+      if (Ha <= 0 || Wb <= 0) continue;
+      // taps of this class: (a + pad_h - r*dil_h) % sh == 0, offset dr = (...) / sh
+      int drs[16], rr[16], nr = 0, dss[16], ss[16], ns = 0;
+      for (int r = 0; r < d.R; ++r) {
+        int v = a + d.pad_h - r * d.dil_h;
+        if (((v % d.stride_h) + d.stride_h) % d.stride_h == 0 && nr < 16) {
+          drs[nr] = (v >= 0) ? v / d.stride_h : -((-v) / d.stride_h);
+          rr[nr++] = r;
+        }
+      }
+      for (int s = 0; s < d.S; ++s) {
+        int v = b + d.pad_w - s * d.dil_w;
+        if (((v % d.stride_w) + d.stride_w) % d.stride_w == 0 && ns < 16) {
+          dss[ns] = (v >= 0) ? v / d.stride_w : -((-v) / d.stride_w);
+          ss[ns++] = s;
+        }
+      }
+      if (nr == 0 || ns == 0) continue;  // class receives no contribution -> zeros
+      int lo_h = drs[0], lo_w = dss[0];
+      for (int i = 1; i < nr; ++i) lo_h = drs[i] < lo_h ? drs[i] : lo_h;
+      for (int i = 1; i < ns; ++i) lo_w = dss[i] < lo_w ? dss[i] : lo_w;
+      FpropLaunch L;
+      memset(&L, 0, sizeof(L));
+      L.a = dy; L.aN = d.N; L.aH = P; L.aW = Q; L.aC = d.K;
+      L.lower_h = lo_h; L.lower_w = lo_w;
+      L.upper_h = lo_h + Ha - P; L.upper_w = lo_w + Wb - Q;
+      CNB_REQUIRE(corners_ok(L.lower_h) && corners_ok(L.lower_w) && corners_ok(L.upper_h) &&
+                      corners_ok(L.upper_w),
+                  CNB_ERR_UNSUPPORTED, "conv_tc_dgrad(strided): corners outside the im2col range");
+      L.trav_h = 1; L.trav_w = 1;
+      L.outP = Ha; L.outQ = Wb;
+      L.ntaps = 0;
+      for (int i = 0; i < nr; ++i)
+        for (int j = 0; j < ns; ++j) {
+          int t = L.ntaps++;
+          L.off_h[t] = (int16_t)(drs[i] - lo_h);
+          L.off_w[t] = (int16_t)(dss[j] - lo_w);
+          L.widx[t] = (uint8_t)(rr[i] * d.S + ss[j]);
+        }
+      L.w = wt; L.Kout = d.C; L.RS = RS;
+      bf16* tmp = reinterpret_cast<bf16*>(tmp_base + (size_t)cls * cls_bytes);
+      L.out = tmp; L.bias = nullptr; L.flags = 0;
+      L.tiled2d = false;
+      CNB_TRY(launch_fprop(L, st));
+      sp.src[cls] = tmp;
+    }
+  int64_t total = (int64_t)d.N * d.H * d.W * (d.C / 8);
+  dgrad_interleave_k<<<grid_for(total, 256), 256, 0, st>>>(sp, (bf16*)dx);
+  return check_launch("dgrad_interleave");
+}
+
+template <int NT, int SA, int SB, bool IM2COL>
+static int launch_wgrad_inst(const WgradParams& prm, int grid, cudaStream_t st) {
+  constexpr size_t smem = (size_t)SA * 2 * 64 * 128 + (size_t)SB * (NT / 64) * 64 * 128 +
+                          (2 * SA + 2 * SB + 1) * 8 + 16 + 1024;
+  static bool attr_done = false;
+  auto kern = conv_wgrad_tc_k<NT, SA, SB, IM2COL>;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cudaFuncSetAttribute(wgrad): %s",
+                cudaGetErrorString(e));
+    attr_done = true;
+  }
+  kern<<<grid, kTcThreads, smem, st>>>(prm);
+  return check_launch("conv_wgrad_tc");
+}
+
+int conv_tc_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* dw, void* ws,
+                  size_t ws_bytes, cudaStream_t st) {
+  CNB_TRY(load_driver_fns());
+  int P, Q;
+  conv_out_dims(d, P, Q);
+  const int RS = d.R * d.S;
+  const int M = d.N * P * Q;
+  WgradParams prm;
+  memset(&prm, 0, sizeof(prm));
+  int NT;
+  wgrad_geometry(d, NT, prm.taps_per_cta, prm.tap_groups, prm.cin_tiles, prm.cout_tiles, prm.splits,
+                 prm.pixblk_per_split);
+  const int64_t wsz = (int64_t)d.K * RS * d.C;
+  float* part = dw;
+  if (prm.splits > 1) {
+    CNB_REQUIRE(ws && ws_bytes >= (size_t)prm.splits * wsz * sizeof(float) + 1024, CNB_ERR_WORKSPACE,
+                "conv_tc_wgrad: workspace %zu < %zu", ws_bytes,
+                (size_t)prm.splits * wsz * sizeof(float) + 1024);
+    part = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(ws) + 255) & ~(uintptr_t)255);
+  }
+  const bool tiled2d = (RS == 1 && d.stride_h == 1 && d.stride_w == 1 && d.pad_h == 0 && d.pad_w == 0);
+  {
+    uint64_t dims[2] = {(uint64_t)d.K, (uint64_t)M};
+    uint64_t str[1] = {(uint64_t)d.K * 2};
+    uint32_t box[2] = {64, 64};
+    CNB_TRY(make_tiled_map(&prm.tmDy, dy, 2, dims, str, box, "dy"));
+  }
+  if (tiled2d) {
+    uint64_t dims[2] = {(uint64_t)d.C, (uint64_t)M};
+    uint64_t str[1] = {(uint64_t)d.C * 2};
+    uint32_t box[2] = {64, 64};
+    CNB_TRY(make_tiled_map(&prm.tmX, x, 2, dims, str, box, "x(2d)"));
+  } else {
+    int upper_h = d.pad_h - (d.R - 1) * d.dil_h;
+    int upper_w = d.pad_w - (d.S - 1) * d.dil_w;
+    CNB_TRY(make_im2col_map(&prm.tmX, x, d.N, d.H, d.W, d.C, -d.pad_w, -d.pad_h, upper_w, upper_h,
+                            d.stride_w, d.stride_h, 64, "x(im2col)"));
+  }
+  prm.out = part;
+  prm.M = M;
+  prm.outP = P; prm.outQ = Q;
+  prm.lower_h = -d.pad_h; prm.lower_w = -d.pad_w;
+  prm.trav_h = d.stride_h; prm.trav_w = d.stride_w;
+  prm.K = d.K; prm.Cg = d.C; prm.RS = RS;
+  prm.num_taps = RS;
+  for (int r = 0; r < d.R; ++r)
+    for (int s = 0; s < d.S; ++s) {
+      prm.off_h[r * d.S + s] = (int16_t)(r * d.dil_h);
+      prm.off_w[r * d.S + s] = (int16_t)(s * d.dil_w);
+    }
+  const int64_t grid64 = (int64_t)prm.splits * prm.cout_tiles * prm.cin_tiles * prm.tap_groups;
+  CNB_REQUIRE(grid64 < (1ll << 31), CNB_ERR_UNSUPPORTED, "conv_tc_wgrad: grid too large");
+  const int grid = (int)grid64;
+  int s;
+  if (tiled2d) {
+    if (NT == 64) s = launch_wgrad_inst<64, 3, 4, false>(prm, grid, st);
+    else if (NT == 128) s = launch_wgrad_inst<128, 3, 4, false>(prm, grid, st);
+    else s = launch_wgrad_inst<256, 3, 3, false>(prm, grid, st);
+  } else {
+    if (NT == 64) s = launch_wgrad_inst<64, 3, 6, true>(prm, grid, st);
+    else if (NT == 128) s = launch_wgrad_inst<128, 3, 4, true>(prm, grid, st);
+    else s = launch_wgrad_inst<256, 3, 3, true>(prm, grid, st);
+  }
+  CNB_TRY(s);
+  if (prm.splits > 1) {
+    sum_splits_tc_k<<<grid_for(wsz, 256), 256, 0, st>>>(part, dw, prm.splits, wsz);
+    CNB_TRY(check_launch("wgrad_sum_splits"));
+  }
+  return CNB_OK;
+}
+
+}  // namespace cnb

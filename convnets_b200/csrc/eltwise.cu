@@ -1,0 +1,583 @@
+// eltwise.cu — bandwidth-bound element-wise, data-movement, pooling-to-vector and gating kernels.
+// All are 128-bit vectorised over the innermost (channel) dimension of NHWC tensors and sized as
+// grid-stride loops over a multiple of the SM count.  Roofline: HBM.
+#include "common.cuh"
+
+namespace cnb {
+
+thread_local char g_last_error[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+constexpr int kThreads = 256;
+
+// ------------------------------------------------------------------ relu / add
+template <typename T, int V>
+__global__ void relu_fwd_k(const T* __restrict__ x, T* __restrict__ y, int64_t nvec) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    Pack<T, V> a = ld_pack<T, V>(x + i * V), o;
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      float f = to_f(a.v[j]);
+      // torch relu: NaN propagates (clamp_min semantics)
+      o.v[j] = (f > 0.f || f != f) ? a.v[j] : from_f<T>(0.f);
+    }
+    st_pack<T, V>(y + i * V, o);
+  }
+}
+
+// dx = dy * (y > 0)
+template <typename T, int V>
+__global__ void relu_bwd_k(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx,
+                           int64_t nvec) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    Pack<T, V> a = ld_pack<T, V>(y + i * V), g = ld_pack<T, V>(dy + i * V), o;
+#pragma unroll
+    for (int j = 0; j < V; ++j) o.v[j] = to_f(a.v[j]) > 0.f ? g.v[j] : from_f<T>(0.f);
+    st_pack<T, V>(dx + i * V, o);
+  }
+}
+
+template <typename T, int V, bool RELU>
+__global__ void add_k(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ y,
+                      int64_t nvec) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    Pack<T, V> p = ld_pack<T, V>(a + i * V), q = ld_pack<T, V>(b + i * V), o;
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      // the reference adds in the storage dtype (output += identity), then F.relu
+      T s = from_f<T>(to_f(p.v[j]) + to_f(q.v[j]));
+      float f = to_f(s);
+      o.v[j] = (!RELU || f > 0.f || f != f) ? s : from_f<T>(0.f);
+    }
+    st_pack<T, V>(y + i * V, o);
+  }
+}
+
+// ------------------------------------------------------------------ cast
+template <typename TS, typename TD>
+__global__ void cast_k(const TS* __restrict__ s, TD* __restrict__ d, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    d[i] = from_f<TD>(to_f(s[i]));
+}
+// fp32 -> bf16, 4 elements per thread (16B load, 8B store)
+__global__ void cast_f32_bf16_v4(const float* __restrict__ s, bf16* __restrict__ d, int64_t nvec) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nvec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    Pack<float, 4> a = ld_pack<float, 4>(s + i * 4);
+    Pack<bf16, 4> o;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o.v[j] = __float2bfloat16_rn(a.v[j]);
+    st_pack<bf16, 4>(d + i * 4, o);
+  }
+}
+
+// ------------------------------------------------------------------ NCHW fp32 -> NHWC T
+// One block transposes a [C x 32] (channels x pixels) slab through shared memory so both the
+// NCHW reads (pixel-contiguous) and the NHWC writes (channel-contiguous) are coalesced.
+template <typename T>
+__global__ void nchw_to_nhwc_k(const float* __restrict__ src, T* __restrict__ dst, int C, int HW) {
+  extern __shared__ float tile[];  // [C][33]
+  const int n = blockIdx.y;
+  const int p0 = blockIdx.x * 32;
+  const float* s = src + (int64_t)n * C * HW;
+  T* o = dst + (int64_t)n * HW * C;
+  for (int i = threadIdx.x; i < C * 32; i += blockDim.x) {
+    int c = i / 32, p = i % 32;
+    tile[c * 33 + p] = (p0 + p < HW) ? s[(int64_t)c * HW + p0 + p] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C * 32; i += blockDim.x) {
+    int p = i / C, c = i % C;
+    if (p0 + p < HW) o[(int64_t)(p0 + p) * C + c] = from_f<T>(tile[c * 33 + p]);
+  }
+}
+
+// ------------------------------------------------------------------ channel shuffle / slab copy
+// y[m, j*g + i] = x[m, i*(C/g) + j]; one thread per output element pair is fine: rows are short
+// and both sides stay within one row (L1/L2 absorb the permutation), traffic = 2 * numel.
+template <typename T>
+__global__ void shuffle_k(const T* __restrict__ x, T* __restrict__ y, int64_t M, int C, int g) {
+  const int cpg = C / g;
+  const int64_t total = M * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t m = i / C;
+    int co = (int)(i - m * C);
+    int j = co / g, gi = co - j * g;
+    y[i] = x[m * C + (int64_t)gi * cpg + j];
+  }
+}
+
+template <typename T, int V>
+__global__ void copy_channels_k(const T* __restrict__ src, int srcC, int srcOff,
+                                T* __restrict__ dst, int dstC, int dstOff, int64_t M, int Cv) {
+  const int64_t total = M * Cv;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t m = i / Cv;
+    int c = (int)(i - m * Cv) * V;
+    st_pack<T, V>(dst + m * dstC + dstOff + c, ld_pack<T, V>(src + m * srcC + srcOff + c));
+  }
+}
+
+// ------------------------------------------------------------------ global average pool
+// grid (N, ceil(C / (V*CV))), block (CV, RY): thread (cx, ry) sums rows ry, ry+RY, ... of its V
+// channels; cross-ry reduction in shared memory.  One pass over x.
+template <typename T, int V>
+__global__ void gap_fwd_k(const T* __restrict__ x, const T* __restrict__ x2, float* __restrict__ y,
+                          int HW, int C) {
+  extern __shared__ float red[];  // [RY][CV*V]
+  const int n = blockIdx.x;
+  const int cv = blockIdx.y * blockDim.x + threadIdx.x;
+  const int c0 = cv * V;
+  float acc[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) acc[j] = 0.f;
+  if (c0 < C) {
+    const T* base = x + (int64_t)n * HW * C + c0;
+    const T* base2 = x2 ? x2 + (int64_t)n * HW * C + c0 : nullptr;
+    for (int r = threadIdx.y; r < HW; r += blockDim.y) {
+      Pack<T, V> a = ld_pack<T, V>(base + (int64_t)r * C);
+#pragma unroll
+      for (int j = 0; j < V; ++j) acc[j] += to_f(a.v[j]);
+      if (base2) {
+        Pack<T, V> b = ld_pack<T, V>(base2 + (int64_t)r * C);
+#pragma unroll
+        for (int j = 0; j < V; ++j) acc[j] += to_f(b.v[j]);
+      }
+    }
+  }
+  const int W = blockDim.x * V;
+#pragma unroll
+  for (int j = 0; j < V; ++j) red[threadIdx.y * W + threadIdx.x * V + j] = acc[j];
+  __syncthreads();
+  if (threadIdx.y == 0 && c0 < C) {
+    const float inv = 1.f / (float)HW;
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      float s = 0.f;
+      for (int r = 0; r < (int)blockDim.y; ++r) s += red[r * W + threadIdx.x * V + j];
+      y[(int64_t)n * C + c0 + j] = s * inv;
+    }
+  }
+}
+
+template <typename T, int V>
+__global__ void gap_bwd_k(const float* __restrict__ dy, T* __restrict__ dx, int64_t total_vec,
+                          int HW, int Cv) {
+  const float inv = 1.f / (float)HW;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t row = i / Cv;
+    int cv = (int)(i - row * Cv);
+    int64_t n = row / HW;
+    Pack<T, V> o;
+#pragma unroll
+    for (int j = 0; j < V; ++j) o.v[j] = from_f<T>(dy[n * (int64_t)Cv * V + cv * V + j] * inv);
+    st_pack<T, V>(dx + i * V, o);
+  }
+}
+
+// ------------------------------------------------------------------ SE scale
+template <typename T, int V>
+__global__ void se_scale_fwd_k(const T* __restrict__ x, const float* __restrict__ s,
+                               T* __restrict__ y, int64_t total_vec, int HW, int Cv) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t row = i / Cv;
+    int cv = (int)(i - row * Cv);
+    int64_t n = row / HW;
+    const float* sp = s + n * (int64_t)Cv * V + cv * V;
+    Pack<T, V> a = ld_pack<T, V>(x + i * V), o;
+#pragma unroll
+    for (int j = 0; j < V; ++j) o.v[j] = from_f<T>(to_f(a.v[j]) * to_f(from_f<T>(sp[j])));
+    st_pack<T, V>(y + i * V, o);
+  }
+}
+
+// dx = dy * s ; ds[n,c] = sum_hw dy*x.  Same thread layout as gap_fwd_k (one pass over x, dy).
+template <typename T, int V>
+__global__ void se_scale_bwd_k(const T* __restrict__ x, const float* __restrict__ s,
+                               const T* __restrict__ dy, T* __restrict__ dx,
+                               float* __restrict__ ds, int HW, int C) {
+  extern __shared__ float red[];
+  const int n = blockIdx.x;
+  const int cv = blockIdx.y * blockDim.x + threadIdx.x;
+  const int c0 = cv * V;
+  float acc[V], sv[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) acc[j] = 0.f;
+  if (c0 < C) {
+#pragma unroll
+    for (int j = 0; j < V; ++j) sv[j] = to_f(from_f<T>(s[(int64_t)n * C + c0 + j]));
+    const int64_t base = (int64_t)n * HW * C + c0;
+    for (int r = threadIdx.y; r < HW; r += blockDim.y) {
+      Pack<T, V> a = ld_pack<T, V>(x + base + (int64_t)r * C);
+      Pack<T, V> g = ld_pack<T, V>(dy + base + (int64_t)r * C), o;
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        float gf = to_f(g.v[j]);
+        acc[j] += gf * to_f(a.v[j]);
+        o.v[j] = from_f<T>(gf * sv[j]);
+      }
+      st_pack<T, V>(dx + base + (int64_t)r * C, o);
+    }
+  }
+  const int W = blockDim.x * V;
+#pragma unroll
+  for (int j = 0; j < V; ++j) red[threadIdx.y * W + threadIdx.x * V + j] = acc[j];
+  __syncthreads();
+  if (threadIdx.y == 0 && c0 < C) {
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      float t = 0.f;
+      for (int r = 0; r < (int)blockDim.y; ++r) t += red[r * W + threadIdx.x * V + j];
+      ds[(int64_t)n * C + c0 + j] = t;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ SK select
+// attn = softmax over 2 paths; written once per (n,c) by a tiny kernel, then applied.
+__global__ void sk_softmax2_k(const float* __restrict__ logits, float* __restrict__ attn, int N,
+                              int C) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N * C) return;
+  int n = i / C, c = i % C;
+  float l0 = logits[((int64_t)n * 2 + 0) * C + c], l1 = logits[((int64_t)n * 2 + 1) * C + c];
+  float m = fmaxf(l0, l1);
+  float e0 = expf(l0 - m), e1 = expf(l1 - m);
+  float inv = 1.f / (e0 + e1);
+  attn[((int64_t)n * 2 + 0) * C + c] = e0 * inv;
+  attn[((int64_t)n * 2 + 1) * C + c] = e1 * inv;
+}
+
+template <typename T, int V>
+__global__ void sk_select_fwd_k(const T* __restrict__ u0, const T* __restrict__ u1,
+                                const float* __restrict__ attn, T* __restrict__ y,
+                                int64_t total_vec, int HW, int Cv) {
+  const int C = Cv * V;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t row = i / Cv;
+    int cv = (int)(i - row * Cv);
+    int64_t n = row / HW;
+    const float* a0 = attn + (n * 2 + 0) * C + cv * V;
+    const float* a1 = attn + (n * 2 + 1) * C + cv * V;
+    Pack<T, V> p = ld_pack<T, V>(u0 + i * V), q = ld_pack<T, V>(u1 + i * V), o;
+#pragma unroll
+    for (int j = 0; j < V; ++j) o.v[j] = from_f<T>(to_f(p.v[j]) * a0[j] + to_f(q.v[j]) * a1[j]);
+    st_pack<T, V>(y + i * V, o);
+  }
+}
+
+// du_i = dy*a_i + dg/HW ; t_i[n,c] = sum_hw dy*u_i ; dlogit_i = a_i*(t_i - (a0*t0 + a1*t1))
+template <typename T, int V>
+__global__ void sk_select_bwd_k(const T* __restrict__ u0, const T* __restrict__ u1,
+                                const float* __restrict__ attn, const T* __restrict__ dy,
+                                const float* __restrict__ dg, T* __restrict__ du0,
+                                T* __restrict__ du1, float* __restrict__ dlogits, int HW, int C) {
+  extern __shared__ float red[];  // [RY][2][W]
+  const int n = blockIdx.x;
+  const int cv = blockIdx.y * blockDim.x + threadIdx.x;
+  const int c0 = cv * V;
+  float t0[V], t1[V], a0[V], a1[V], g[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) t0[j] = t1[j] = 0.f;
+  if (c0 < C) {
+    const float inv = 1.f / (float)HW;
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      a0[j] = attn[((int64_t)n * 2 + 0) * C + c0 + j];
+      a1[j] = attn[((int64_t)n * 2 + 1) * C + c0 + j];
+      g[j] = dg ? dg[(int64_t)n * C + c0 + j] * inv : 0.f;
+    }
+    const int64_t base = (int64_t)n * HW * C + c0;
+    for (int r = threadIdx.y; r < HW; r += blockDim.y) {
+      const int64_t o = base + (int64_t)r * C;
+      Pack<T, V> p = ld_pack<T, V>(u0 + o), q = ld_pack<T, V>(u1 + o), d = ld_pack<T, V>(dy + o);
+      Pack<T, V> o0, o1;
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        float df = to_f(d.v[j]);
+        t0[j] += df * to_f(p.v[j]);
+        t1[j] += df * to_f(q.v[j]);
+        o0.v[j] = from_f<T>(df * a0[j] + g[j]);
+        o1.v[j] = from_f<T>(df * a1[j] + g[j]);
+      }
+      st_pack<T, V>(du0 + o, o0);
+      st_pack<T, V>(du1 + o, o1);
+    }
+  }
+  const int W = blockDim.x * V;
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    red[(threadIdx.y * 2 + 0) * W + threadIdx.x * V + j] = t0[j];
+    red[(threadIdx.y * 2 + 1) * W + threadIdx.x * V + j] = t1[j];
+  }
+  __syncthreads();
+  if (threadIdx.y == 0 && c0 < C) {
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      float s0 = 0.f, s1 = 0.f;
+      for (int r = 0; r < (int)blockDim.y; ++r) {
+        s0 += red[(r * 2 + 0) * W + threadIdx.x * V + j];
+        s1 += red[(r * 2 + 1) * W + threadIdx.x * V + j];
+      }
+      float dot = a0[j] * s0 + a1[j] * s1;
+      dlogits[((int64_t)n * 2 + 0) * C + c0 + j] = a0[j] * (s0 - dot);
+      dlogits[((int64_t)n * 2 + 1) * C + c0 + j] = a1[j] * (s1 - dot);
+    }
+  }
+}
+
+// block geometry for the (n, channel-chunk) x rows reductions
+struct RedGeom {
+  dim3 grid, block;
+  size_t smem;
+};
+static RedGeom red_geom(int N, int C, int V, int planes) {
+  int cvs = C / V;
+  int cx = cvs < 32 ? cvs : 32;
+  // keep cx a power of two <= cvs for simple coverage; gridDim.y covers the remainder
+  int p = 1;
+  while (p * 2 <= cx) p *= 2;
+  cx = p;
+  int ry = 256 / cx;
+  RedGeom g;
+  g.block = dim3(cx, ry);
+  g.grid = dim3(N, (unsigned)ceil_div(cvs, cx));
+  g.smem = (size_t)ry * cx * V * sizeof(float) * planes;
+  return g;
+}
+
+}  // namespace cnb
+
+using namespace cnb;
+
+// ======================================================================= C ABI
+extern "C" {
+
+const char* cnb_version(void) { return "convnets_b200 0.1.0 (sm_100a)"; }
+const char* cnb_last_error(void) { return cnb::g_last_error; }
+uint64_t cnb_launch_count(void) { return cnb::g_launches.load(); }
+
+int cnb_relu_fwd(const void* x, void* y, int64_t n, int dtype, void* stream) {
+  CNB_REQUIRE(x && y && n >= 0 && valid_dtype(dtype), CNB_ERR_INVALID, "cnb_relu_fwd: bad args");
+  if (n == 0) return CNB_OK;
+  int v = pick_vec(n, dtype_size(dtype), x, y);
+  CNB_DISPATCH_TV(dtype, v, (relu_fwd_k<T, V><<<grid_for(n / V, kThreads), kThreads, 0,
+                                                 (cudaStream_t)stream>>>((const T*)x, (T*)y, n / V)));
+  return check_launch("relu_fwd");
+}
+
+int cnb_relu_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype, void* stream) {
+  CNB_REQUIRE(y && dy && dx && n >= 0 && valid_dtype(dtype), CNB_ERR_INVALID,
+              "cnb_relu_bwd: bad args");
+  if (n == 0) return CNB_OK;
+  int v = pick_vec(n, dtype_size(dtype), y, dy, dx);
+  CNB_DISPATCH_TV(dtype, v,
+                  (relu_bwd_k<T, V><<<grid_for(n / V, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+                      (const T*)y, (const T*)dy, (T*)dx, n / V)));
+  return check_launch("relu_bwd");
+}
+
+int cnb_add_relu_fwd(const void* a, const void* b, void* y, int64_t n, int dtype, void* stream) {
+  CNB_REQUIRE(a && b && y && n >= 0 && valid_dtype(dtype), CNB_ERR_INVALID,
+              "cnb_add_relu_fwd: bad args");
+  if (n == 0) return CNB_OK;
+  int v = pick_vec(n, dtype_size(dtype), a, b, y);
+  CNB_DISPATCH_TV(dtype, v,
+                  (add_k<T, V, true><<<grid_for(n / V, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+                      (const T*)a, (const T*)b, (T*)y, n / V)));
+  return check_launch("add_relu_fwd");
+}
+
+int cnb_add_relu_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype, void* stream) {
+  return cnb_relu_bwd(y, dy, dx, n, dtype, stream);
+}
+
+int cnb_add(const void* a, const void* b, void* y, int64_t n, int dtype, void* stream) {
+  CNB_REQUIRE(a && b && y && n >= 0 && valid_dtype(dtype), CNB_ERR_INVALID, "cnb_add: bad args");
+  if (n == 0) return CNB_OK;
+  int v = pick_vec(n, dtype_size(dtype), a, b, y);
+  CNB_DISPATCH_TV(dtype, v,
+                  (add_k<T, V, false><<<grid_for(n / V, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+                      (const T*)a, (const T*)b, (T*)y, n / V)));
+  return check_launch("add");
+}
+
+int cnb_cast(const void* src, int sdt, void* dst, int ddt, int64_t n, void* stream) {
+  CNB_REQUIRE(src && dst && n >= 0 && valid_dtype(sdt) && valid_dtype(ddt), CNB_ERR_INVALID,
+              "cnb_cast: bad args");
+  if (n == 0) return CNB_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (sdt == CNB_F32 && ddt == CNB_BF16) {
+    if (n % 4 == 0 && (uintptr_t)src % 16 == 0 && (uintptr_t)dst % 8 == 0)
+      cast_f32_bf16_v4<<<grid_for(n / 4, kThreads), kThreads, 0, st>>>((const float*)src,
+                                                                       (bf16*)dst, n / 4);
+    else
+      cast_k<float, bf16><<<grid_for(n, kThreads), kThreads, 0, st>>>((const float*)src, (bf16*)dst, n);
+  } else if (sdt == CNB_BF16 && ddt == CNB_F32) {
+    cast_k<bf16, float><<<grid_for(n, kThreads), kThreads, 0, st>>>((const bf16*)src, (float*)dst, n);
+  } else if (sdt == CNB_F32) {
+    cast_k<float, float><<<grid_for(n, kThreads), kThreads, 0, st>>>((const float*)src, (float*)dst, n);
+  } else {
+    cast_k<bf16, bf16><<<grid_for(n, kThreads), kThreads, 0, st>>>((const bf16*)src, (bf16*)dst, n);
+  }
+  return check_launch("cast");
+}
+
+int cnb_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t H, int32_t W,
+                     int dtype, void* stream) {
+  CNB_REQUIRE(src && dst && N > 0 && C > 0 && H > 0 && W > 0 && valid_dtype(dtype), CNB_ERR_INVALID,
+              "cnb_nchw_to_nhwc: bad args");
+  CNB_REQUIRE((size_t)C * 33 * 4 <= 48 * 1024, CNB_ERR_UNSUPPORTED,
+              "cnb_nchw_to_nhwc: C=%d too large (input-image conversion only)", C);
+  int HW = H * W;
+  dim3 grid((unsigned)ceil_div(HW, 32), N);
+  size_t smem = (size_t)C * 33 * sizeof(float);
+  CNB_DISPATCH_T(dtype, (nchw_to_nhwc_k<T><<<grid, 256, smem, (cudaStream_t)stream>>>(src, (T*)dst, C, HW)));
+  return check_launch("nchw_to_nhwc");
+}
+
+int cnb_channel_shuffle(const void* x, void* y, int64_t M, int32_t C, int32_t groups, int dtype,
+                        void* stream) {
+  CNB_REQUIRE(x && y && M >= 0 && C > 0 && groups > 0 && valid_dtype(dtype), CNB_ERR_INVALID,
+              "cnb_channel_shuffle: bad args");
+  CNB_REQUIRE(C % groups == 0, CNB_ERR_INVALID, "cnb_channel_shuffle: C=%d not divisible by groups=%d",
+              C, groups);
+  if (M == 0) return CNB_OK;
+  CNB_DISPATCH_T(dtype, (shuffle_k<T><<<grid_for(M * C, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+                            (const T*)x, (T*)y, M, C, groups)));
+  return check_launch("channel_shuffle");
+}
+
+int cnb_copy_channels(const void* src, int32_t src_C, int32_t src_off, void* dst, int32_t dst_C,
+                      int32_t dst_off, int64_t M, int32_t Ccopy, int dtype, void* stream) {
+  CNB_REQUIRE(src && dst && M >= 0 && Ccopy > 0 && valid_dtype(dtype), CNB_ERR_INVALID,
+              "cnb_copy_channels: bad args");
+  CNB_REQUIRE(src_off >= 0 && dst_off >= 0 && src_off + Ccopy <= src_C && dst_off + Ccopy <= dst_C,
+              CNB_ERR_INVALID, "cnb_copy_channels: slab [%d,+%d) / [%d,+%d) outside rows of %d / %d",
+              src_off, Ccopy, dst_off, Ccopy, src_C, dst_C);
+  if (M == 0) return CNB_OK;
+  size_t esz = dtype_size(dtype);
+  int v = (int)(16 / esz);
+  auto ok = [&](int vv) {
+    return Ccopy % vv == 0 && src_C % vv == 0 && dst_C % vv == 0 && src_off % vv == 0 &&
+           dst_off % vv == 0 && (uintptr_t)src % (vv * esz) == 0 && (uintptr_t)dst % (vv * esz) == 0;
+  };
+  while (v > 1 && !ok(v)) v >>= 1;
+  CNB_DISPATCH_TV(dtype, v,
+                  (copy_channels_k<T, V><<<grid_for(M * (Ccopy / V), kThreads), kThreads, 0,
+                                           (cudaStream_t)stream>>>((const T*)src, src_C, src_off,
+                                                                   (T*)dst, dst_C, dst_off, M,
+                                                                   Ccopy / V)));
+  return check_launch("copy_channels");
+}
+
+int cnb_gap_fwd(const void* x, float* y, int32_t N, int32_t HW, int32_t C, int dtype, void* stream) {
+  CNB_REQUIRE(x && y && N > 0 && HW > 0 && C > 0 && valid_dtype(dtype), CNB_ERR_INVALID,
+              "cnb_gap_fwd: bad args");
+  int v = pick_vec(C, dtype_size(dtype), x);
+  RedGeom g = red_geom(N, C, v, 1);
+  CNB_DISPATCH_TV(dtype, v, (gap_fwd_k<T, V><<<g.grid, g.block, g.smem, (cudaStream_t)stream>>>(
+                                (const T*)x, (const T*)nullptr, y, HW, C)));
+  return check_launch("gap_fwd");
+}
+
+int cnb_sk_fuse_gap_fwd(const void* u0, const void* u1, float* gout, int32_t N, int32_t HW,
+                        int32_t C, int dtype, void* stream) {
+  CNB_REQUIRE(u0 && u1 && gout && N > 0 && HW > 0 && C > 0 && valid_dtype(dtype), CNB_ERR_INVALID,
+              "cnb_sk_fuse_gap_fwd: bad args");
+  int v = pick_vec(C, dtype_size(dtype), u0, u1);
+  RedGeom g = red_geom(N, C, v, 1);
+  CNB_DISPATCH_TV(dtype, v, (gap_fwd_k<T, V><<<g.grid, g.block, g.smem, (cudaStream_t)stream>>>(
+                                (const T*)u0, (const T*)u1, gout, HW, C)));
+  return check_launch("sk_fuse_gap_fwd");
+}
+
+int cnb_gap_bwd(const float* dy, void* dx, int32_t N, int32_t HW, int32_t C, int dtype,
+                void* stream) {
+  CNB_REQUIRE(dy && dx && N > 0 && HW > 0 && C > 0 && valid_dtype(dtype), CNB_ERR_INVALID,
+              "cnb_gap_bwd: bad args");
+  int v = pick_vec(C, dtype_size(dtype), dx);
+  int64_t total = (int64_t)N * HW * (C / v);
+  CNB_DISPATCH_TV(dtype, v, (gap_bwd_k<T, V><<<grid_for(total, kThreads), kThreads, 0,
+                                                (cudaStream_t)stream>>>(dy, (T*)dx, total, HW, C / V)));
+  return check_launch("gap_bwd");
+}
+
+int cnb_se_scale_fwd(const void* x, const float* s, void* y, int32_t N, int32_t HW, int32_t C,
+                     int dtype, void* stream) {
+  CNB_REQUIRE(x && s && y && N > 0 && HW > 0 && C > 0 && valid_dtype(dtype), CNB_ERR_INVALID,
+              "cnb_se_scale_fwd: bad args");
+  int v = pick_vec(C, dtype_size(dtype), x, y);
+  int64_t total = (int64_t)N * HW * (C / v);
+  CNB_DISPATCH_TV(dtype, v,
+                  (se_scale_fwd_k<T, V><<<grid_for(total, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+                      (const T*)x, s, (T*)y, total, HW, C / V)));
+  return check_launch("se_scale_fwd");
+}
+
+int cnb_se_scale_bwd(const void* x, const float* s, const void* dy, void* dx, float* ds, int32_t N,
+                     int32_t HW, int32_t C, int dtype, void* stream) {
+  CNB_REQUIRE(x && s && dy && dx && ds && N > 0 && HW > 0 && C > 0 && valid_dtype(dtype),
+              CNB_ERR_INVALID, "cnb_se_scale_bwd: bad args");
+  int v = pick_vec(C, dtype_size(dtype), x, dy, dx);
+  RedGeom g = red_geom(N, C, v, 1);
+  CNB_DISPATCH_TV(dtype, v, (se_scale_bwd_k<T, V><<<g.grid, g.block, g.smem, (cudaStream_t)stream>>>(
+                                (const T*)x, s, (const T*)dy, (T*)dx, ds, HW, C)));
+  return check_launch("se_scale_bwd");
+}
+
+int cnb_sk_select_fwd(const void* u0, const void* u1, const float* logits, float* attn, void* y,
+                      int32_t N, int32_t HW, int32_t C, int dtype, void* stream) {
+  CNB_REQUIRE(u0 && u1 && logits && attn && y && N > 0 && HW > 0 && C > 0 && valid_dtype(dtype),
+              CNB_ERR_INVALID, "cnb_sk_select_fwd: bad args");
+  cudaStream_t st = (cudaStream_t)stream;
+  sk_softmax2_k<<<(unsigned)ceil_div((int64_t)N * C, 256), 256, 0, st>>>(logits, attn, N, C);
+  CNB_TRY(check_launch("sk_softmax2"));
+  int v = pick_vec(C, dtype_size(dtype), u0, u1, y);
+  if (v > 4) v = 4;  // attn is read as scalars; keep register pressure low
+  int64_t total = (int64_t)N * HW * (C / v);
+  CNB_DISPATCH_TV(dtype, v, (sk_select_fwd_k<T, V><<<grid_for(total, kThreads), kThreads, 0, st>>>(
+                                (const T*)u0, (const T*)u1, attn, (T*)y, total, HW, C / V)));
+  return check_launch("sk_select_fwd");
+}
+
+int cnb_sk_select_bwd(const void* u0, const void* u1, const float* attn, const void* dy,
+                      const float* dg, void* du0, void* du1, float* dlogits, int32_t N, int32_t HW,
+                      int32_t C, int dtype, void* stream) {
+  CNB_REQUIRE(u0 && u1 && attn && dy && du0 && du1 && dlogits && N > 0 && HW > 0 && C > 0 &&
+                  valid_dtype(dtype),
+              CNB_ERR_INVALID, "cnb_sk_select_bwd: bad args");
+  int v = pick_vec(C, dtype_size(dtype), u0, u1, dy, du0);
+  if (v > 4) v = 4;
+  while (v > 1 && (uintptr_t)du1 % (v * dtype_size(dtype)) != 0) v >>= 1;
+  RedGeom g = red_geom(N, C, v, 2);
+  CNB_DISPATCH_TV(dtype, v, (sk_select_bwd_k<T, V><<<g.grid, g.block, g.smem, (cudaStream_t)stream>>>(
+                                (const T*)u0, (const T*)u1, attn, (const T*)dy, dg, (T*)du0,
+                                (T*)du1, dlogits, HW, C)));
+  return check_launch("sk_select_bwd");
+}
+
+}  // extern "C"

@@ -1,0 +1,255 @@
+// pool.cu — max / average pooling forward and backward over NHWC tensors (HBM-bound).
+// Replaces aten::max_pool2d_with_indices(_backward) and aten::avg_pool2d(_backward) reached from
+// reference src/basemodel.py:1017-1033.  One thread handles V contiguous channels of one output
+// (forward) or input (backward) pixel; backward is a gather, so it needs neither atomics nor a
+// zero-fill pass and is deterministic.
+#include <math_constants.h>
+
+#include "common.cuh"
+
+namespace cnb {
+
+constexpr int kPoolThreads = 256;
+
+struct PoolP {
+  int N, H, W, C, P, Q, kh, kw, sh, sw, ph, pw;
+};
+
+// PyTorch rule (aten/src/ATen/native/cuda/DilatedMaxPool2d.cu): scan the window row-major over
+// in-bounds positions only, take `val > max || isnan(val)`; index = h*W + w.
+template <typename T, int V>
+__global__ void maxpool_fwd_k(const T* __restrict__ x, T* __restrict__ y, int32_t* __restrict__ idx,
+                              PoolP p, int64_t total_vec) {
+  const int Cv = p.C / V;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int cv = (int)(i % Cv);
+    int64_t pix = i / Cv;
+    int q = (int)(pix % p.Q);
+    int64_t t = pix / p.Q;
+    int oh = (int)(t % p.P);
+    int n = (int)(t / p.P);
+    int h0 = oh * p.sh - p.ph, w0 = q * p.sw - p.pw;
+    int h1 = min(h0 + p.kh, p.H), w1 = min(w0 + p.kw, p.W);
+    h0 = max(h0, 0);
+    w0 = max(w0, 0);
+    float best[V];
+    int bi[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      best[j] = -CUDART_INF_F;
+      bi[j] = h0 * p.W + w0;
+    }
+    const T* base = x + (int64_t)n * p.H * p.W * p.C + cv * V;
+    for (int h = h0; h < h1; ++h)
+      for (int w = w0; w < w1; ++w) {
+        Pack<T, V> a = ld_pack<T, V>(base + ((int64_t)h * p.W + w) * p.C);
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          float f = to_f(a.v[j]);
+          if (f > best[j] || f != f) {
+            best[j] = f;
+            bi[j] = h * p.W + w;
+          }
+        }
+      }
+    Pack<T, V> o;
+    Pack<int32_t, V> oi;
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      o.v[j] = from_f<T>(best[j]);
+      oi.v[j] = bi[j];
+    }
+    st_pack<T, V>(y + i * V, o);
+    st_pack<int32_t, V>(idx + i * V, oi);
+  }
+}
+
+// dx[n,h,w,c] = sum over output windows containing (h,w) of dy * (idx == h*W+w)
+template <typename T, int V>
+__global__ void maxpool_bwd_k(const T* __restrict__ dy, const int32_t* __restrict__ idx,
+                              T* __restrict__ dx, PoolP p, int64_t total_vec) {
+  const int Cv = p.C / V;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int cv = (int)(i % Cv);
+    int64_t pix = i / Cv;
+    int w = (int)(pix % p.W);
+    int64_t t = pix / p.W;
+    int h = (int)(t % p.H);
+    int n = (int)(t / p.H);
+    // output rows oh with oh*sh - ph <= h < oh*sh - ph + kh
+    int oh_lo = (h + p.ph - p.kh + p.sh) / p.sh;  // ceil((h+ph-kh+1)/sh)
+    if (h + p.ph - p.kh + 1 <= 0) oh_lo = 0;
+    int oh_hi = min((h + p.ph) / p.sh, p.P - 1);
+    int ow_lo = (w + p.pw - p.kw + p.sw) / p.sw;
+    if (w + p.pw - p.kw + 1 <= 0) ow_lo = 0;
+    int ow_hi = min((w + p.pw) / p.sw, p.Q - 1);
+    const int me = h * p.W + w;
+    float acc[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] = 0.f;
+    for (int oh = oh_lo; oh <= oh_hi; ++oh)
+      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+        int64_t o = (((int64_t)n * p.P + oh) * p.Q + ow) * p.C + cv * V;
+        Pack<int32_t, V> ii = ld_pack<int32_t, V>(idx + o);
+        Pack<T, V> g = ld_pack<T, V>(dy + o);
+#pragma unroll
+        for (int j = 0; j < V; ++j)
+          if (ii.v[j] == me) acc[j] += to_f(g.v[j]);
+      }
+    Pack<T, V> out;
+#pragma unroll
+    for (int j = 0; j < V; ++j) out.v[j] = from_f<T>(acc[j]);
+    st_pack<T, V>(dx + i * V, out);
+  }
+}
+
+// count_include_pad=True: divisor is always kh*kw; padded positions contribute zero.
+template <typename T, int V>
+__global__ void avgpool_fwd_k(const T* __restrict__ x, T* __restrict__ y, PoolP p,
+                              int64_t total_vec) {
+  const int Cv = p.C / V;
+  const float inv = 1.f / (float)(p.kh * p.kw);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int cv = (int)(i % Cv);
+    int64_t pix = i / Cv;
+    int q = (int)(pix % p.Q);
+    int64_t t = pix / p.Q;
+    int oh = (int)(t % p.P);
+    int n = (int)(t / p.P);
+    int h0 = oh * p.sh - p.ph, w0 = q * p.sw - p.pw;
+    int h1 = min(h0 + p.kh, p.H), w1 = min(w0 + p.kw, p.W);
+    h0 = max(h0, 0);
+    w0 = max(w0, 0);
+    float acc[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] = 0.f;
+    const T* base = x + (int64_t)n * p.H * p.W * p.C + cv * V;
+    for (int h = h0; h < h1; ++h)
+      for (int w = w0; w < w1; ++w) {
+        Pack<T, V> a = ld_pack<T, V>(base + ((int64_t)h * p.W + w) * p.C);
+#pragma unroll
+        for (int j = 0; j < V; ++j) acc[j] += to_f(a.v[j]);
+      }
+    Pack<T, V> o;
+#pragma unroll
+    for (int j = 0; j < V; ++j) o.v[j] = from_f<T>(acc[j] * inv);
+    st_pack<T, V>(y + i * V, o);
+  }
+}
+
+template <typename T, int V>
+__global__ void avgpool_bwd_k(const T* __restrict__ dy, T* __restrict__ dx, PoolP p,
+                              int64_t total_vec) {
+  const int Cv = p.C / V;
+  const float inv = 1.f / (float)(p.kh * p.kw);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int cv = (int)(i % Cv);
+    int64_t pix = i / Cv;
+    int w = (int)(pix % p.W);
+    int64_t t = pix / p.W;
+    int h = (int)(t % p.H);
+    int n = (int)(t / p.H);
+    int oh_lo = (h + p.ph - p.kh + p.sh) / p.sh;
+    if (h + p.ph - p.kh + 1 <= 0) oh_lo = 0;
+    int oh_hi = min((h + p.ph) / p.sh, p.P - 1);
+    int ow_lo = (w + p.pw - p.kw + p.sw) / p.sw;
+    if (w + p.pw - p.kw + 1 <= 0) ow_lo = 0;
+    int ow_hi = min((w + p.pw) / p.sw, p.Q - 1);
+    float acc[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[j] = 0.f;
+    for (int oh = oh_lo; oh <= oh_hi; ++oh)
+      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+        int64_t o = (((int64_t)n * p.P + oh) * p.Q + ow) * p.C + cv * V;
+        Pack<T, V> g = ld_pack<T, V>(dy + o);
+#pragma unroll
+        for (int j = 0; j < V; ++j) acc[j] += to_f(g.v[j]);
+      }
+    Pack<T, V> out;
+#pragma unroll
+    for (int j = 0; j < V; ++j) out.v[j] = from_f<T>(acc[j] * inv);
+    st_pack<T, V>(dx + i * V, out);
+  }
+}
+
+static int make_pool(const cnb_pool_desc* d, PoolP& p, const char* who) {
+  CNB_REQUIRE(d != nullptr, CNB_ERR_INVALID, "%s: null descriptor", who);
+  CNB_REQUIRE(d->N > 0 && d->H > 0 && d->W > 0 && d->C > 0 && d->kh > 0 && d->kw > 0 &&
+                  d->stride_h > 0 && d->stride_w > 0 && d->pad_h >= 0 && d->pad_w >= 0 &&
+                  valid_dtype(d->dtype),
+              CNB_ERR_INVALID, "%s: bad descriptor", who);
+  // PyTorch: pad should be at most half of kernel size
+  CNB_REQUIRE(d->pad_h * 2 <= d->kh && d->pad_w * 2 <= d->kw, CNB_ERR_INVALID,
+              "%s: pad should be at most half of kernel size", who);
+  p = PoolP{d->N, d->H, d->W, d->C, 0, 0, d->kh, d->kw, d->stride_h, d->stride_w, d->pad_h, d->pad_w};
+  p.P = (d->H + 2 * d->pad_h - d->kh) / d->stride_h + 1;
+  p.Q = (d->W + 2 * d->pad_w - d->kw) / d->stride_w + 1;
+  CNB_REQUIRE(p.P > 0 && p.Q > 0, CNB_ERR_INVALID, "%s: output size is too small (%dx%d)", who, p.P,
+              p.Q);
+  return CNB_OK;
+}
+
+}  // namespace cnb
+
+using namespace cnb;
+
+extern "C" {
+
+int cnb_maxpool_fwd(const cnb_pool_desc* d, const void* x, void* y, int32_t* idx, void* stream) {
+  PoolP p;
+  CNB_TRY(make_pool(d, p, "cnb_maxpool_fwd"));
+  CNB_REQUIRE(x && y && idx, CNB_ERR_INVALID, "cnb_maxpool_fwd: null pointer");
+  int v = pick_vec(p.C, dtype_size(d->dtype), x, y);
+  if (v > 4) v = 4;
+  while (v > 1 && (uintptr_t)idx % (v * 4) != 0) v >>= 1;
+  int64_t total = (int64_t)p.N * p.P * p.Q * (p.C / v);
+  CNB_DISPATCH_TV(d->dtype, v,
+                  (maxpool_fwd_k<T, V><<<grid_for(total, kPoolThreads), kPoolThreads, 0,
+                                         (cudaStream_t)stream>>>((const T*)x, (T*)y, idx, p, total)));
+  return check_launch("maxpool_fwd");
+}
+
+int cnb_maxpool_bwd(const cnb_pool_desc* d, const void* dy, const int32_t* idx, void* dx,
+                    void* stream) {
+  PoolP p;
+  CNB_TRY(make_pool(d, p, "cnb_maxpool_bwd"));
+  CNB_REQUIRE(dy && idx && dx, CNB_ERR_INVALID, "cnb_maxpool_bwd: null pointer");
+  int v = pick_vec(p.C, dtype_size(d->dtype), dy, dx);
+  if (v > 4) v = 4;
+  while (v > 1 && (uintptr_t)idx % (v * 4) != 0) v >>= 1;
+  int64_t total = (int64_t)p.N * p.H * p.W * (p.C / v);
+  CNB_DISPATCH_TV(d->dtype, v,
+                  (maxpool_bwd_k<T, V><<<grid_for(total, kPoolThreads), kPoolThreads, 0,
+                                         (cudaStream_t)stream>>>((const T*)dy, idx, (T*)dx, p, total)));
+  return check_launch("maxpool_bwd");
+}
+
+int cnb_avgpool_fwd(const cnb_pool_desc* d, const void* x, void* y, void* stream) {
+  PoolP p;
+  CNB_TRY(make_pool(d, p, "cnb_avgpool_fwd"));
+  CNB_REQUIRE(x && y, CNB_ERR_INVALID, "cnb_avgpool_fwd: null pointer");
+  int v = pick_vec(p.C, dtype_size(d->dtype), x, y);
+  int64_t total = (int64_t)p.N * p.P * p.Q * (p.C / v);
+  CNB_DISPATCH_TV(d->dtype, v,
+                  (avgpool_fwd_k<T, V><<<grid_for(total, kPoolThreads), kPoolThreads, 0,
+                                         (cudaStream_t)stream>>>((const T*)x, (T*)y, p, total)));
+  return check_launch("avgpool_fwd");
+}
+
+int cnb_avgpool_bwd(const cnb_pool_desc* d, const void* dy, void* dx, void* stream) {
+  PoolP p;
+  CNB_TRY(make_pool(d, p, "cnb_avgpool_bwd"));
+  CNB_REQUIRE(dy && dx, CNB_ERR_INVALID, "cnb_avgpool_bwd: null pointer");
+  int v = pick_vec(p.C, dtype_size(d->dtype), dy, dx);
+  int64_t total = (int64_t)p.N * p.H * p.W * (p.C / v);
+  CNB_DISPATCH_TV(d->dtype, v,
+                  (avgpool_bwd_k<T, V><<<grid_for(total, kPoolThreads), kPoolThreads, 0,
+                                         (cudaStream_t)stream>>>((const T*)dy, (T*)dx, p, total)));
+  return check_launch("avgpool_bwd");
+}
+
+}  // extern "C"

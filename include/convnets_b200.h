@@ -1,0 +1,197 @@
+/*
+ * convnets_b200.h — C ABI of libconvnets_b200.so
+ *
+ * B200-native (sm_100a) replacement for the arithmetic layer ("L0") underneath the ConvNets
+ * architecture zoo.  The reference has no native interface of its own: every entry point below
+ * replaces a PyTorch library call the reference reaches from its layer factories
+ * (reference src/basemodel.py:966-1067) and model files; the call site each one replaces is cited
+ * on the declaration.  The reference-side binding a maintainer adds is the ctypes stub shown in
+ * INTEGRATION.md (the reference is pure Python, so ctypes is its FFI).
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch types.  All tensor pointers are DEVICE pointers
+ *     owned by the caller; the library never frees or retains them past the call.
+ *   - activations are NHWC ("channels_last"): x[n][h][w][c]; conv weights are KRSC:
+ *     w[k][r][s][c/groups]; both in `dtype` (CNB_F32 or CNB_BF16).  Weight gradients, BatchNorm
+ *     parameters / statistics and reduction outputs are always fp32.
+ *   - every function enqueues work on `stream` (a cudaStream_t passed as void*) and returns
+ *     immediately; no implicit device synchronisation.
+ *   - return value: 0 = ok, negative = cnb_status error; cnb_last_error() gives a thread-local
+ *     message.  There is NO silent fallback: an unsupported shape is an error.
+ *   - scratch memory comes from the caller, sized by the *_workspace_bytes query.
+ */
+#ifndef CONVNETS_B200_H
+#define CONVNETS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum { CNB_F32 = 0, CNB_BF16 = 1 } cnb_dtype;
+
+typedef enum {
+  CNB_OK = 0,
+  CNB_ERR_INVALID = -1,     /* bad descriptor / null pointer / misaligned pointer */
+  CNB_ERR_UNSUPPORTED = -2, /* valid but not implemented for this shape/dtype */
+  CNB_ERR_CUDA = -3,        /* launch or driver failure (message has the CUDA error string) */
+  CNB_ERR_WORKSPACE = -4    /* workspace too small */
+} cnb_status;
+
+/* cnb_conv_desc.flags (forward epilogue) */
+#define CNB_CONV_BIAS 1
+#define CNB_CONV_RELU 2
+/* cnb_conv_desc.algo */
+#define CNB_ALGO_AUTO 0 /* tcgen05 implicit GEMM when the shape qualifies, else CUDA-core */
+#define CNB_ALGO_SIMT 1 /* force the CUDA-core implicit GEMM (exact fp32 FMA accumulate) */
+#define CNB_ALGO_TC 2   /* force the tcgen05 path; error if the shape does not qualify */
+/* direction argument of the queries */
+#define CNB_FWD 0
+#define CNB_DGRAD 1
+#define CNB_WGRAD 2
+
+/* 2-D convolution problem; replaces the arguments of nn.Conv2d as built by
+ * reference src/basemodel.py:966-979 (conv2d) and :981-997 (conv2d_depthwise). */
+typedef struct cnb_conv_desc {
+  int32_t N, H, W, C; /* input batch, height, width, channels */
+  int32_t K;          /* output channels */
+  int32_t R, S;       /* filter height, width */
+  int32_t stride_h, stride_w;
+  int32_t pad_h, pad_w;
+  int32_t dil_h, dil_w;
+  int32_t groups;
+  int32_t dtype; /* cnb_dtype of x / w / y */
+  int32_t flags;
+  int32_t algo;
+} cnb_conv_desc;
+
+/* Pooling problem; replaces nn.MaxPool2d / nn.AvgPool2d as built by
+ * reference src/basemodel.py:1017-1033. */
+typedef struct cnb_pool_desc {
+  int32_t N, H, W, C;
+  int32_t kh, kw, stride_h, stride_w, pad_h, pad_w;
+  int32_t dtype;
+} cnb_pool_desc;
+
+/* BatchNorm2d problem over an NHWC tensor viewed as [M = N*H*W, C];
+ * replaces nn.BatchNorm2d at reference src/basemodel.py:1008,1061, src/densenet.py:80,117,124,182,
+ * src/mobilenet_v1.py:108,119. */
+#define CNB_BN_RELU 1 /* y = relu(bn(x) [+ residual])  (fuses nn.ReLU, basemodel.py:1012) */
+#define CNB_BN_ADD 2  /* a residual tensor is added before the activation */
+typedef struct cnb_bn_desc {
+  int64_t M; /* N*H*W */
+  int32_t C;
+  int32_t dtype;
+  int32_t flags;
+  float eps;
+  float momentum;
+} cnb_bn_desc;
+
+/* ---- library ------------------------------------------------------------------------- */
+const char* cnb_version(void);
+const char* cnb_last_error(void);
+/* number of kernels this library has launched in the calling process (all threads) */
+uint64_t cnb_launch_count(void);
+
+/* ---- convolution: aten::convolution / convolution_backward (reference src/basemodel.py:974,992)
+ * Dense, grouped (src/resnext.py:93,168; src/shufflenet_v1.py:119-141), dilated
+ * (src/sknet.py:192-201) and depthwise (src/basemodel.py:992) are all served by these three. */
+int cnb_conv2d_out_dims(const cnb_conv_desc* d, int32_t* P, int32_t* Q);
+/* 1 if the tcgen05 tensor-core path would run for this direction, 0 for CUDA cores, <0 error */
+int cnb_conv2d_uses_tc(const cnb_conv_desc* d, int direction);
+size_t cnb_conv2d_workspace_bytes(const cnb_conv_desc* d, int direction);
+/* y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R,S,C/g]) (+ bias[K] fp32) (ReLU) */
+int cnb_conv2d_fwd(const cnb_conv_desc* d, const void* x, const void* w, const float* bias, void* y,
+                   void* workspace, size_t workspace_bytes, void* stream);
+/* dx[N,H,W,C] = conv_transpose(dy[N,P,Q,K], w) */
+int cnb_conv2d_dgrad(const cnb_conv_desc* d, const void* dy, const void* w, void* dx,
+                     void* workspace, size_t workspace_bytes, void* stream);
+/* dw[K,R,S,C/g] (fp32) = x (*) dy ; dbias[K] (fp32, may be NULL) = sum over N,P,Q of dy */
+int cnb_conv2d_wgrad(const cnb_conv_desc* d, const void* x, const void* dy, float* dw, float* dbias,
+                     void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- BatchNorm2d: aten::native_batch_norm / _backward ------------------------------------ */
+size_t cnb_bn_workspace_bytes(const cnb_bn_desc* d);
+/* training forward: batch statistics (biased var for normalisation, unbiased for running_var),
+ * running-stat update, y = [relu]((x-mean)*rstd*gamma + beta [+ residual]).
+ * save_mean / save_rstd: fp32 [C] outputs kept for backward. */
+int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, const float* gamma,
+                     const float* beta, float* running_mean, float* running_var, void* y,
+                     float* save_mean, float* save_rstd, void* workspace, size_t workspace_bytes,
+                     void* stream);
+/* inference forward with running statistics */
+int cnb_bn_fwd_eval(const cnb_bn_desc* d, const void* x, const void* residual, const float* gamma,
+                    const float* beta, const float* running_mean, const float* running_var, void* y,
+                    void* workspace, size_t workspace_bytes, void* stream);
+/* backward of the training forward.  y is the forward output (needed only with CNB_BN_RELU, for
+ * the mask y > 0); d_residual (may be NULL) receives the masked upstream gradient. */
+int cnb_bn_bwd(const cnb_bn_desc* d, const void* x, const void* y, const void* dy,
+               const float* gamma, const float* save_mean, const float* save_rstd, void* dx,
+               void* d_residual, float* dgamma, float* dbeta, void* workspace,
+               size_t workspace_bytes, void* stream);
+
+/* ---- element-wise: aten::relu_/threshold_backward (basemodel.py:1012; resnet.py:154,194),
+ * aten::add_ (resnet.py:151,191) ---------------------------------------------------------- */
+int cnb_relu_fwd(const void* x, void* y, int64_t n, int dtype, void* stream);
+int cnb_relu_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype, void* stream);
+/* y = relu(a + b) */
+int cnb_add_relu_fwd(const void* a, const void* b, void* y, int64_t n, int dtype, void* stream);
+/* dx = dy * (y > 0) (serves both addends) */
+int cnb_add_relu_bwd(const void* y, const void* dy, void* dx, int64_t n, int dtype, void* stream);
+/* y = a + b (gradient accumulation of branching graphs) */
+int cnb_add(const void* a, const void* b, void* y, int64_t n, int dtype, void* stream);
+
+/* ---- pooling: aten::max_pool2d_with_indices / avg_pool2d / adaptive_avg_pool2d ------------ */
+/* idx[N,P,Q,C] int32 = h*W + w of the first maximum in row-major window scan (PyTorch's rule;
+ * padding is never selected; NaN propagates). */
+int cnb_maxpool_fwd(const cnb_pool_desc* d, const void* x, void* y, int32_t* idx, void* stream);
+int cnb_maxpool_bwd(const cnb_pool_desc* d, const void* dy, const int32_t* idx, void* dx,
+                    void* stream);
+/* count_include_pad=True, ceil_mode=False (reference src/shufflenet_v1.py:148, densenet.py:188) */
+int cnb_avgpool_fwd(const cnb_pool_desc* d, const void* x, void* y, void* stream);
+int cnb_avgpool_bwd(const cnb_pool_desc* d, const void* dy, void* dx, void* stream);
+/* global average pool: y[N,C] (fp32) = mean over HW of x[N,HW,C]  (basemodel.py:1035-1042) */
+int cnb_gap_fwd(const void* x, float* y, int32_t N, int32_t HW, int32_t C, int dtype, void* stream);
+int cnb_gap_bwd(const float* dy, void* dx, int32_t N, int32_t HW, int32_t C, int dtype,
+                void* stream);
+
+/* ---- data movement ------------------------------------------------------------------------ */
+/* channel shuffle (reference src/shufflenet_v1.py:173-190): y[:, j*g+i] = x[:, i*(C/g)+j] */
+int cnb_channel_shuffle(const void* x, void* y, int64_t M, int32_t C, int32_t groups, int dtype,
+                        void* stream);
+/* strided channel-slab copy: dst[m, dst_off + c] = src[m, src_off + c], c < Ccopy.  Serves
+ * torch.cat(dim=1) (densenet.py:140, inceptionnet_v1.py:142, squeezenet.py:153,
+ * shufflenet_v1.py:167) forward (dst is the concat buffer) and backward (src is its gradient). */
+int cnb_copy_channels(const void* src, int32_t src_C, int32_t src_off, void* dst, int32_t dst_C,
+                      int32_t dst_off, int64_t M, int32_t Ccopy, int dtype, void* stream);
+/* layout / precision conversion of the network input: src fp32 NCHW -> dst `dtype` NHWC */
+int cnb_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t H, int32_t W,
+                     int dtype, void* stream);
+/* element-wise precision conversion (fp32 master weights -> bf16 operand copy, etc.) */
+int cnb_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n, void* stream);
+
+/* ---- gating --------------------------------------------------------------------------------
+ * SE scale (reference src/se_resnet.py:253): y[n,hw,c] = x[n,hw,c] * s[n,c]   (s fp32) */
+int cnb_se_scale_fwd(const void* x, const float* s, void* y, int32_t N, int32_t HW, int32_t C,
+                     int dtype, void* stream);
+/* dx = dy * s ; ds[n,c] = sum_hw dy * x */
+int cnb_se_scale_bwd(const void* x, const float* s, const void* dy, void* dx, float* ds, int32_t N,
+                     int32_t HW, int32_t C, int dtype, void* stream);
+/* SK fuse (reference src/sknet.py:226-231): g[n,c] (fp32) = mean_hw (u0 + u1) */
+int cnb_sk_fuse_gap_fwd(const void* u0, const void* u1, float* g, int32_t N, int32_t HW, int32_t C,
+                        int dtype, void* stream);
+/* SK select (reference src/sknet.py:238-240): a = softmax over the 2 paths of logits[n,2,C]
+ * (fp32); y = u0*a0 + u1*a1.  attn[n,2,C] (fp32) is kept for backward. */
+int cnb_sk_select_fwd(const void* u0, const void* u1, const float* logits, float* attn, void* y,
+                      int32_t N, int32_t HW, int32_t C, int dtype, void* stream);
+/* du_i = dy*a_i + dg[n,c]/HW ; dlogits = softmax backward of (sum_hw dy*u_i) */
+int cnb_sk_select_bwd(const void* u0, const void* u1, const float* attn, const void* dy,
+                      const float* dg, void* du0, void* du1, float* dlogits, int32_t N, int32_t HW,
+                      int32_t C, int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CONVNETS_B200_H */
