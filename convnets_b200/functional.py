@@ -1,0 +1,630 @@
+"""torch.autograd.Function wrappers over the libconvnets_b200 C ABI.
+
+Each function here is the drop-in for one library op the reference reaches through torch.nn
+(SURVEY.md §2.1).  Tensors are logical NCHW / physical NHWC (torch.channels_last), dtype bf16
+or fp32; parameters, statistics and weight gradients are fp32.  PyTorch only provides device
+memory, streams and the autograd tape; all arithmetic on the feature maps happens in the CUDA
+library.  There is no CPU path: a non-CUDA tensor raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import torch
+
+from . import lib as _L
+
+_CL = torch.channels_last
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return _L.CNB_F32
+    if t.dtype == torch.bfloat16:
+        return _L.CNB_BF16
+    raise TypeError(f"convnets_b200 supports float32 and bfloat16 activations, got {t.dtype}")
+
+
+def _cuda(*ts: Optional[torch.Tensor]) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError(
+                "convnets_b200 ops run only on CUDA tensors (sm_100a); there is no CPU fallback. "
+                "Use the oracle/ package for CPU reference results.")
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _nhwc(t: torch.Tensor) -> torch.Tensor:
+    if t.dim() != 4:
+        raise ValueError(f"expected a 4-D NCHW tensor, got shape {tuple(t.shape)}")
+    return t if t.is_contiguous(memory_format=_CL) else t.contiguous(memory_format=_CL)
+
+
+def _empty_nhwc(n, c, h, w, dtype, device) -> torch.Tensor:
+    return torch.empty((n, c, h, w), dtype=dtype, device=device, memory_format=_CL)
+
+
+_workspaces: dict = {}
+
+
+def _workspace(nbytes: int, device: torch.device) -> torch.Tensor:
+    """Grow-only per-device scratch buffer.  Safe to share between ops because every op that
+    uses it is enqueued on the same (current) stream, in order."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def _pair(v):
+    return (int(v), int(v)) if isinstance(v, int) else (int(v[0]), int(v[1]))
+
+
+# ----------------------------------------------------------------------------- layout / dtype
+def to_nhwc(x: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    """Network-input conversion: fp32 NCHW -> `dtype` NHWC (reference: the H2D'd batch enters
+    the first conv as fp32 NCHW, src/basemodel.py:185-188)."""
+    _cuda(x)
+    if x.dim() != 4:
+        raise ValueError("to_nhwc expects [N, C, H, W]")
+    if x.dtype == dtype and x.is_contiguous(memory_format=_CL):
+        return x
+    if x.dtype != torch.float32 or not x.is_contiguous():
+        x = x.float().contiguous()
+    n, c, h, w = x.shape
+    y = _empty_nhwc(n, c, h, w, dtype, x.device)
+    lib = _L.load()
+    _L.check(lib.cnb_nchw_to_nhwc(_p(x), _p(y), n, c, h, w, _dt(y), _stream()), "cnb_nchw_to_nhwc")
+    return y
+
+
+def cast(src: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    """Element-wise precision conversion preserving strides (dense tensors only)."""
+    _cuda(src)
+    dst = torch.empty_like(src, dtype=dtype)
+    lib = _L.load()
+    _L.check(lib.cnb_cast(_p(src), _dt(src), _p(dst), _dt(dst), src.numel(), _stream()), "cnb_cast")
+    return dst
+
+
+def pack_weight(weight: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    """fp32 master weight [K, C/g, R, S] -> KRSC operand copy in `dtype` (a channels_last tensor
+    of the same logical shape)."""
+    w = weight.detach()
+    if not w.is_contiguous(memory_format=_CL):
+        w = w.contiguous(memory_format=_CL)
+    if w.dtype == dtype:
+        return w
+    return cast(w, dtype)
+
+
+# ----------------------------------------------------------------------------- convolution
+def _conv_desc(x_shape, w_shape, stride, padding, dilation, groups, dtype_code, flags, algo):
+    n, c, h, w = x_shape
+    k, cg, r, s = w_shape
+    if c != cg * groups:
+        raise RuntimeError(
+            f"Given groups={groups}, weight of size {list(w_shape)}, expected input{list(x_shape)} "
+            f"to have {cg * groups} channels, but got {c} channels instead")
+    d = _L.ConvDesc(n, h, w, c, k, r, s, stride[0], stride[1], padding[0], padding[1],
+                    dilation[0], dilation[1], groups, dtype_code, flags, algo)
+    return d
+
+
+class _Conv2dFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, wpack, stride, padding, dilation, groups, algo):
+        _cuda(x, wpack, bias)
+        lib = _L.load()
+        x = _nhwc(x)
+        if x.dtype != wpack.dtype:
+            raise TypeError(f"conv2d: activation dtype {x.dtype} != packed weight dtype {wpack.dtype}")
+        flags = _L.CNB_CONV_BIAS if bias is not None else 0
+        d = _conv_desc(x.shape, wpack.shape, stride, padding, dilation, groups, _dt(x), flags, algo)
+        P, Q = C.c_int32(), C.c_int32()
+        _L.check(lib.cnb_conv2d_out_dims(C.byref(d), C.byref(P), C.byref(Q)), "cnb_conv2d_out_dims")
+        y = _empty_nhwc(x.shape[0], wpack.shape[0], P.value, Q.value, x.dtype, x.device)
+        nws = lib.cnb_conv2d_workspace_bytes(C.byref(d), _L.CNB_FWD)
+        ws = _workspace(nws, x.device)
+        b32 = None if bias is None else bias.detach().float().contiguous()
+        _L.check(lib.cnb_conv2d_fwd(C.byref(d), _p(x), _p(wpack), _p(b32), _p(y), _p(ws), ws.numel(),
+                                    _stream()), "cnb_conv2d_fwd")
+        ctx.save_for_backward(x, wpack)
+        ctx.desc = d
+        ctx.has_bias = bias is not None
+        ctx.wshape = tuple(weight.shape)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _L.load()
+        x, wpack = ctx.saved_tensors
+        d = ctx.desc
+        dy = _nhwc(dy)
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x, memory_format=_CL)
+            nws = lib.cnb_conv2d_workspace_bytes(C.byref(d), _L.CNB_DGRAD)
+            ws = _workspace(nws, x.device)
+            _L.check(lib.cnb_conv2d_dgrad(C.byref(d), _p(dy), _p(wpack), _p(dx), _p(ws), ws.numel(),
+                                          _stream()), "cnb_conv2d_dgrad")
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            dw = torch.empty(ctx.wshape, dtype=torch.float32, device=x.device, memory_format=_CL)
+            if ctx.has_bias:
+                db = torch.empty(ctx.wshape[0], dtype=torch.float32, device=x.device)
+            nws = lib.cnb_conv2d_workspace_bytes(C.byref(d), _L.CNB_WGRAD)
+            ws = _workspace(nws, x.device)
+            _L.check(lib.cnb_conv2d_wgrad(C.byref(d), _p(x), _p(dy), _p(dw), _p(db), _p(ws),
+                                          ws.numel(), _stream()), "cnb_conv2d_wgrad")
+        return dx, dw, db, None, None, None, None, None, None
+
+
+def conv2d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, wpack=None,
+           algo=_L.CNB_ALGO_AUTO):
+    """Drop-in for F.conv2d as reached from nn.Conv2d (reference src/basemodel.py:974,992).
+    `weight` is the fp32 master parameter; `wpack` an optional pre-packed operand copy."""
+    if wpack is None:
+        wpack = pack_weight(weight, x.dtype)
+    return _Conv2dFn.apply(x, weight, bias, wpack, _pair(stride), _pair(padding), _pair(dilation),
+                           int(groups), int(algo))
+
+
+def conv2d_uses_tc(x_shape, w_shape, stride, padding, dilation, groups, dtype, direction) -> bool:
+    """Which path a conv would take: True = tcgen05 implicit GEMM, False = CUDA cores."""
+    code = _L.CNB_BF16 if dtype == torch.bfloat16 else _L.CNB_F32
+    d = _conv_desc(x_shape, w_shape, _pair(stride), _pair(padding), _pair(dilation), groups, code, 0,
+                   _L.CNB_ALGO_AUTO)
+    r = _L.load().cnb_conv2d_uses_tc(C.byref(d), direction)
+    if r < 0:
+        _L.check(r, "cnb_conv2d_uses_tc")
+    return bool(r)
+
+
+# ----------------------------------------------------------------------------- batch norm
+class _BatchNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps,
+                relu):
+        _cuda(x, residual, gamma, beta)
+        lib = _L.load()
+        x = _nhwc(x)
+        n, c, h, w = x.shape
+        flags = (_L.CNB_BN_RELU if relu else 0) | (_L.CNB_BN_ADD if residual is not None else 0)
+        if residual is not None:
+            residual = _nhwc(residual)
+            if residual.shape != x.shape or residual.dtype != x.dtype:
+                raise RuntimeError("batch_norm: residual must match x in shape and dtype")
+        d = _L.BnDesc(n * h * w, c, _dt(x), flags, float(eps), float(momentum))
+        y = torch.empty_like(x, memory_format=_CL)
+        ws = _workspace(lib.cnb_bn_workspace_bytes(C.byref(d)), x.device)
+        g32 = None if gamma is None else gamma.detach()
+        b32 = None if beta is None else beta.detach()
+        if training:
+            if n * h * w <= 1:
+                raise ValueError(
+                    f"Expected more than 1 value per channel when training, got input size {list(x.shape)}")
+            mean = torch.empty(c, dtype=torch.float32, device=x.device)
+            rstd = torch.empty(c, dtype=torch.float32, device=x.device)
+            _L.check(lib.cnb_bn_fwd_train(C.byref(d), _p(x), _p(residual), _p(g32), _p(b32),
+                                          _p(running_mean), _p(running_var), _p(y), _p(mean),
+                                          _p(rstd), _p(ws), ws.numel(), _stream()), "cnb_bn_fwd_train")
+            ctx.save_for_backward(x, y if relu else None, g32, mean, rstd)
+        else:
+            _L.check(lib.cnb_bn_fwd_eval(C.byref(d), _p(x), _p(residual), _p(g32), _p(b32),
+                                         _p(running_mean), _p(running_var), _p(y), _p(ws), ws.numel(),
+                                         _stream()), "cnb_bn_fwd_eval")
+            ctx.save_for_backward()
+        ctx.training = training
+        ctx.desc = d
+        ctx.has_res = residual is not None
+        ctx.affine = gamma is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        if not ctx.training:
+            raise NotImplementedError(
+                "backward through inference-mode BatchNorm is not part of the reference hot path "
+                "(valid_model runs under no_grad, src/basemodel.py:304)")
+        lib = _L.load()
+        x, y, gamma, mean, rstd = ctx.saved_tensors
+        d = ctx.desc
+        dy = _nhwc(dy)
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        dx = torch.empty_like(x, memory_format=_CL)
+        dres = torch.empty_like(x, memory_format=_CL) if (ctx.has_res and ctx.needs_input_grad[1]) else None
+        c = x.shape[1]
+        dgamma = torch.empty(c, dtype=torch.float32, device=x.device) if ctx.affine else None
+        dbeta = torch.empty(c, dtype=torch.float32, device=x.device) if ctx.affine else None
+        ws = _workspace(lib.cnb_bn_workspace_bytes(C.byref(d)), x.device)
+        _L.check(lib.cnb_bn_bwd(C.byref(d), _p(x), _p(y), _p(dy), _p(gamma), _p(mean), _p(rstd),
+                                _p(dx), _p(dres), _p(dgamma), _p(dbeta), _p(ws), ws.numel(),
+                                _stream()), "cnb_bn_bwd")
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None
+
+
+def batch_norm(x, gamma, beta, running_mean, running_var, training, momentum=0.1, eps=1e-5,
+               relu=False, residual=None):
+    """Drop-in for F.batch_norm on NCHW feature maps (+ optional fused residual add / ReLU)."""
+    return _BatchNormFn.apply(x, residual, gamma, beta, running_mean, running_var, bool(training),
+                              float(momentum), float(eps), bool(relu))
+
+
+# ----------------------------------------------------------------------------- element-wise
+class _ReluFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        _cuda(x)
+        lib = _L.load()
+        if not (x.is_contiguous() or (x.dim() == 4 and x.is_contiguous(memory_format=_CL))):
+            x = x.contiguous()
+        y = torch.empty_like(x)
+        _L.check(lib.cnb_relu_fwd(_p(x), _p(y), x.numel(), _dt(x), _stream()), "cnb_relu_fwd")
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _L.load()
+        (y,) = ctx.saved_tensors
+        dy = _like(dy, y)
+        dx = torch.empty_like(y)
+        _L.check(lib.cnb_relu_bwd(_p(y), _p(dy), _p(dx), y.numel(), _dt(y), _stream()), "cnb_relu_bwd")
+        return dx
+
+
+def _like(g: torch.Tensor, ref: torch.Tensor) -> torch.Tensor:
+    """Bring an incoming gradient to the dtype and exact memory layout of `ref`."""
+    if g.dtype != ref.dtype:
+        g = g.to(ref.dtype)
+    if g.shape != ref.shape:
+        raise RuntimeError(f"gradient shape {tuple(g.shape)} != {tuple(ref.shape)}")
+    if g.stride() != ref.stride():
+        out = torch.empty_like(ref)
+        out.copy_(g)
+        return out
+    return g
+
+
+def relu(x):
+    """Drop-in for nn.ReLU / F.relu (reference src/basemodel.py:1012; src/resnet.py:154,194)."""
+    return _ReluFn.apply(x)
+
+
+class _AddReluFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, a, b):
+        _cuda(a, b)
+        lib = _L.load()
+        a = _nhwc(a)
+        b = _like(b, a) if b.shape == a.shape else b
+        if a.shape != b.shape or a.dtype != b.dtype:
+            raise RuntimeError("add_relu: operands must match in shape and dtype")
+        y = torch.empty_like(a)
+        _L.check(lib.cnb_add_relu_fwd(_p(a), _p(b), _p(y), a.numel(), _dt(a), _stream()),
+                 "cnb_add_relu_fwd")
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _L.load()
+        (y,) = ctx.saved_tensors
+        dy = _like(dy, y)
+        dx = torch.empty_like(y)
+        _L.check(lib.cnb_add_relu_bwd(_p(y), _p(dy), _p(dx), y.numel(), _dt(y), _stream()),
+                 "cnb_add_relu_bwd")
+        return dx, dx
+
+
+def add_relu(a, b):
+    """relu(a + b): the `output += identity; F.relu(output)` tail of every residual block
+    (reference src/resnet.py:151-154,191-194 and the resnext/se/sk equivalents)."""
+    return _AddReluFn.apply(a, b)
+
+
+# ----------------------------------------------------------------------------- pooling
+def _pool_desc(x, kernel_size, stride, padding):
+    kh, kw = _pair(kernel_size)
+    sh, sw = _pair(stride if stride is not None else kernel_size)
+    ph, pw = _pair(padding)
+    n, c, h, w = x.shape
+    if ph * 2 > kh or pw * 2 > kw:
+        raise RuntimeError("pad should be at most half of effective kernel size")
+    P = (h + 2 * ph - kh) // sh + 1
+    Q = (w + 2 * pw - kw) // sw + 1
+    if P <= 0 or Q <= 0:
+        raise RuntimeError(f"Given input size: ({c}x{h}x{w}). Calculated output size: ({c}x{P}x{Q}). "
+                           "Output size is too small")
+    return _L.PoolDesc(n, h, w, c, kh, kw, sh, sw, ph, pw, _dt(x)), P, Q
+
+
+class _MaxPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, kernel_size, stride, padding, return_indices):
+        _cuda(x)
+        lib = _L.load()
+        x = _nhwc(x)
+        d, P, Q = _pool_desc(x, kernel_size, stride, padding)
+        n, c = x.shape[0], x.shape[1]
+        y = _empty_nhwc(n, c, P, Q, x.dtype, x.device)
+        idx = torch.empty((n, c, P, Q), dtype=torch.int32, device=x.device, memory_format=_CL)
+        _L.check(lib.cnb_maxpool_fwd(C.byref(d), _p(x), _p(y), _p(idx), _stream()), "cnb_maxpool_fwd")
+        ctx.save_for_backward(idx)
+        ctx.desc = d
+        ctx.xshape = tuple(x.shape)
+        ctx.mark_non_differentiable(idx)
+        return y, idx
+
+    @staticmethod
+    def backward(ctx, dy, _didx):
+        lib = _L.load()
+        (idx,) = ctx.saved_tensors
+        dy = _nhwc(dy)
+        n, c, h, w = ctx.xshape
+        dx = _empty_nhwc(n, c, h, w, dy.dtype, dy.device)
+        _L.check(lib.cnb_maxpool_bwd(C.byref(ctx.desc), _p(dy), _p(idx), _p(dx), _stream()),
+                 "cnb_maxpool_bwd")
+        return dx, None, None, None, None
+
+
+def max_pool2d(x, kernel_size, stride=None, padding=0, return_indices=False):
+    """Drop-in for F.max_pool2d (reference src/basemodel.py:1017-1024).  Indices are int32
+    h*W+w with PyTorch's first-maximum rule."""
+    y, idx = _MaxPoolFn.apply(x, kernel_size, stride, padding, True)
+    return (y, idx) if return_indices else y
+
+
+class _AvgPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, kernel_size, stride, padding):
+        _cuda(x)
+        lib = _L.load()
+        x = _nhwc(x)
+        d, P, Q = _pool_desc(x, kernel_size, stride, padding)
+        y = _empty_nhwc(x.shape[0], x.shape[1], P, Q, x.dtype, x.device)
+        _L.check(lib.cnb_avgpool_fwd(C.byref(d), _p(x), _p(y), _stream()), "cnb_avgpool_fwd")
+        ctx.desc = d
+        ctx.xshape = tuple(x.shape)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _L.load()
+        dy = _nhwc(dy)
+        n, c, h, w = ctx.xshape
+        dx = _empty_nhwc(n, c, h, w, dy.dtype, dy.device)
+        _L.check(lib.cnb_avgpool_bwd(C.byref(ctx.desc), _p(dy), _p(dx), _stream()), "cnb_avgpool_bwd")
+        return dx, None, None, None
+
+
+def avg_pool2d(x, kernel_size, stride=None, padding=0):
+    """Drop-in for F.avg_pool2d with count_include_pad=True, ceil_mode=False
+    (reference src/basemodel.py:1026-1033)."""
+    return _AvgPoolFn.apply(x, kernel_size, stride, padding)
+
+
+class _GapFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        _cuda(x)
+        lib = _L.load()
+        x = _nhwc(x)
+        n, c, h, w = x.shape
+        y = torch.empty((n, c, 1, 1), dtype=torch.float32, device=x.device)
+        _L.check(lib.cnb_gap_fwd(_p(x), _p(y), n, h * w, c, _dt(x), _stream()), "cnb_gap_fwd")
+        ctx.xshape = tuple(x.shape)
+        ctx.xdtype = x.dtype
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _L.load()
+        n, c, h, w = ctx.xshape
+        dy = dy.float().contiguous()
+        dx = _empty_nhwc(n, c, h, w, ctx.xdtype, dy.device)
+        _L.check(lib.cnb_gap_bwd(_p(dy), _p(dx), n, h * w, c, _dt(dx), _stream()), "cnb_gap_bwd")
+        return dx
+
+
+def global_avg_pool2d(x):
+    """Drop-in for nn.AdaptiveAvgPool2d(1) (reference src/basemodel.py:1035-1042); the pooled
+    vector is produced in fp32 (the classifier / gate MLPs consume it in fp32)."""
+    return _GapFn.apply(x)
+
+
+# ----------------------------------------------------------------------------- data movement
+class _ShuffleFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, groups):
+        _cuda(x)
+        lib = _L.load()
+        x = _nhwc(x)
+        n, c, h, w = x.shape
+        if c % groups != 0:
+            raise RuntimeError(f"channel_shuffle: {c} channels not divisible by {groups} groups")
+        y = torch.empty_like(x, memory_format=_CL)
+        _L.check(lib.cnb_channel_shuffle(_p(x), _p(y), n * h * w, c, groups, _dt(x), _stream()),
+                 "cnb_channel_shuffle")
+        ctx.groups = groups
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _L.load()
+        dy = _nhwc(dy)
+        n, c, h, w = dy.shape
+        dx = torch.empty_like(dy, memory_format=_CL)
+        # inverse permutation of a (g, C/g) transpose is the (C/g, g) transpose
+        _L.check(lib.cnb_channel_shuffle(_p(dy), _p(dx), n * h * w, c, c // ctx.groups, _dt(dy),
+                                         _stream()), "cnb_channel_shuffle(bwd)")
+        return dx, None
+
+
+def channel_shuffle(x, groups: int):
+    """Drop-in for ShuffleUnit.channel_shuffle (reference src/shufflenet_v1.py:173-190)."""
+    return _ShuffleFn.apply(x, int(groups))
+
+
+class _CatFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, *xs):
+        _cuda(*xs)
+        lib = _L.load()
+        xs = [_nhwc(t) for t in xs]
+        n, _, h, w = xs[0].shape
+        for t in xs:
+            if t.shape[0] != n or t.shape[2] != h or t.shape[3] != w or t.dtype != xs[0].dtype:
+                raise RuntimeError("cat: tensors must match except in the channel dimension")
+        ctot = sum(t.shape[1] for t in xs)
+        y = _empty_nhwc(n, ctot, h, w, xs[0].dtype, xs[0].device)
+        off = 0
+        for t in xs:
+            c = t.shape[1]
+            _L.check(lib.cnb_copy_channels(_p(t), c, 0, _p(y), ctot, off, n * h * w, c, _dt(t),
+                                           _stream()), "cnb_copy_channels")
+            off += c
+        ctx.sizes = [t.shape[1] for t in xs]
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _L.load()
+        dy = _nhwc(dy)
+        n, ctot, h, w = dy.shape
+        outs = []
+        off = 0
+        for i, c in enumerate(ctx.sizes):
+            if ctx.needs_input_grad[i]:
+                g = _empty_nhwc(n, c, h, w, dy.dtype, dy.device)
+                _L.check(lib.cnb_copy_channels(_p(dy), ctot, off, _p(g), c, 0, n * h * w, c, _dt(dy),
+                                               _stream()), "cnb_copy_channels(bwd)")
+                outs.append(g)
+            else:
+                outs.append(None)
+            off += c
+        return tuple(outs)
+
+
+def cat_channels(xs: Sequence[torch.Tensor]):
+    """Drop-in for torch.cat(xs, dim=1) on feature maps (reference src/densenet.py:140,
+    src/inceptionnet_v1.py:142, src/squeezenet.py:153, src/shufflenet_v1.py:167)."""
+    return _CatFn.apply(*xs)
+
+
+# ----------------------------------------------------------------------------- gating
+class _SeScaleFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, s):
+        _cuda(x, s)
+        lib = _L.load()
+        x = _nhwc(x)
+        n, c, h, w = x.shape
+        s2 = s.reshape(n, c).float().contiguous()
+        y = torch.empty_like(x, memory_format=_CL)
+        _L.check(lib.cnb_se_scale_fwd(_p(x), _p(s2), _p(y), n, h * w, c, _dt(x), _stream()),
+                 "cnb_se_scale_fwd")
+        ctx.save_for_backward(x, s2)
+        ctx.sshape = tuple(s.shape)
+        ctx.sdtype = s.dtype
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _L.load()
+        x, s2 = ctx.saved_tensors
+        n, c, h, w = x.shape
+        dy = _nhwc(dy)
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        dx = torch.empty_like(x, memory_format=_CL)
+        ds = torch.empty((n, c), dtype=torch.float32, device=x.device)
+        _L.check(lib.cnb_se_scale_bwd(_p(x), _p(s2), _p(dy), _p(dx), _p(ds), n, h * w, c, _dt(x),
+                                      _stream()), "cnb_se_scale_bwd")
+        return dx, ds.reshape(ctx.sshape).to(ctx.sdtype)
+
+
+def se_scale(x, s):
+    """x * s.expand_as(x) with s of shape [N, C, 1, 1] (reference src/se_resnet.py:253)."""
+    return _SeScaleFn.apply(x, s)
+
+
+class _SkFuseGapFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, u0, u1):
+        _cuda(u0, u1)
+        lib = _L.load()
+        u0, u1 = _nhwc(u0), _nhwc(u1)
+        n, c, h, w = u0.shape
+        g = torch.empty((n, c, 1, 1), dtype=torch.float32, device=u0.device)
+        _L.check(lib.cnb_sk_fuse_gap_fwd(_p(u0), _p(u1), _p(g), n, h * w, c, _dt(u0), _stream()),
+                 "cnb_sk_fuse_gap_fwd")
+        ctx.xshape = tuple(u0.shape)
+        ctx.xdtype = u0.dtype
+        return g
+
+    @staticmethod
+    def backward(ctx, dg):
+        lib = _L.load()
+        n, c, h, w = ctx.xshape
+        dg = dg.float().contiguous()
+        du = _empty_nhwc(n, c, h, w, ctx.xdtype, dg.device)
+        _L.check(lib.cnb_gap_bwd(_p(dg), _p(du), n, h * w, c, _dt(du), _stream()), "cnb_gap_bwd")
+        return du, du
+
+
+def sk_fuse_gap(u0, u1):
+    """global_avgpool(u0 + u1) (reference src/sknet.py:226-231), fp32 [N, C, 1, 1]."""
+    return _SkFuseGapFn.apply(u0, u1)
+
+
+class _SkSelectFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, u0, u1, logits):
+        _cuda(u0, u1, logits)
+        lib = _L.load()
+        u0, u1 = _nhwc(u0), _nhwc(u1)
+        n, c, h, w = u0.shape
+        lg = logits.reshape(n, 2, c).float().contiguous()
+        attn = torch.empty_like(lg)
+        y = torch.empty_like(u0, memory_format=_CL)
+        _L.check(lib.cnb_sk_select_fwd(_p(u0), _p(u1), _p(lg), _p(attn), _p(y), n, h * w, c, _dt(u0),
+                                       _stream()), "cnb_sk_select_fwd")
+        ctx.save_for_backward(u0, u1, attn)
+        ctx.lshape = tuple(logits.shape)
+        ctx.ldtype = logits.dtype
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _L.load()
+        u0, u1, attn = ctx.saved_tensors
+        n, c, h, w = u0.shape
+        dy = _nhwc(dy)
+        if dy.dtype != u0.dtype:
+            dy = dy.to(u0.dtype)
+        du0 = torch.empty_like(u0, memory_format=_CL)
+        du1 = torch.empty_like(u0, memory_format=_CL)
+        dl = torch.empty((n, 2, c), dtype=torch.float32, device=u0.device)
+        _L.check(lib.cnb_sk_select_bwd(_p(u0), _p(u1), _p(attn), _p(dy), None, _p(du0), _p(du1),
+                                       _p(dl), n, h * w, c, _dt(u0), _stream()), "cnb_sk_select_bwd")
+        return du0, du1, dl.reshape(ctx.lshape).to(ctx.ldtype)
+
+
+def sk_select(u0, u1, logits):
+    """sum_i u_i * softmax_i(logits) over the two SK paths (reference src/sknet.py:233-240).
+    `logits` is [N, 2*C, 1, 1] (path-major, as produced by torch.cat of the attention convs)."""
+    return _SkSelectFn.apply(u0, u1, logits)

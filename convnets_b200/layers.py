@@ -1,0 +1,88 @@
+"""Drop-in nn.Module layers backed by libconvnets_b200.
+
+Each class subclasses the torch.nn layer the reference constructs in its factories
+(reference src/basemodel.py:966-1067), so `isinstance` checks in `init_params`
+(src/basemodel.py:92-104), attribute reads in `save_conv_outshape` (:734-763), parameter names
+and state_dict keys are all unchanged; only `forward` differs — it calls the CUDA library.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from . import functional as F_
+from . import lib as _L
+
+
+class Conv2d(nn.Conv2d):
+    """nn.Conv2d whose forward / backward run in libconvnets_b200 (tcgen05 implicit GEMM for
+    dense bf16 layers, CUDA cores for fp32 / grouped / depthwise)."""
+
+    algo = _L.CNB_ALGO_AUTO
+
+    def _packed(self, dtype: torch.dtype) -> torch.Tensor:
+        w = self.weight
+        key = (w._version, w.data_ptr(), dtype)
+        cache = self.__dict__.get("_cnb_pack")
+        if cache is None or cache[0] != key:
+            cache = (key, F_.pack_weight(w, dtype))
+            self.__dict__["_cnb_pack"] = cache
+        return cache[1]
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self.padding_mode != "zeros" or isinstance(self.padding, str):
+            raise NotImplementedError("convnets_b200.Conv2d supports integer zero padding only")
+        return F_.conv2d(x, self.weight, self.bias, self.stride, self.padding, self.dilation,
+                         self.groups, wpack=self._packed(x.dtype), algo=self.algo)
+
+
+class BatchNorm2d(nn.BatchNorm2d):
+    """nn.BatchNorm2d (per-replica batch statistics, as in the reference) with an optional fused
+    ReLU: `fuse_relu` is set by convert() when the next module is nn.ReLU."""
+
+    fuse_relu = False
+
+    def forward(self, x: torch.Tensor, residual: torch.Tensor | None = None) -> torch.Tensor:
+        self._check_input_dim(x)
+        training = self.training or (self.running_mean is None and self.running_var is None)
+        momentum = 0.0 if self.momentum is None else self.momentum
+        if self.training and self.track_running_stats and self.num_batches_tracked is not None:
+            self.num_batches_tracked.add_(1)
+            if self.momentum is None:
+                momentum = 1.0 / float(self.num_batches_tracked)
+        rm = self.running_mean if (not training or self.track_running_stats) else None
+        rv = self.running_var if (not training or self.track_running_stats) else None
+        return F_.batch_norm(x, self.weight, self.bias, rm, rv, training, momentum, self.eps,
+                             relu=self.fuse_relu, residual=residual)
+
+
+class ReLU(nn.ReLU):
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return F_.relu(x)
+
+
+class MaxPool2d(nn.MaxPool2d):
+    def forward(self, x: torch.Tensor):
+        if self.dilation not in (1, (1, 1)) or self.ceil_mode:
+            raise NotImplementedError("convnets_b200.MaxPool2d: dilation=1, ceil_mode=False only")
+        return F_.max_pool2d(x, self.kernel_size, self.stride, self.padding, self.return_indices)
+
+
+class AvgPool2d(nn.AvgPool2d):
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self.ceil_mode or not self.count_include_pad or self.divisor_override is not None:
+            raise NotImplementedError(
+                "convnets_b200.AvgPool2d: count_include_pad=True, ceil_mode=False only (the "
+                "reference's configuration, src/basemodel.py:1026-1033)")
+        return F_.avg_pool2d(x, self.kernel_size, self.stride, self.padding)
+
+
+class AdaptiveAvgPool2d(nn.AdaptiveAvgPool2d):
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self.output_size not in (1, (1, 1)):
+            raise NotImplementedError("convnets_b200.AdaptiveAvgPool2d: output_size=1 only")
+        return F_.global_avg_pool2d(x)
+
+
+class Identity(nn.Identity):
+    """Placeholder left where convert() fused an nn.ReLU into the preceding BatchNorm2d."""

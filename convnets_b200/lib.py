@@ -1,0 +1,120 @@
+"""ctypes binding of libconvnets_b200.so (the C ABI declared in include/convnets_b200.h).
+
+This is the only place the shared library is loaded.  There is no fallback: if the library is
+missing or fails to load, importing a layer that needs it raises immediately.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libconvnets_b200.so")
+
+CNB_F32, CNB_BF16 = 0, 1
+CNB_CONV_BIAS, CNB_CONV_RELU = 1, 2
+CNB_ALGO_AUTO, CNB_ALGO_SIMT, CNB_ALGO_TC = 0, 1, 2
+CNB_FWD, CNB_DGRAD, CNB_WGRAD = 0, 1, 2
+CNB_BN_RELU, CNB_BN_ADD = 1, 2
+
+
+class ConvDesc(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in (
+        "N", "H", "W", "C", "K", "R", "S", "stride_h", "stride_w", "pad_h", "pad_w",
+        "dil_h", "dil_w", "groups", "dtype", "flags", "algo")]
+
+
+class PoolDesc(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in (
+        "N", "H", "W", "C", "kh", "kw", "stride_h", "stride_w", "pad_h", "pad_w", "dtype")]
+
+
+class BnDesc(C.Structure):
+    _fields_ = [("M", C.c_int64), ("C", C.c_int32), ("dtype", C.c_int32), ("flags", C.c_int32),
+                ("eps", C.c_float), ("momentum", C.c_float)]
+
+
+_P = C.c_void_p
+_I = C.c_int
+_I32 = C.c_int32
+_I64 = C.c_int64
+_SZ = C.c_size_t
+
+# name -> (restype, argtypes).  Must list every symbol of include/convnets_b200.h
+# (tests/test_abi.py parses the header and checks this table and the .so against it).
+SIGNATURES = {
+    "cnb_version": (C.c_char_p, []),
+    "cnb_last_error": (C.c_char_p, []),
+    "cnb_launch_count": (C.c_uint64, []),
+    "cnb_conv2d_out_dims": (_I, [C.POINTER(ConvDesc), C.POINTER(_I32), C.POINTER(_I32)]),
+    "cnb_conv2d_uses_tc": (_I, [C.POINTER(ConvDesc), _I]),
+    "cnb_conv2d_workspace_bytes": (_SZ, [C.POINTER(ConvDesc), _I]),
+    "cnb_conv2d_fwd": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _SZ, _P]),
+    "cnb_conv2d_dgrad": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _SZ, _P]),
+    "cnb_conv2d_wgrad": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _SZ, _P]),
+    "cnb_bn_workspace_bytes": (_SZ, [C.POINTER(BnDesc)]),
+    "cnb_bn_fwd_train": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
+    "cnb_bn_fwd_eval": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
+    "cnb_bn_bwd": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
+    "cnb_relu_fwd": (_I, [_P, _P, _I64, _I, _P]),
+    "cnb_relu_bwd": (_I, [_P, _P, _P, _I64, _I, _P]),
+    "cnb_add_relu_fwd": (_I, [_P, _P, _P, _I64, _I, _P]),
+    "cnb_add_relu_bwd": (_I, [_P, _P, _P, _I64, _I, _P]),
+    "cnb_add": (_I, [_P, _P, _P, _I64, _I, _P]),
+    "cnb_maxpool_fwd": (_I, [C.POINTER(PoolDesc), _P, _P, _P, _P]),
+    "cnb_maxpool_bwd": (_I, [C.POINTER(PoolDesc), _P, _P, _P, _P]),
+    "cnb_avgpool_fwd": (_I, [C.POINTER(PoolDesc), _P, _P, _P]),
+    "cnb_avgpool_bwd": (_I, [C.POINTER(PoolDesc), _P, _P, _P]),
+    "cnb_gap_fwd": (_I, [_P, _P, _I32, _I32, _I32, _I, _P]),
+    "cnb_gap_bwd": (_I, [_P, _P, _I32, _I32, _I32, _I, _P]),
+    "cnb_channel_shuffle": (_I, [_P, _P, _I64, _I32, _I32, _I, _P]),
+    "cnb_copy_channels": (_I, [_P, _I32, _I32, _P, _I32, _I32, _I64, _I32, _I, _P]),
+    "cnb_nchw_to_nhwc": (_I, [_P, _P, _I32, _I32, _I32, _I32, _I, _P]),
+    "cnb_cast": (_I, [_P, _I, _P, _I, _I64, _P]),
+    "cnb_se_scale_fwd": (_I, [_P, _P, _P, _I32, _I32, _I32, _I, _P]),
+    "cnb_se_scale_bwd": (_I, [_P, _P, _P, _P, _P, _I32, _I32, _I32, _I, _P]),
+    "cnb_sk_fuse_gap_fwd": (_I, [_P, _P, _P, _I32, _I32, _I32, _I, _P]),
+    "cnb_sk_select_fwd": (_I, [_P, _P, _P, _P, _P, _I32, _I32, _I32, _I, _P]),
+    "cnb_sk_select_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I32, _I32, _I32, _I, _P]),
+}
+
+_lib = None
+
+
+class CnbError(RuntimeError):
+    """A libconvnets_b200 call returned a non-zero status."""
+
+
+def load() -> C.CDLL:
+    """Load the shared library (once) and attach the prototypes.  Raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise CnbError(
+            f"{LIB_PATH} not found: build it with `python -m convnets_b200.build` "
+            "(or __graft_entry__.build()).  There is no CPU / eager fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the .so lacks a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    return load().cnb_last_error().decode("utf-8", "replace")
+
+
+def check(status: int, what: str) -> None:
+    if status != 0:
+        raise CnbError(f"{what} failed (status {status}): {last_error()}")
+
+
+def version() -> str:
+    return load().cnb_version().decode()
+
+
+def launch_count() -> int:
+    return int(load().cnb_launch_count())

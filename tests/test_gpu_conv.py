@@ -1,0 +1,94 @@
+"""GPU parity of the convolution entry points (cnb_conv2d_fwd / dgrad / wgrad) against the
+oracle, per layer signature.  Every case runs in its own subprocess (tests/tc_probe.py) with a
+timeout, so a faulting tensor-core kernel fails one case instead of wedging the session.
+
+Tolerances (BASELINE.json north_star): rel-L2 <= 1e-2 in bf16 mode, <= 1e-4 in fp32-IO mode.
+Oracle inputs are pre-rounded to the storage dtype, so only accumulation/output rounding differ.
+"""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PROBE = os.path.join(ROOT, "tests", "tc_probe.py")
+
+
+def c(N, C, H, W, K, R, S=None, **kw):
+    d = dict(N=N, C=C, H=H, W=W, K=K, R=R, S=R if S is None else S)
+    d.update(kw)
+    return d
+
+
+# tensor-core (tcgen05) cases: ResNet-50 / DenseNet / Inception style signatures at small batch
+TC_CASES = [
+    c(2, 64, 16, 16, 64, 1),                          # pure GEMM, one n-tile of 64
+    c(3, 256, 7, 7, 128, 1),                          # M = 147 (ragged last m-tile), K-loop of 4
+    c(2, 128, 14, 14, 512, 1),                        # BLOCK_N = 256, two n-tiles
+    c(2, 64, 14, 14, 64, 3, pad=1),                   # 3x3 im2col, padding by zero-fill
+    c(2, 128, 15, 15, 128, 3, pad=1, stride=2),       # strided 3x3 (parity-class dgrad)
+    c(2, 256, 14, 14, 512, 1, stride=2),              # strided 1x1 projection
+    c(2, 32, 12, 12, 64, 3, pad=2, dil=2),            # dilated, C < 64 (channel zero-fill)
+    c(2, 16, 9, 9, 32, 5, pad=2),                     # 5x5 (Inception), C = 16
+    c(2, 8, 20, 20, 64, 7, pad=3, stride=2),          # 7x7 stride 2 stem-like, C = 8
+    c(1, 96, 10, 10, 208, 3, pad=1),                  # C, K not multiples of 64
+    c(2, 64, 8, 8, 64, 3, pad=1, bias=True),          # bias epilogue + bias grad
+    c(4, 512, 7, 7, 512, 3, pad=1),                   # deep K loop (72 k-blocks), NT=256 wgrad
+    c(8, 64, 56, 56, 64, 3, pad=1),                   # many m-tiles, split-K wgrad
+    c(8, 256, 28, 28, 128, 1),                        # wgrad NT=256 x 2 cout tiles? (K=128: 1 tile)
+]
+
+# CUDA-core cases: fp32-IO mode, grouped, tiny channel counts, stems
+SIMT_CASES = [
+    c(2, 3, 17, 17, 24, 3, pad=1, stride=2, dtype="f32"),              # RGB stem
+    c(2, 3, 32, 32, 64, 7, pad=3, stride=2, dtype="bf16"),             # bf16 stem, C = 3
+    c(2, 64, 9, 9, 64, 3, pad=1, dtype="f32"),                         # fp32-IO dense
+    c(2, 128, 10, 10, 128, 3, pad=1, groups=32, dtype="bf16"),         # ResNeXt 4 ch/group
+    c(2, 128, 10, 10, 128, 3, pad=2, dil=2, groups=32, stride=2, dtype="f32"),  # SK path 2
+    c(2, 240, 7, 7, 60, 1, groups=3, dtype="bf16"),                    # ShuffleNet g3 compress
+    c(2, 60, 7, 7, 240, 1, groups=3, dtype="f32", bias=True),          # ShuffleNet g3 expand
+    c(3, 32, 1, 1, 64, 1, dtype="f32", bias=True),                     # SK attention conv [B,d,1,1]
+    c(2, 64, 14, 14, 64, 3, pad=1, dtype="bf16", algo="simt"),         # forced CUDA-core bf16
+    c(2, 32, 13, 13, 32, 3, pad=1, groups=32, dtype="bf16"),           # depthwise s1
+    c(2, 64, 14, 14, 64, 3, pad=1, stride=2, groups=64, dtype="f32"),  # depthwise s2
+    c(2, 60, 7, 7, 60, 3, pad=1, stride=2, groups=60, dtype="bf16"),   # depthwise, C % 8 != 0
+]
+
+
+def run_probe(case, timeout=180):
+    env = dict(os.environ)
+    p = subprocess.run([sys.executable, PROBE, json.dumps(case)], capture_output=True, text=True,
+                       timeout=timeout, env=env)
+    line = [l for l in p.stdout.splitlines() if l.startswith("PROBE_RESULT ")]
+    if p.returncode != 0 or not line:
+        pytest.fail(f"probe failed rc={p.returncode}\nstdout:\n{p.stdout[-2000:]}\nstderr:\n{p.stderr[-3000:]}")
+    return json.loads(line[-1][len("PROBE_RESULT "):])
+
+
+def check(res, tol):
+    msgs = []
+    for k in ("fwd", "dgrad", "wgrad", "bgrad"):
+        if k in res and not (res[k]["rel_l2"] <= tol):
+            msgs.append(f"{k}: {json.dumps(res[k])}")
+    assert not msgs, "parity failure for %s (uses_tc=%s):\n%s" % (
+        json.dumps(res["case"]), res["uses_tc"], "\n".join(msgs))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", TC_CASES, ids=lambda d: "N{N}C{C}H{H}K{K}R{R}".format(**d) + "".join(
+    f"{k}{v}" for k, v in d.items() if k in ("stride", "pad", "dil", "bias")))
+def test_conv_tensor_core(case):
+    case = dict(case, dtype="bf16", algo="tc")
+    res = run_probe(case)
+    assert res["uses_tc"] == [True, True, True]
+    check(res, 1e-2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", SIMT_CASES, ids=lambda d: "N{N}C{C}H{H}K{K}R{R}".format(**d) + "".join(
+    f"{k}{v}" for k, v in d.items() if k in ("stride", "pad", "dil", "groups", "dtype", "bias", "algo")))
+def test_conv_cuda_core(case):
+    res = run_probe(case)
+    check(res, 1e-4 if case["dtype"] == "f32" else 1e-2)
