@@ -46,8 +46,8 @@ def test_batch_norm_train(dtype, shape, relu, res):
     gamma, beta = torch.rand(c) + 0.5, torch.randn(c)
     rm, rv = torch.randn(c), torch.rand(c) + 0.5
     dy = rnd(*shape, dtype=dtype)
-    y_ref, rm_ref, rv_ref, mean_ref, rstd_ref = O.batch_norm_train(x, gamma, beta, rm, rv, 0.1, 1e-5, relu, r)
-    dx_ref, dg_ref, db_ref, dr_ref = O.batch_norm_train_grads(x, gamma, beta, dy, 1e-5, relu, r)
+    y_ref, rm_ref, rv_ref, mean_ref, rstd_ref = O.batch_norm_train(x, gamma, beta, rm, rv, 0.1, 1e-5, relu, r, storage=dtype)
+    dx_ref, dg_ref, db_ref, dr_ref = O.batch_norm_train_grads(x, gamma, beta, dy, 1e-5, relu, r, storage=dtype)
 
     xd, rd = dev(x, True), (dev(r, True) if res else None)
     gd, bd = dev(gamma, True), dev(beta, True)
