@@ -1,0 +1,406 @@
+#!/usr/bin/env python
+"""bench.py — training throughput of the conv hot path (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # this framework on N B200s
+    python bench.py --impl reference --gpus N --steps K --warmup W   # reference CPU path (oracle port)
+
+One "step" = one iteration of MultiClassBaseModel.train_model (reference src/basemodel.py:245-296):
+zero_grad -> forward -> CrossEntropyLoss(sum) -> backward -> [gradient all-reduce] -> Adam step, on
+one synthetic batch (B images per GPU).  Default workload: BASELINE.json configs[1] — ResNet-50,
+224x224, batch 256 per GPU, bf16 feature maps with fp32 accumulate and fp32 master weights.
+
+`value`  : images/sec, inputs already resident in HBM when the timed region starts.
+`e2e`    : the same metric through the public API (model.train_model over a loader of pinned HOST
+           batches): every step includes the H2D copy of its batch and the D2H read of loss/score.
+`roofline`: the dominant kernel family of the step, timed live with CUDA events (one extra traced
+           step after the timed region) against MEASURED_PEAKS.json.
+`cpu_baseline`: the oracle port of the reference path on the host cores, bounded sample.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "train images/sec (ResNet-50 224x224)"
+UNIT = "images/sec"
+
+# model name -> (zoo class name, kind, default per-GPU batch)
+WORKLOADS = {
+    "resnet50": ("ResNet", "50", 256),
+}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--model", default="resnet50", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0, help="images per GPU (0 = workload default)")
+    ap.add_argument("--hw", type=int, default=224)
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "f32"])
+    ap.add_argument("--cpu-batch", type=int, default=16, help="batch of the CPU baseline sample")
+    ap.add_argument("--cpu-steps", type=int, default=4)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--trace-out", default="", help="write the per-call device-time table here")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return {"hbm": float(d["hbm_gbs"]), "tensor_burst": float(d["bf16_tflops"]),
+                "tensor": float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), "src": "measured"}
+    # fallback stated in /opt/skills/guides/B200_PROFILING.md
+    return {"hbm": 6650.0, "tensor_burst": 1590.0, "tensor": 1400.0, "src": "fallback"}
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the oracle port of the reference path on the host cores
+def cpu_reference(args, steps, warmup, batch):
+    from oracle import zoo as Z
+    from convnets_b200 import zoo as M
+    cls, kind, _ = WORKLOADS[args.model]
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    torch.manual_seed(21)
+    s = M.Settings(kind=kind, input_size=(3, args.hw, args.hw), num_classes=10, dropout_rate=0.0)
+    s.device.set_device("cpu")
+    sd = {k: v.detach().clone() for k, v in getattr(M, cls)(s).state_dict().items()}
+    g = torch.Generator().manual_seed(21)
+    x = torch.randn(batch, 3, args.hw, args.hw, generator=g)
+    y = torch.randint(0, 10, (batch,), generator=g)
+    state = {}
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        sd, _, loss, _ = Z.train_step(cls, sd, x, y, kind, state, lr=s.learning_rate,
+                                      weight_decay=s.weight_decay)
+        float(loss)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    med = statistics.median(times)
+    return {"value": batch / med, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{cls}-{kind} fp32 {args.hw}x{args.hw}, batch {batch}, median of {steps} "
+                      f"train steps after {warmup} warm-up (oracle.zoo.train_step, torch "
+                      f"{torch.__version__} CPU ops, {threads} threads)",
+            "ms_per_step": med * 1e3}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps = max(1, min(args.steps, 8))
+    warmup = max(1, min(args.warmup, 2))
+    cb = cpu_reference(args, steps, warmup, args.cpu_batch)
+    cls, kind, _ = WORKLOADS[args.model]
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT,
+        "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "ms_per_step": cb["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": f"{cls}-{kind} train step, {args.hw}x{args.hw}x3, 10 classes, "
+                               f"CPU sample batch {args.cpu_batch}"},
+        "cpu_baseline": {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "200"], stdout=self.f,
+                stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.f.read().splitlines():
+            c = [t.strip() for t in ln.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2])); pw.append(float(c[3]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        os.unlink(self.f.name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "power_w_max": max(pw), "samples": len(sm)}
+
+
+class HostLoader:
+    """A minimal DataLoader stand-in for train_model: pinned host batches + `.dataset` length."""
+
+    def __init__(self, batches):
+        self.batches = batches
+        self.dataset = range(sum(int(b[1].numel()) for b in batches))
+
+    def __iter__(self):
+        return iter(self.batches)
+
+    def __len__(self):
+        return len(self.batches)
+
+
+def conv_flops(d):
+    P = (d["H"] + 2 * d["pad_h"] - d["dil_h"] * (d["R"] - 1) - 1) // d["stride_h"] + 1
+    Q = (d["W"] + 2 * d["pad_w"] - d["dil_w"] * (d["S"] - 1) - 1) // d["stride_w"] + 1
+    return 2.0 * d["N"] * P * Q * d["K"] * (d["C"] // d["groups"]) * d["R"] * d["S"], P, Q
+
+
+def summarise_trace(trace, pk):
+    """Group the traced C-ABI calls into kernel families; algorithmic flops / bytes per SURVEY §8d."""
+    fam = {}
+    for name, a, ms in trace:
+        flops = byts = 0.0
+        key = name
+        if name.startswith("cnb_conv2d_") and a and isinstance(a[0], dict):
+            d = a[0]
+            flops, P, Q = conv_flops(d)
+            es = 2 if d["dtype"] == 1 else 4
+            byts = (d["N"] * d["H"] * d["W"] * d["C"] + d["N"] * P * Q * d["K"]) * es + \
+                d["K"] * (d["C"] // d["groups"]) * d["R"] * d["S"] * es
+            if d["groups"] == d["C"] and d["groups"] > 1:
+                key = name + "(depthwise)"
+        elif name.startswith("cnb_bn_") and a and isinstance(a[0], dict):
+            d = a[0]
+            es = 2 if d["dtype"] == 1 else 4
+            n_t = {"cnb_bn_fwd_train": 2, "cnb_bn_fwd_eval": 2, "cnb_bn_bwd": 3}[name]
+            if d["flags"] & 2:
+                n_t += 1  # residual read (fwd) / residual-gradient write (bwd)
+            if name == "cnb_bn_bwd" and d["flags"] & 1:
+                n_t += 1  # y read for the ReLU mask
+            byts = n_t * d["M"] * d["C"] * es
+        f = fam.setdefault(key, {"calls": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
+        f["calls"] += 1
+        f["ms"] += ms
+        f["flops"] += flops
+        f["bytes"] += byts
+    total = sum(f["ms"] for f in fam.values()) or 1.0
+    for f in fam.values():
+        f["share"] = f["ms"] / total
+        f["tflops"] = f["flops"] / (f["ms"] * 1e-3) / 1e12 if f["ms"] > 0 else 0.0
+        f["gbs"] = f["bytes"] / (f["ms"] * 1e-3) / 1e9 if f["ms"] > 0 else 0.0
+    return fam, total
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    from convnets_b200 import convert, lib as L, zoo as M
+    from convnets_b200.dataparallel import GradSync
+
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: convnets_b200 has no CPU fallback "
+                           "(use --impl reference for the CPU path)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    L.load()
+    cls, kind, defb = WORKLOADS[args.model]
+    B = args.batch or defb
+    dtype = torch.bfloat16 if args.dtype == "bf16" else torch.float32
+
+    torch.manual_seed(21)
+    s = M.Settings(kind=kind, input_size=(3, args.hw, args.hw), num_classes=10)
+    s.device.set_device(f"cuda:{local}")
+    model = getattr(M, cls)(s)
+    convert(model, dtype=dtype)
+    s.device.move(model)
+    model.init_optimizer()
+    sync = GradSync(model) if world > 1 else None
+
+    g = torch.Generator().manual_seed(21 + rank)
+    n_host = 2
+    host = [(torch.randn(B, 3, args.hw, args.hw, generator=g).pin_memory(),
+             torch.randint(0, 10, (B,), generator=g).pin_memory()) for _ in range(n_host)]
+    resident = [(x.to(dev), y.to(dev)) for x, y in host]
+
+    def step(batch):
+        model.optimizer.zero_grad()
+        out = model(batch[0])
+        loss = model.cost_function(out.float(), batch[1])
+        loss.backward()
+        model.gradient_clipping()
+        model.optimizer.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    model.train()
+    for i in range(args.warmup):
+        step(resident[i % n_host])
+    barrier()
+    clocks = ClockSampler(torch.cuda.current_device() if "CUDA_VISIBLE_DEVICES" not in os.environ
+                          else local)
+    if rank == 0:
+        clocks.start()
+    n0 = L.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        loss = step(resident[i % n_host])
+    e1.record()
+    barrier()
+    launches = L.launch_count() - n0
+    ms = e0.elapsed_time(e1)
+    final_loss = float(loss.item())
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    clk = clocks.stop() if rank == 0 else None
+    value = world * B * args.steps / (ms * 1e-3)
+
+    # ---- end to end through the public API (train_model over pinned host batches)
+    e2e = None
+    if not args.no_e2e:
+        loader = HostLoader([host[i % n_host] for i in range(args.steps)])
+        model.train_model(HostLoader(host[:1]))  # warm the path (pinned -> device copies)
+        barrier()
+        t0 = time.perf_counter()
+        e0.record()
+        model.train_model(loader)
+        e1.record()
+        barrier()
+        wall = (time.perf_counter() - t0) * 1e3
+        t = torch.tensor([max(e0.elapsed_time(e1), 0.0), wall], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_e = float(t[0].item())
+        x0, y0 = host[0]
+        e2e = {"value": world * B * args.steps / (ms_e * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": x0.numel() * x0.element_size() + y0.numel() * y0.element_size(),
+               "d2h_bytes_per_step": 4 + 8, "ms_per_step": ms_e / args.steps,
+               "wall_ms_per_step": float(t[1].item()) / args.steps,
+               "api": "MultiClassBaseModel.train_model(loader of pinned host batches)"}
+
+    # ---- roofline of the dominant kernel family: one traced step (outside the timed regions)
+    roof, fam = None, None
+    if rank == 0:
+        pk = peaks()
+        step(resident[0])
+        torch.cuda.synchronize()
+        L.trace_begin()
+        step(resident[0])
+        trace = L.trace_end()
+        fam, total = summarise_trace(trace, pk)
+        top = max(fam.items(), key=lambda kv: kv[1]["ms"])
+        name, f = top
+        per = f["calls"]
+        if name.startswith("cnb_conv2d_") and "depthwise" not in name:
+            roof = {"bound": "tensor", "achieved": f["tflops"], "peak": pk["tensor"], "unit": "TFLOP/s",
+                    "frac": f["tflops"] / pk["tensor"], "traffic": None}
+        else:
+            roof = {"bound": "hbm", "achieved": f["gbs"], "peak": pk["hbm"], "unit": "GB/s",
+                    "frac": f["gbs"] / pk["hbm"], "traffic": None}
+        roof.update({"kernel": name, "launches_per_step": per, "avg_launch_ms": f["ms"] / per,
+                     "share_of_step": f["share"], "peak_source": pk["src"] +
+                     (" (sustained cuBLAS bf16)" if roof["bound"] == "tensor" else " (copy)"),
+                     "traced_step_ms": total})
+        conv_ms = sum(v["ms"] for k, v in fam.items() if k.startswith("cnb_conv2d_"))
+        conv_fl = sum(v["flops"] for k, v in fam.items() if k.startswith("cnb_conv2d_"))
+        roof["all_conv_tflops"] = conv_fl / (conv_ms * 1e-3) / 1e12 if conv_ms else 0.0
+        roof["all_conv_share"] = conv_ms / total
+        if args.trace_out:
+            os.makedirs(os.path.dirname(os.path.abspath(args.trace_out)), exist_ok=True)
+            with open(args.trace_out, "w") as fh:
+                json.dump({"families": fam, "calls": [[n, a, m] for n, a, m in trace]}, fh)
+        tbl = sorted(fam.items(), key=lambda kv: -kv[1]["ms"])
+        for k, v in tbl:
+            print(f"# {k:34s} calls {v['calls']:4d}  {v['ms']:8.3f} ms  {100 * v['share']:5.1f}%  "
+                  f"{v['tflops']:7.1f} TFLOP/s  {v['gbs']:7.0f} GB/s", file=sys.stderr)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu = cpu_reference(args, args.cpu_steps, 1, args.cpu_batch)
+        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+            "config": {"workload": f"{cls}-{kind} train step (fwd + CE-sum loss + bwd + Adam), "
+                                   f"{args.hw}x{args.hw}x3, 10 classes, batch {B}/GPU",
+                       "global_batch": B * world, "parallelism": f"dp{world}",
+                       "l2": "working set per step (activations > 10 GB) far exceeds the 126 MB L2; "
+                             "no explicit flush",
+                       "dropout_rate": s.dropout_rate, "optimizer": "Adam lr 0.01 wd 1e-4",
+                       "final_loss": final_loss},
+            "clocks": clk, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof,
+            "cpu_baseline": cpu,
+        }
+        if sync is not None:
+            line["config"]["allreduces_per_step"] = sync.launched // max(1, (args.steps * (1 if args.no_e2e else 2) + args.warmup + 3))
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

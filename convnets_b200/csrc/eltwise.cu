@@ -93,20 +93,21 @@ __global__ void cast_f32_bf16_v4(const float* __restrict__ s, bf16* __restrict__
 // One block transposes a [C x 32] (channels x pixels) slab through shared memory so both the
 // NCHW reads (pixel-contiguous) and the NHWC writes (channel-contiguous) are coalesced.
 template <typename T>
-__global__ void nchw_to_nhwc_k(const float* __restrict__ src, T* __restrict__ dst, int C, int HW) {
+__global__ void nchw_to_nhwc_k(const float* __restrict__ src, T* __restrict__ dst, int C, int Cd,
+                               int HW) {
   extern __shared__ float tile[];  // [C][33]
   const int n = blockIdx.y;
   const int p0 = blockIdx.x * 32;
   const float* s = src + (int64_t)n * C * HW;
-  T* o = dst + (int64_t)n * HW * C;
+  T* o = dst + (int64_t)n * HW * Cd;
   for (int i = threadIdx.x; i < C * 32; i += blockDim.x) {
     int c = i / 32, p = i % 32;
     tile[c * 33 + p] = (p0 + p < HW) ? s[(int64_t)c * HW + p0 + p] : 0.f;
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < C * 32; i += blockDim.x) {
-    int p = i / C, c = i % C;
-    if (p0 + p < HW) o[(int64_t)(p0 + p) * C + c] = from_f<T>(tile[c * 33 + p]);
+  for (int i = threadIdx.x; i < Cd * 32; i += blockDim.x) {
+    int p = i / Cd, c = i % Cd;
+    if (p0 + p < HW) o[(int64_t)(p0 + p) * Cd + c] = from_f<T>(c < C ? tile[c * 33 + p] : 0.f);
   }
 }
 
@@ -447,15 +448,15 @@ int cnb_cast(const void* src, int sdt, void* dst, int ddt, int64_t n, void* stre
 }
 
 int cnb_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t H, int32_t W,
-                     int dtype, void* stream) {
-  CNB_REQUIRE(src && dst && N > 0 && C > 0 && H > 0 && W > 0 && valid_dtype(dtype), CNB_ERR_INVALID,
-              "cnb_nchw_to_nhwc: bad args");
+                     int32_t C_dst, int dtype, void* stream) {
+  CNB_REQUIRE(src && dst && N > 0 && C > 0 && H > 0 && W > 0 && C_dst >= C && valid_dtype(dtype),
+              CNB_ERR_INVALID, "cnb_nchw_to_nhwc: bad args");
   CNB_REQUIRE((size_t)C * 33 * 4 <= 48 * 1024, CNB_ERR_UNSUPPORTED,
               "cnb_nchw_to_nhwc: C=%d too large (input-image conversion only)", C);
   int HW = H * W;
   dim3 grid((unsigned)ceil_div(HW, 32), N);
   size_t smem = (size_t)C * 33 * sizeof(float);
-  CNB_DISPATCH_T(dtype, (nchw_to_nhwc_k<T><<<grid, 256, smem, (cudaStream_t)stream>>>(src, (T*)dst, C, HW)));
+  CNB_DISPATCH_T(dtype, (nchw_to_nhwc_k<T><<<grid, 256, smem, (cudaStream_t)stream>>>(src, (T*)dst, C, C_dst, HW)));
   return check_launch("nchw_to_nhwc");
 }
 

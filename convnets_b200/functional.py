@@ -71,20 +71,23 @@ def _pair(v):
 
 
 # ----------------------------------------------------------------------------- layout / dtype
-def to_nhwc(x: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+def to_nhwc(x: torch.Tensor, dtype: torch.dtype, c_dst: Optional[int] = None) -> torch.Tensor:
     """Network-input conversion: fp32 NCHW -> `dtype` NHWC (reference: the H2D'd batch enters
-    the first conv as fp32 NCHW, src/basemodel.py:185-188)."""
+    the first conv as fp32 NCHW, src/basemodel.py:185-188).  With `c_dst` > C the result has
+    c_dst channels, the extra ones zero (feeds the tensor-core stem)."""
     _cuda(x)
     if x.dim() != 4:
         raise ValueError("to_nhwc expects [N, C, H, W]")
-    if x.dtype == dtype and x.is_contiguous(memory_format=_CL):
+    n, c, h, w = x.shape
+    c_dst = c if c_dst is None else int(c_dst)
+    if c_dst == c and x.dtype == dtype and x.is_contiguous(memory_format=_CL):
         return x
     if x.dtype != torch.float32 or not x.is_contiguous():
         x = x.float().contiguous()
-    n, c, h, w = x.shape
-    y = _empty_nhwc(n, c, h, w, dtype, x.device)
+    y = _empty_nhwc(n, c_dst, h, w, dtype, x.device)
     lib = _L.load()
-    _L.check(lib.cnb_nchw_to_nhwc(_p(x), _p(y), n, c, h, w, _dt(y), _stream()), "cnb_nchw_to_nhwc")
+    _L.check(lib.cnb_nchw_to_nhwc(_p(x), _p(y), n, c, h, w, c_dst, _dt(y), _stream()),
+             "cnb_nchw_to_nhwc")
     return y
 
 
@@ -97,10 +100,15 @@ def cast(src: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
     return dst
 
 
-def pack_weight(weight: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+def pack_weight(weight: torch.Tensor, dtype: torch.dtype, c_dst: Optional[int] = None) -> torch.Tensor:
     """fp32 master weight [K, C/g, R, S] -> KRSC operand copy in `dtype` (a channels_last tensor
-    of the same logical shape)."""
+    of the same logical shape, or with the channel dimension zero-padded to `c_dst`)."""
     w = weight.detach()
+    if c_dst is not None and c_dst > w.shape[1]:
+        wp = torch.empty((w.shape[0], c_dst, w.shape[2], w.shape[3]), dtype=w.dtype, device=w.device,
+                         memory_format=_CL).zero_()
+        wp[:, :w.shape[1]] = w
+        w = wp
     if not w.is_contiguous(memory_format=_CL):
         w = w.contiguous(memory_format=_CL)
     if w.dtype == dtype:
@@ -161,13 +169,16 @@ class _Conv2dFn(torch.autograd.Function):
             _L.check(lib.cnb_conv2d_dgrad(C.byref(d), _p(dy), _p(wpack), _p(dx), _p(ws), ws.numel(),
                                           _stream()), "cnb_conv2d_dgrad")
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
-            dw = torch.empty(ctx.wshape, dtype=torch.float32, device=x.device, memory_format=_CL)
+            dw = torch.empty(tuple(wpack.shape), dtype=torch.float32, device=x.device,
+                             memory_format=_CL)
             if ctx.has_bias:
                 db = torch.empty(ctx.wshape[0], dtype=torch.float32, device=x.device)
             nws = lib.cnb_conv2d_workspace_bytes(C.byref(d), _L.CNB_WGRAD)
             ws = _workspace(nws, x.device)
             _L.check(lib.cnb_conv2d_wgrad(C.byref(d), _p(x), _p(dy), _p(dw), _p(db), _p(ws),
                                           ws.numel(), _stream()), "cnb_conv2d_wgrad")
+            if tuple(dw.shape) != ctx.wshape:  # zero-padded input channels (RGB stem)
+                dw = dw[:, :ctx.wshape[1]].contiguous(memory_format=_CL)
         return dx, dw, db, None, None, None, None, None, None
 
 

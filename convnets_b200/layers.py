@@ -19,21 +19,32 @@ class Conv2d(nn.Conv2d):
     dense bf16 layers, CUDA cores for fp32 / grouped / depthwise)."""
 
     algo = _L.CNB_ALGO_AUTO
+    # set by convert(): arithmetic dtype of the feature maps, and whether this layer is the
+    # network entry (its fp32 NCHW input batch is converted to `compute_dtype` NHWC first)
+    compute_dtype = None
+    cast_input = False
 
-    def _packed(self, dtype: torch.dtype) -> torch.Tensor:
+    def _packed(self, dtype: torch.dtype, c_dst=None) -> torch.Tensor:
         w = self.weight
-        key = (w._version, w.data_ptr(), dtype)
+        key = (w._version, w.data_ptr(), dtype, c_dst)
         cache = self.__dict__.get("_cnb_pack")
         if cache is None or cache[0] != key:
-            cache = (key, F_.pack_weight(w, dtype))
+            cache = (key, F_.pack_weight(w, dtype, c_dst))
             self.__dict__["_cnb_pack"] = cache
         return cache[1]
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if self.padding_mode != "zeros" or isinstance(self.padding, str):
             raise NotImplementedError("convnets_b200.Conv2d supports integer zero padding only")
+        c_dst = None
+        if self.cast_input and self.compute_dtype is not None and not x.requires_grad:
+            # network entry: fp32 NCHW batch -> compute dtype NHWC; an RGB stem is zero-padded to 8
+            # channels so that it qualifies for the tensor-core path (16-byte TMA rows)
+            if self.compute_dtype == torch.bfloat16 and self.groups == 1 and x.shape[1] % 8:
+                c_dst = (x.shape[1] + 7) // 8 * 8
+            x = F_.to_nhwc(x, self.compute_dtype, c_dst)
         return F_.conv2d(x, self.weight, self.bias, self.stride, self.padding, self.dilation,
-                         self.groups, wpack=self._packed(x.dtype), algo=self.algo)
+                         self.groups, wpack=self._packed(x.dtype, c_dst), algo=self.algo)
 
 
 class BatchNorm2d(nn.BatchNorm2d):
@@ -42,7 +53,8 @@ class BatchNorm2d(nn.BatchNorm2d):
 
     fuse_relu = False
 
-    def forward(self, x: torch.Tensor, residual: torch.Tensor | None = None) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, residual: torch.Tensor | None = None,
+                relu: bool | None = None) -> torch.Tensor:
         self._check_input_dim(x)
         training = self.training or (self.running_mean is None and self.running_var is None)
         momentum = 0.0 if self.momentum is None else self.momentum
@@ -53,7 +65,7 @@ class BatchNorm2d(nn.BatchNorm2d):
         rm = self.running_mean if (not training or self.track_running_stats) else None
         rv = self.running_var if (not training or self.track_running_stats) else None
         return F_.batch_norm(x, self.weight, self.bias, rm, rv, training, momentum, self.eps,
-                             relu=self.fuse_relu, residual=residual)
+                             relu=self.fuse_relu if relu is None else relu, residual=residual)
 
 
 class ReLU(nn.ReLU):

@@ -69,7 +69,7 @@ SIGNATURES = {
     "cnb_gap_bwd": (_I, [_P, _P, _I32, _I32, _I32, _I, _P]),
     "cnb_channel_shuffle": (_I, [_P, _P, _I64, _I32, _I32, _I, _P]),
     "cnb_copy_channels": (_I, [_P, _I32, _I32, _P, _I32, _I32, _I64, _I32, _I, _P]),
-    "cnb_nchw_to_nhwc": (_I, [_P, _P, _I32, _I32, _I32, _I32, _I, _P]),
+    "cnb_nchw_to_nhwc": (_I, [_P, _P, _I32, _I32, _I32, _I32, _I32, _I, _P]),
     "cnb_cast": (_I, [_P, _I, _P, _I, _I64, _P]),
     "cnb_se_scale_fwd": (_I, [_P, _P, _P, _I32, _I32, _I32, _I, _P]),
     "cnb_se_scale_bwd": (_I, [_P, _P, _P, _P, _P, _I32, _I32, _I32, _I, _P]),
@@ -99,8 +99,69 @@ def load() -> C.CDLL:
         fn = getattr(lib, name)  # AttributeError if the .so lacks a declared symbol
         fn.restype = res
         fn.argtypes = args
-    _lib = lib
-    return lib
+    _lib = _Calls(lib)
+    return _lib
+
+
+class _Calls:
+    """Attribute proxy over the CDLL.  Normally a pass-through; between `trace_begin()` and
+    `trace_end()` every entry point that enqueues work is bracketed by CUDA events on the
+    launching stream so bench.py can attribute device time to kernels (measurement only)."""
+
+    def __init__(self, cdll):
+        self._cdll = cdll
+        self._trace = None
+
+    def __getattr__(self, name):
+        fn = getattr(self._cdll, name)
+        if name in _NO_STREAM:
+            setattr(self, name, fn)
+            return fn
+
+        def call(*args, _fn=fn, _name=name):
+            tr = self._trace
+            if tr is None:
+                return _fn(*args)
+            import torch
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            r = _fn(*args)
+            e1.record()
+            tr.append((_name, _describe(args), e0, e1))
+            return r
+
+        setattr(self, name, call)
+        return call
+
+
+_NO_STREAM = {"cnb_version", "cnb_last_error", "cnb_launch_count", "cnb_conv2d_out_dims",
+              "cnb_conv2d_uses_tc", "cnb_conv2d_workspace_bytes", "cnb_bn_workspace_bytes"}
+
+
+def _describe(args):
+    """Plain-Python copy of the scalar arguments / descriptor fields of one call."""
+    out = []
+    for a in args:
+        obj = getattr(a, "_obj", None)  # byref(struct)
+        if isinstance(obj, C.Structure):
+            out.append({f: getattr(obj, f) for f, _ in obj._fields_})
+        elif isinstance(a, (int, float)):
+            out.append(a)
+    return out
+
+
+def trace_begin() -> None:
+    load()._trace = []
+
+
+def trace_end():
+    """-> list of (entry point, args, milliseconds); synchronises the device."""
+    import torch
+    lib = load()
+    tr, lib._trace = lib._trace, None
+    torch.cuda.synchronize()
+    return [(n, d, e0.elapsed_time(e1)) for n, d, e0, e1 in (tr or [])]
 
 
 def last_error() -> str:

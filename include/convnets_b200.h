@@ -166,9 +166,11 @@ int cnb_channel_shuffle(const void* x, void* y, int64_t M, int32_t C, int32_t gr
  * shufflenet_v1.py:167) forward (dst is the concat buffer) and backward (src is its gradient). */
 int cnb_copy_channels(const void* src, int32_t src_C, int32_t src_off, void* dst, int32_t dst_C,
                       int32_t dst_off, int64_t M, int32_t Ccopy, int dtype, void* stream);
-/* layout / precision conversion of the network input: src fp32 NCHW -> dst `dtype` NHWC */
+/* layout / precision conversion of the network input: src fp32 NCHW [N,C,H,W] -> dst `dtype`
+ * NHWC [N,H,W,C_dst], channels C..C_dst-1 zero-filled (C_dst = 8 lets an RGB stem take the
+ * tensor-core path, whose TMA rows must be multiples of 16 bytes) */
 int cnb_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t H, int32_t W,
-                     int dtype, void* stream);
+                     int32_t C_dst, int dtype, void* stream);
 /* element-wise precision conversion (fp32 master weights -> bf16 operand copy, etc.) */
 int cnb_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n, void* stream);
 

@@ -251,9 +251,6 @@ def test_sk_fuse_select(dtype):
     dg = torch.randn(n, c, 1, 1)
     (y.float() * dev(dy).float()).sum().backward(retain_graph=True)
     a, b, l = (t.double().requires_grad_(True) for t in (u0, u1, logits))
-    (O.sk_select(a, b, l) * dy.double()).sum().backward()
-    # oracle helper detaches; redo with plain torch for the gradient
-    a, b, l = (t.double().requires_grad_(True) for t in (u0, u1, logits))
     fm = torch.stack([a, b], dim=1)
     att = torch.softmax(l.reshape(n, 2, c, 1, 1), dim=1)
     (torch.sum(fm * att, dim=1) * dy.double()).sum().backward()
