@@ -3,16 +3,18 @@
 // src/basemodel.py:1008,1061; src/densenet.py:80,117,124,182; src/mobilenet_v1.py:108,119.
 //
 // Structure (all HBM-bound, 128-bit accesses along C):
-//   stats   : per-(row-chunk, channel) shifted sums  -> fp32 partials in the workspace
-//   finalize: Chan-merge of the partials in fp64, running-stat update, scale/shift vectors
+//   stats   : per-(row-chunk, channel) shifted sums -> fp32 partials in the workspace; the last
+//             CTA of each channel block to arrive merges the partials in split order (fp64),
+//             updates the running statistics and emits the scale/shift vectors
 //   apply   : y = [relu](x*scale + shift [+ residual])
-//   bwd     : reduce (sum dy', sum dy'*xhat) -> finalize (dgamma, dbeta, coefficients) -> dx
-// Two-stage reductions (no atomics) keep results bit-reproducible run to run.
+//   bwd     : reduce (sum dy', sum dy'*(x-mean)) + last-CTA merge (dgamma, dbeta, coefficients) -> dx
+// The merges sum in a fixed order (no floating-point atomics): results are bit-reproducible.
 #include "common.cuh"
 
 namespace cnb {
 
 constexpr int kBnThreads = 256;
+constexpr int kBnUnroll = 4;
 
 struct BnGeom {
   int V;          // channels per thread
@@ -23,7 +25,9 @@ struct BnGeom {
   int64_t rows_per_split;
 };
 
-static BnGeom bn_geom(int64_t M, int C, int V) {
+// `waves`: target resident CTAs per SM.  The reduction kernels use few, fat CTAs (their partials
+// are merged by the last CTA of each channel block); the streaming kernels use more.
+static BnGeom bn_geom(int64_t M, int C, int V, int waves) {
   BnGeom g;
   g.V = V;
   int cvs = C / V;
@@ -32,28 +36,128 @@ static BnGeom bn_geom(int64_t M, int C, int V) {
   g.cx = p;
   g.ry = kBnThreads / g.cx;
   g.cblocks = (int)ceil_div(cvs, g.cx);
-  int64_t target = (int64_t)sm_count() * 8;
+  int64_t target = (int64_t)sm_count() * waves;
   int64_t splits = ceil_div(target, g.cblocks);
-  int64_t max_splits = ceil_div(M, (int64_t)g.ry * 4);  // at least ~4 rows per thread
+  int64_t max_splits = ceil_div(M, (int64_t)g.ry * kBnUnroll);  // >= one unrolled trip per thread
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
-  if (splits > 4096) splits = 4096;
+  if (splits > 2048) splits = 2048;
   g.rows_per_split = ceil_div(M, splits);
   g.splits = (int)ceil_div(M, g.rows_per_split);
   return g;
 }
 
-// workspace layout (floats): [0, 3*splits*C) partials | then up to 5*C floats of per-channel
+// Arrival counters for the "last CTA of a channel block merges the partials" step.  Library-owned,
+// zero-initialised once per device and left at zero by every kernel that uses them; each call
+// takes the next of kCounterSlots slots so that calls in flight on different streams do not share.
+constexpr int kCounterSlots = 64, kCountersPerSlot = 64;
+static int* bn_counters(int cblocks) {
+  static int* base[64] = {nullptr};
+  static std::atomic<unsigned> next{0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || cblocks > kCountersPerSlot) return nullptr;
+  if (!base[dev]) {
+    int* p = nullptr;
+    if (cudaMalloc(&p, kCounterSlots * kCountersPerSlot * sizeof(int)) != cudaSuccess) return nullptr;
+    cudaMemset(p, 0, kCounterSlots * kCountersPerSlot * sizeof(int));
+    base[dev] = p;
+  }
+  return base[dev] + (next.fetch_add(1) % kCounterSlots) * kCountersPerSlot;
+}
+
+// workspace layout (floats): [0, 2*splits*C) partials | then 5*C floats of per-channel
 // coefficients (scale, shift / c1, c2, c3)
 
+struct BnFwdFin {
+  const float* gamma; const float* beta;
+  float* rmean; float* rvar; float* save_mean; float* save_rstd; float* scale; float* shift;
+  float eps, momentum;
+};
+struct BnBwdFin {
+  const float* gamma; const float* rstd;
+  float* dgamma; float* dbeta; float* c1; float* c2; float* c3;
+};
+
+// Block-level tail shared by the two reduction kernels: tree-reduce the per-thread (s, q) over the
+// row lanes, store the CTA's partial, and let the last-arriving CTA of this channel block sum all
+// partials in split order (fixed order => bit-reproducible) in fp64.  Returns true in the threads
+// that own a finished channel (S, Q valid).
+template <int V>
+__device__ __forceinline__ bool bn_block_merge(float (&s)[V], float (&q)[V], float* red,
+                                               float* __restrict__ part, int C, int splits,
+                                               int* __restrict__ counter, int& c_out, double& S,
+                                               double& Q) {
+  const int cx = blockDim.x, ry = blockDim.y;
+  const int W = cx * V;
+  const int t = threadIdx.y * cx + threadIdx.x;
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    red[(threadIdx.y * 2 + 0) * W + threadIdx.x * V + j] = s[j];
+    red[(threadIdx.y * 2 + 1) * W + threadIdx.x * V + j] = q[j];
+  }
+  __syncthreads();
+  for (int st = ry >> 1; st > 0; st >>= 1) {
+    if ((int)threadIdx.y < st) {
+#pragma unroll
+      for (int j = 0; j < 2 * V; ++j) {
+        const int col = threadIdx.x * V + (j % V);
+        const int which = j / V;
+        red[(threadIdx.y * 2 + which) * W + col] += red[((threadIdx.y + st) * 2 + which) * W + col];
+      }
+    }
+    __syncthreads();
+  }
+  const int cbase = blockIdx.x * W;
+  for (int i = t; i < 2 * W; i += kBnThreads) {
+    const int which = i / W, col = i % W;
+    if (cbase + col < C)
+      part[((int64_t)blockIdx.y * 2 + which) * C + cbase + col] = red[which * W + col];
+  }
+  __threadfence();
+  __syncthreads();
+  __shared__ int s_last;
+  if (t == 0) {
+    int prev = atomicAdd(counter + blockIdx.x, 1);
+    s_last = (prev == splits - 1);
+    if (s_last) counter[blockIdx.x] = 0;  // leave the slot clean for the next call
+  }
+  __syncthreads();
+  if (!s_last) return false;
+  __threadfence();
+  // 256 threads = (256 / W) split-lanes x W channels
+  double* dred = reinterpret_cast<double*>(red);
+  const int lanes = kBnThreads / W;
+  const int col = t % W, lane = t / W;
+  const int c = cbase + col;
+  double a = 0.0, b = 0.0;
+  if (c < C)
+    for (int sp = lane; sp < splits; sp += lanes) {
+      a += (double)__ldcg(part + ((int64_t)sp * 2 + 0) * C + c);
+      b += (double)__ldcg(part + ((int64_t)sp * 2 + 1) * C + c);
+    }
+  __syncthreads();
+  dred[(lane * 2 + 0) * W + col] = a;
+  dred[(lane * 2 + 1) * W + col] = b;
+  __syncthreads();
+  if (lane != 0 || c >= C) return false;
+  S = 0.0; Q = 0.0;
+  for (int l = 0; l < lanes; ++l) {
+    S += dred[(l * 2 + 0) * W + col];
+    Q += dred[(l * 2 + 1) * W + col];
+  }
+  c_out = c;
+  return true;
+}
+
 // ---------------------------------------------------------------- forward statistics
-// partial[split][0][c] = sum(x - K_c), partial[split][1][c] = sum((x - K_c)^2) with the pivot
-// K_c = x[first row of the split][c] (kills the mean^2/var cancellation of a raw sumsq).
-// pivot[split][c] is stored too.
+// Shifted sums about the pivot K_c = x[row 0][c] (kills the mean^2/var cancellation of a raw
+// sum of squares): s = sum(x - K), q = sum((x - K)^2); mean = K + s/M, var = q/M - (s/M)^2.
 template <typename T, int V>
-__global__ void bn_stats_k(const T* __restrict__ x, float* __restrict__ part, int64_t M, int C,
-                           int64_t rows_per_split) {
-  extern __shared__ float red[];  // [ry][2][cx*V]
+__global__ void __launch_bounds__(kBnThreads)
+bn_stats_k(const T* __restrict__ x, float* __restrict__ part, int64_t M, int C,
+           int64_t rows_per_split, int splits, int* __restrict__ counter, BnFwdFin f) {
+  extern __shared__ __align__(16) float red[];  // [ry][2][cx*V] floats (>= lanes*2*W doubles)
   const int cv = blockIdx.x * blockDim.x + threadIdx.x;
   const int c0 = cv * V;
   const int64_t r0 = blockIdx.y * rows_per_split;
@@ -63,82 +167,51 @@ __global__ void bn_stats_k(const T* __restrict__ x, float* __restrict__ part, in
 #pragma unroll
   for (int j = 0; j < V; ++j) s[j] = q[j] = piv[j] = 0.f;
   if (c0 < C) {
-    Pack<T, V> p0 = ld_pack<T, V>(x + r0 * C + c0);
+    Pack<T, V> p0 = ld_pack<T, V>(x + c0);
 #pragma unroll
     for (int j = 0; j < V; ++j) piv[j] = to_f(p0.v[j]);
-    for (int64_t r = r0 + threadIdx.y; r < r1; r += blockDim.y) {
-      Pack<T, V> a = ld_pack<T, V>(x + r * C + c0);
+    const int64_t step = (int64_t)blockDim.y * kBnUnroll;
+    for (int64_t r = r0 + threadIdx.y; r < r1; r += step) {
+      Pack<T, V> a[kBnUnroll];
 #pragma unroll
-      for (int j = 0; j < V; ++j) {
-        float d = to_f(a.v[j]) - piv[j];
-        s[j] += d;
-        q[j] = fmaf(d, d, q[j]);
+      for (int u = 0; u < kBnUnroll; ++u) {
+        int64_t rr = r + (int64_t)u * blockDim.y;
+        if (rr < r1) a[u] = ld_pack<T, V>(x + rr * C + c0);
+      }
+#pragma unroll
+      for (int u = 0; u < kBnUnroll; ++u) {
+        int64_t rr = r + (int64_t)u * blockDim.y;
+        if (rr < r1) {
+#pragma unroll
+          for (int j = 0; j < V; ++j) {
+            float d = to_f(a[u].v[j]) - piv[j];
+            s[j] += d;
+            q[j] = fmaf(d, d, q[j]);
+          }
+        }
       }
     }
   }
-  const int W = blockDim.x * V;
-#pragma unroll
-  for (int j = 0; j < V; ++j) {
-    red[(threadIdx.y * 2 + 0) * W + threadIdx.x * V + j] = s[j];
-    red[(threadIdx.y * 2 + 1) * W + threadIdx.x * V + j] = q[j];
+  int c;
+  double S, Q;
+  if (!bn_block_merge<V>(s, q, red, part, C, splits, counter, c, S, Q)) return;
+  const double K = (double)to_f(x[c]);
+  const double ms = S / (double)M;
+  const double mean = K + ms;
+  double var = Q / (double)M - ms * ms;  // biased: used for normalisation
+  if (var < 0.0) var = 0.0;
+  const float rstd = (float)(1.0 / sqrt(var + (double)f.eps));
+  const float mu = (float)mean;
+  f.save_mean[c] = mu;
+  f.save_rstd[c] = rstd;
+  if (f.rmean) f.rmean[c] = (1.f - f.momentum) * f.rmean[c] + f.momentum * mu;
+  if (f.rvar) {
+    double unbiased = M > 1 ? var * (double)M / (double)(M - 1) : var;
+    f.rvar[c] = (1.f - f.momentum) * f.rvar[c] + f.momentum * (float)unbiased;
   }
-  __syncthreads();
-  if (threadIdx.y == 0 && c0 < C) {
-    float* out = part + (int64_t)blockIdx.y * 3 * C;
-#pragma unroll
-    for (int j = 0; j < V; ++j) {
-      float ts = 0.f, tq = 0.f;
-      for (int r = 0; r < (int)blockDim.y; ++r) {
-        ts += red[(r * 2 + 0) * W + threadIdx.x * V + j];
-        tq += red[(r * 2 + 1) * W + threadIdx.x * V + j];
-      }
-      out[0 * C + c0 + j] = ts;
-      out[1 * C + c0 + j] = tq;
-      out[2 * C + c0 + j] = piv[j];
-    }
-  }
-}
-
-// One thread per channel: merge split partials (Chan et al.) in fp64, emit mean / rstd, update
-// the running statistics (momentum, unbiased variance) and the fused scale / shift vectors.
-__global__ void bn_finalize_fwd_k(const float* __restrict__ part, int splits, int64_t M,
-                                  int64_t rows_per_split, int C, const float* __restrict__ gamma,
-                                  const float* __restrict__ beta, float* __restrict__ rmean,
-                                  float* __restrict__ rvar, float* __restrict__ save_mean,
-                                  float* __restrict__ save_rstd, float* __restrict__ scale,
-                                  float* __restrict__ shift, float eps, float momentum) {
-  int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double n_acc = 0.0, mean = 0.0, m2 = 0.0;
-  for (int s = 0; s < splits; ++s) {
-    int64_t r0 = (int64_t)s * rows_per_split;
-    int64_t r1 = r0 + rows_per_split;
-    if (r1 > M) r1 = M;
-    double nb = (double)(r1 - r0);
-    const float* p = part + (int64_t)s * 3 * C;
-    double sb = p[c], qb = p[C + c], kb = p[2 * C + c];
-    double mean_b = kb + sb / nb;
-    double m2_b = qb - sb * sb / nb;
-    if (m2_b < 0.0) m2_b = 0.0;
-    double delta = mean_b - mean;
-    double n_new = n_acc + nb;
-    mean += delta * nb / n_new;
-    m2 += m2_b + delta * delta * n_acc * nb / n_new;
-    n_acc = n_new;
-  }
-  double var = m2 / (double)M;  // biased: used for normalisation
-  float rstd = (float)(1.0 / sqrt(var + (double)eps));
-  float mu = (float)mean;
-  save_mean[c] = mu;
-  save_rstd[c] = rstd;
-  if (rmean) rmean[c] = (1.f - momentum) * rmean[c] + momentum * mu;
-  if (rvar) {
-    double unbiased = M > 1 ? m2 / (double)(M - 1) : var;
-    rvar[c] = (1.f - momentum) * rvar[c] + momentum * (float)unbiased;
-  }
-  float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
-  scale[c] = g * rstd;
-  shift[c] = b - mu * g * rstd;
+  const float g = f.gamma ? f.gamma[c] : 1.f, b = f.beta ? f.beta[c] : 0.f;
+  f.scale[c] = g * rstd;
+  f.shift[c] = b - mu * g * rstd;
 }
 
 __global__ void bn_eval_coeff_k(const float* __restrict__ gamma, const float* __restrict__ beta,
@@ -153,39 +226,67 @@ __global__ void bn_eval_coeff_k(const float* __restrict__ gamma, const float* __
   shift[c] = b - rmean[c] * g * rstd;
 }
 
-// y = [relu](x*scale + shift [+ res])
+// y = [relu](x*scale + shift [+ res]); 2-D thread map (channel vector fixed per thread, so the
+// coefficients live in registers), kBnUnroll independent 16-byte loads in flight per thread.
 template <typename T, int V, bool RELU, bool ADD>
-__global__ void bn_apply_k(const T* __restrict__ x, const T* __restrict__ res,
-                           const float* __restrict__ scale, const float* __restrict__ shift,
-                           T* __restrict__ y, int64_t total_vec, int Cv) {
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    int cv = (int)(i % Cv);
-    Pack<T, V> a = ld_pack<T, V>(x + i * V), o;
-    Pack<T, V> r;
-    if (ADD) r = ld_pack<T, V>(res + i * V);
+__global__ void __launch_bounds__(kBnThreads)
+bn_apply_k(const T* __restrict__ x, const T* __restrict__ res, const float* __restrict__ scale,
+           const float* __restrict__ shift, T* __restrict__ y, int64_t M, int C,
+           int64_t rows_per_split) {
+  const int cv = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c0 = cv * V;
+  if (c0 >= C) return;
+  const int64_t r0 = blockIdx.y * rows_per_split;
+  int64_t r1 = r0 + rows_per_split;
+  if (r1 > M) r1 = M;
+  float sc[V], sh[V];
 #pragma unroll
-    for (int j = 0; j < V; ++j) {
-      float f = fmaf(to_f(a.v[j]), scale[cv * V + j], shift[cv * V + j]);
-      if (ADD) {
-        // the reference materialises bn(x) in the storage dtype before `output += identity`
-        f = to_f(from_f<T>(f)) + to_f(r.v[j]);
+  for (int j = 0; j < V; ++j) {
+    sc[j] = scale[c0 + j];
+    sh[j] = shift[c0 + j];
+  }
+  const int64_t step = (int64_t)blockDim.y * kBnUnroll;
+  for (int64_t r = r0 + threadIdx.y; r < r1; r += step) {
+    Pack<T, V> a[kBnUnroll], rs[kBnUnroll];
+#pragma unroll
+    for (int u = 0; u < kBnUnroll; ++u) {
+      int64_t rr = r + (int64_t)u * blockDim.y;
+      if (rr < r1) {
+        a[u] = ld_pack<T, V>(x + rr * C + c0);
+        if (ADD) rs[u] = ld_pack<T, V>(res + rr * C + c0);
       }
-      if (RELU) f = (f > 0.f || f != f) ? f : 0.f;
-      o.v[j] = from_f<T>(f);
     }
-    st_pack<T, V>(y + i * V, o);
+#pragma unroll
+    for (int u = 0; u < kBnUnroll; ++u) {
+      int64_t rr = r + (int64_t)u * blockDim.y;
+      if (rr < r1) {
+        Pack<T, V> o;
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          float v = fmaf(to_f(a[u].v[j]), sc[j], sh[j]);
+          if (ADD) {
+            // the reference materialises bn(x) in the storage dtype before `output += identity`
+            v = to_f(from_f<T>(v)) + to_f(rs[u].v[j]);
+          }
+          if (RELU) v = (v > 0.f || v != v) ? v : 0.f;
+          o.v[j] = from_f<T>(v);
+        }
+        st_pack<T, V>(y + rr * C + c0, o);
+      }
+    }
   }
 }
 
 // ---------------------------------------------------------------- backward reduce
-// partial[split][0][c] = sum dy', partial[split][1][c] = sum dy' * (x - mean)   (dy' = masked dy)
+// s = sum dy', q = sum dy' * (x - mean)   (dy' = dy masked by y > 0 when ReLU is fused), then
+// dbeta = s ; dgamma = rstd * q ; dx = c1 * (dy' - c2 - (x - mean) * c3) with
+// c1 = gamma*rstd, c2 = s/M, c3 = rstd^2 * q / M
 template <typename T, int V, bool RELU>
-__global__ void bn_bwd_reduce_k(const T* __restrict__ x, const T* __restrict__ y,
-                                const T* __restrict__ dy, const float* __restrict__ mean,
-                                float* __restrict__ part, int64_t M, int C,
-                                int64_t rows_per_split) {
-  extern __shared__ float red[];
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_reduce_k(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy,
+                const float* __restrict__ mean, float* __restrict__ part, int64_t M, int C,
+                int64_t rows_per_split, int splits, int* __restrict__ counter, BnBwdFin f) {
+  extern __shared__ __align__(16) float red[];
   const int cv = blockIdx.x * blockDim.x + threadIdx.x;
   const int c0 = cv * V;
   const int64_t r0 = blockIdx.y * rows_per_split;
@@ -197,99 +298,105 @@ __global__ void bn_bwd_reduce_k(const T* __restrict__ x, const T* __restrict__ y
   if (c0 < C) {
 #pragma unroll
     for (int j = 0; j < V; ++j) mu[j] = mean[c0 + j];
-    for (int64_t r = r0 + threadIdx.y; r < r1; r += blockDim.y) {
-      Pack<T, V> a = ld_pack<T, V>(x + r * C + c0);
-      Pack<T, V> g = ld_pack<T, V>(dy + r * C + c0);
-      Pack<T, V> o;
-      if (RELU) o = ld_pack<T, V>(y + r * C + c0);
+    constexpr int U = 2;
+    const int64_t step = (int64_t)blockDim.y * U;
+    for (int64_t r = r0 + threadIdx.y; r < r1; r += step) {
+      Pack<T, V> a[U], g[U], o[U];
 #pragma unroll
-      for (int j = 0; j < V; ++j) {
-        float gf = to_f(g.v[j]);
-        if (RELU && !(to_f(o.v[j]) > 0.f)) gf = 0.f;
-        s[j] += gf;
-        q[j] = fmaf(gf, to_f(a.v[j]) - mu[j], q[j]);
+      for (int u = 0; u < U; ++u) {
+        int64_t rr = r + (int64_t)u * blockDim.y;
+        if (rr < r1) {
+          a[u] = ld_pack<T, V>(x + rr * C + c0);
+          g[u] = ld_pack<T, V>(dy + rr * C + c0);
+          if (RELU) o[u] = ld_pack<T, V>(y + rr * C + c0);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        int64_t rr = r + (int64_t)u * blockDim.y;
+        if (rr < r1) {
+#pragma unroll
+          for (int j = 0; j < V; ++j) {
+            float gf = to_f(g[u].v[j]);
+            if (RELU && !(to_f(o[u].v[j]) > 0.f)) gf = 0.f;
+            s[j] += gf;
+            q[j] = fmaf(gf, to_f(a[u].v[j]) - mu[j], q[j]);
+          }
+        }
       }
     }
   }
-  const int W = blockDim.x * V;
-#pragma unroll
-  for (int j = 0; j < V; ++j) {
-    red[(threadIdx.y * 2 + 0) * W + threadIdx.x * V + j] = s[j];
-    red[(threadIdx.y * 2 + 1) * W + threadIdx.x * V + j] = q[j];
-  }
-  __syncthreads();
-  if (threadIdx.y == 0 && c0 < C) {
-    float* out = part + (int64_t)blockIdx.y * 3 * C;
-#pragma unroll
-    for (int j = 0; j < V; ++j) {
-      float ts = 0.f, tq = 0.f;
-      for (int r = 0; r < (int)blockDim.y; ++r) {
-        ts += red[(r * 2 + 0) * W + threadIdx.x * V + j];
-        tq += red[(r * 2 + 1) * W + threadIdx.x * V + j];
-      }
-      out[0 * C + c0 + j] = ts;
-      out[1 * C + c0 + j] = tq;
-    }
-  }
-}
-
-// dbeta = sum dy' ; dgamma = rstd * sum dy'(x-mean) ;
-// dx = c1 * (dy' - c2 - (x - mean) * c3), c1 = gamma*rstd, c2 = dbeta/M, c3 = rstd^2 * sumxc / M
-__global__ void bn_finalize_bwd_k(const float* __restrict__ part, int splits, int64_t M, int C,
-                                  const float* __restrict__ gamma, const float* __restrict__ rstd,
-                                  float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                  float* __restrict__ c1, float* __restrict__ c2,
-                                  float* __restrict__ c3) {
-  int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  double s = 0.0, q = 0.0;
-  for (int i = 0; i < splits; ++i) {
-    const float* p = part + (int64_t)i * 3 * C;
-    s += (double)p[c];
-    q += (double)p[C + c];
-  }
-  float rs = rstd[c];
-  float g = gamma ? gamma[c] : 1.f;
-  if (dbeta) dbeta[c] = (float)s;
-  if (dgamma) dgamma[c] = (float)(q * (double)rs);
-  c1[c] = g * rs;
-  c2[c] = (float)(s / (double)M);
-  c3[c] = (float)(q * (double)rs * (double)rs / (double)M);
+  int c;
+  double S, Q;
+  if (!bn_block_merge<V>(s, q, red, part, C, splits, counter, c, S, Q)) return;
+  const float rs = f.rstd[c];
+  const float g = f.gamma ? f.gamma[c] : 1.f;
+  if (f.dbeta) f.dbeta[c] = (float)S;
+  if (f.dgamma) f.dgamma[c] = (float)(Q * (double)rs);
+  f.c1[c] = g * rs;
+  f.c2[c] = (float)(S / (double)M);
+  f.c3[c] = (float)(Q * (double)rs * (double)rs / (double)M);
 }
 
 template <typename T, int V, bool RELU, bool DRES>
-__global__ void bn_bwd_dx_k(const T* __restrict__ x, const T* __restrict__ y,
-                            const T* __restrict__ dy, const float* __restrict__ mean,
-                            const float* __restrict__ c1, const float* __restrict__ c2,
-                            const float* __restrict__ c3, T* __restrict__ dx,
-                            T* __restrict__ dres, int64_t total_vec, int Cv) {
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    int cv = (int)(i % Cv);
-    Pack<T, V> a = ld_pack<T, V>(x + i * V), g = ld_pack<T, V>(dy + i * V), o, m, dr;
-    if (RELU) m = ld_pack<T, V>(y + i * V);
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_dx_k(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy,
+            const float* __restrict__ mean, const float* __restrict__ c1,
+            const float* __restrict__ c2, const float* __restrict__ c3, T* __restrict__ dx,
+            T* __restrict__ dres, int64_t M, int C, int64_t rows_per_split) {
+  const int cv = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c0 = cv * V;
+  if (c0 >= C) return;
+  const int64_t r0 = blockIdx.y * rows_per_split;
+  int64_t r1 = r0 + rows_per_split;
+  if (r1 > M) r1 = M;
+  // dx = k1*dy' + k3*x + k0  with k1 = c1, k3 = -c1*c3, k0 = c1*(c3*mean - c2)
+  float k1[V], k3[V], k0[V];
 #pragma unroll
-    for (int j = 0; j < V; ++j) {
-      const int c = cv * V + j;
-      float gf = to_f(g.v[j]);
-      if (RELU && !(to_f(m.v[j]) > 0.f)) gf = 0.f;
-      if (DRES) dr.v[j] = from_f<T>(gf);
-      float xc = to_f(a.v[j]) - mean[c];
-      o.v[j] = from_f<T>(c1[c] * (gf - c2[c] - xc * c3[c]));
+  for (int j = 0; j < V; ++j) {
+    const float a1 = c1[c0 + j], a2 = c2[c0 + j], a3 = c3[c0 + j], m = mean[c0 + j];
+    k1[j] = a1;
+    k3[j] = -a1 * a3;
+    k0[j] = a1 * (a3 * m - a2);
+  }
+  constexpr int U = 2;
+  const int64_t step = (int64_t)blockDim.y * U;
+  for (int64_t r = r0 + threadIdx.y; r < r1; r += step) {
+    Pack<T, V> a[U], g[U], m[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      int64_t rr = r + (int64_t)u * blockDim.y;
+      if (rr < r1) {
+        a[u] = ld_pack<T, V>(x + rr * C + c0);
+        g[u] = ld_pack<T, V>(dy + rr * C + c0);
+        if (RELU) m[u] = ld_pack<T, V>(y + rr * C + c0);
+      }
     }
-    st_pack<T, V>(dx + i * V, o);
-    if (DRES) st_pack<T, V>(dres + i * V, dr);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      int64_t rr = r + (int64_t)u * blockDim.y;
+      if (rr < r1) {
+        Pack<T, V> o, dr;
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          float gf = to_f(g[u].v[j]);
+          if (RELU && !(to_f(m[u].v[j]) > 0.f)) gf = 0.f;
+          if (DRES) dr.v[j] = from_f<T>(gf);
+          o.v[j] = from_f<T>(fmaf(k1[j], gf, fmaf(k3[j], to_f(a[u].v[j]), k0[j])));
+        }
+        st_pack<T, V>(dx + rr * C + c0, o);
+        if (DRES) st_pack<T, V>(dres + rr * C + c0, dr);
+      }
+    }
   }
 }
 
-constexpr int kMaxSplits = 4096;
+constexpr int kReduceWaves = 4, kStreamWaves = 8;
 static size_t bn_ws_bytes(int C) {
-  // partials: up to kMaxSplits x 3 x C floats is far too pessimistic; geometry caps
-  // splits*cblocks near 8 waves, so bound by (8*SMs + 1) blocks of at least 1 channel-vector:
-  // splits <= min(kMaxSplits, 8*SMs) -> 3*C*splits floats.
-  int64_t splits = (int64_t)sm_count() * 8;
-  if (splits > kMaxSplits) splits = kMaxSplits;
-  return (size_t)(3 * (int64_t)C * splits + 5 * (int64_t)C) * sizeof(float) + 256;
+  // partials: splits <= min(2048, kReduceWaves*SMs) rows of 2*C floats, then 5*C coefficients
+  int64_t splits = (int64_t)sm_count() * kReduceWaves;
+  if (splits > 2048) splits = 2048;
+  return (size_t)(2 * (int64_t)C * splits + 5 * (int64_t)C) * sizeof(float) + 256;
 }
 
 static int validate_bn(const cnb_bn_desc* d, const char* who) {
@@ -328,25 +435,30 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
   const int C = d->C;
   const int64_t M = d->M;
   int v = pick_vec(C, dtype_size(d->dtype), x, y, add ? residual : nullptr);
-  BnGeom g = bn_geom(M, C, v);
+  BnGeom g = bn_geom(M, C, v, kReduceWaves);
   float* part = (float*)workspace;
-  float* scale = part + (size_t)3 * C * g.splits;
+  float* scale = part + (size_t)2 * C * g.splits;
   float* shift = scale + C;
-  dim3 grid(g.cblocks, g.splits), block(g.cx, g.ry);
-  size_t smem = (size_t)g.ry * 2 * g.cx * v * sizeof(float);
-  CNB_DISPATCH_TV(d->dtype, v, (bn_stats_k<T, V><<<grid, block, smem, st>>>((const T*)x, part, M, C,
-                                                                           g.rows_per_split)));
-  CNB_TRY(check_launch("bn_stats"));
-  bn_finalize_fwd_k<<<(unsigned)ceil_div(C, 128), 128, 0, st>>>(
-      part, g.splits, M, g.rows_per_split, C, gamma, beta, running_mean, running_var, save_mean,
-      save_rstd, scale, shift, d->eps, d->momentum);
-  CNB_TRY(check_launch("bn_finalize_fwd"));
-  int64_t total = M * (C / v);
-  int gr = grid_for(total, kBnThreads);
+  int* counter = bn_counters(g.cblocks);
+  CNB_REQUIRE(counter, CNB_ERR_CUDA, "cnb_bn_fwd_train: cannot allocate the arrival counters");
+  {
+    dim3 grid(g.cblocks, g.splits), block(g.cx, g.ry);
+    size_t smem = (size_t)g.ry * 2 * g.cx * v * sizeof(float);
+    if (smem < 4096) smem = 4096;  // the merge step re-uses it for 256 x 2 doubles
+    BnFwdFin fin{gamma, beta, running_mean, running_var, save_mean, save_rstd, scale, shift,
+                 d->eps, d->momentum};
+    CNB_DISPATCH_TV(d->dtype, v, (bn_stats_k<T, V><<<grid, block, smem, st>>>(
+                                     (const T*)x, part, M, C, g.rows_per_split, g.splits, counter,
+                                     fin)));
+    CNB_TRY(check_launch("bn_stats"));
+  }
+  BnGeom ga = bn_geom(M, C, v, kStreamWaves);
+  dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
+  const int64_t arows = ga.rows_per_split;
 #define APPLY(R, A)                                                                              \
-  CNB_DISPATCH_TV(d->dtype, v, (bn_apply_k<T, V, R, A><<<gr, kBnThreads, 0, st>>>(               \
-                                   (const T*)x, (const T*)residual, scale, shift, (T*)y, total, \
-                                   C / V)))
+  CNB_DISPATCH_TV(d->dtype, v, (bn_apply_k<T, V, R, A><<<agrid, ablock, 0, st>>>(                \
+                                   (const T*)x, (const T*)residual, scale, shift, (T*)y, d->M,  \
+                                   C, arows)))
   if (relu && add) APPLY(true, true);
   else if (relu) APPLY(true, false);
   else if (add) APPLY(false, true);
@@ -374,8 +486,9 @@ int cnb_bn_fwd_eval(const cnb_bn_desc* d, const void* x, const void* residual, c
                                                               running_var, scale, shift, C, d->eps);
   CNB_TRY(check_launch("bn_eval_coeff"));
   int v = pick_vec(C, dtype_size(d->dtype), x, y, add ? residual : nullptr);
-  int64_t total = d->M * (C / v);
-  int gr = grid_for(total, kBnThreads);
+  BnGeom ga = bn_geom(d->M, C, v, kStreamWaves);
+  dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
+  const int64_t arows = ga.rows_per_split;
   if (relu && add) APPLY(true, true);
   else if (relu) APPLY(true, false);
   else if (add) APPLY(false, true);
@@ -401,31 +514,35 @@ int cnb_bn_bwd(const cnb_bn_desc* d, const void* x, const void* y, const void* d
   int v = pick_vec(C, dtype_size(d->dtype), x, dy, dx, relu ? y : nullptr);
   if (d_residual)
     while (v > 1 && (uintptr_t)d_residual % (v * dtype_size(d->dtype)) != 0) v >>= 1;
-  BnGeom g = bn_geom(M, C, v);
+  BnGeom g = bn_geom(M, C, v, kReduceWaves);
   float* part = (float*)workspace;
-  float* c1 = part + (size_t)3 * C * g.splits;
+  float* c1 = part + (size_t)2 * C * g.splits;
   float* c2 = c1 + C;
   float* c3 = c2 + C;
-  dim3 grid(g.cblocks, g.splits), block(g.cx, g.ry);
-  size_t smem = (size_t)g.ry * 2 * g.cx * v * sizeof(float);
-  if (relu)
-    CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_reduce_k<T, V, true><<<grid, block, smem, st>>>(
-                                     (const T*)x, (const T*)y, (const T*)dy, save_mean, part, M, C,
-                                     g.rows_per_split)));
-  else
-    CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_reduce_k<T, V, false><<<grid, block, smem, st>>>(
-                                     (const T*)x, (const T*)y, (const T*)dy, save_mean, part, M, C,
-                                     g.rows_per_split)));
-  CNB_TRY(check_launch("bn_bwd_reduce"));
-  bn_finalize_bwd_k<<<(unsigned)ceil_div(C, 128), 128, 0, st>>>(part, g.splits, M, C, gamma,
-                                                                save_rstd, dgamma, dbeta, c1, c2, c3);
-  CNB_TRY(check_launch("bn_finalize_bwd"));
-  int64_t total = M * (C / v);
-  int gr = grid_for(total, kBnThreads);
+  int* counter = bn_counters(g.cblocks);
+  CNB_REQUIRE(counter, CNB_ERR_CUDA, "cnb_bn_bwd: cannot allocate the arrival counters");
+  {
+    dim3 grid(g.cblocks, g.splits), block(g.cx, g.ry);
+    size_t smem = (size_t)g.ry * 2 * g.cx * v * sizeof(float);
+    if (smem < 4096) smem = 4096;  // the merge step re-uses it for 256 x 2 doubles
+    BnBwdFin fin{gamma, save_rstd, dgamma, dbeta, c1, c2, c3};
+    if (relu)
+      CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_reduce_k<T, V, true><<<grid, block, smem, st>>>(
+                                       (const T*)x, (const T*)y, (const T*)dy, save_mean, part, M, C,
+                                       g.rows_per_split, g.splits, counter, fin)));
+    else
+      CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_reduce_k<T, V, false><<<grid, block, smem, st>>>(
+                                       (const T*)x, (const T*)y, (const T*)dy, save_mean, part, M, C,
+                                       g.rows_per_split, g.splits, counter, fin)));
+    CNB_TRY(check_launch("bn_bwd_reduce"));
+  }
+  BnGeom ga = bn_geom(M, C, v, kStreamWaves);
+  dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
+  const int64_t arows = ga.rows_per_split;
 #define DX(R, D)                                                                                  \
-  CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_dx_k<T, V, R, D><<<gr, kBnThreads, 0, st>>>(               \
+  CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_dx_k<T, V, R, D><<<agrid, ablock, 0, st>>>(                \
                                    (const T*)x, (const T*)y, (const T*)dy, save_mean, c1, c2, c3, \
-                                   (T*)dx, (T*)d_residual, total, C / V)))
+                                   (T*)dx, (T*)d_residual, M, C, arows)))
   if (relu && d_residual) DX(true, true);
   else if (relu) DX(true, false);
   else if (d_residual) DX(false, true);

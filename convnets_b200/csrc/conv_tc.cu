@@ -132,8 +132,12 @@ struct FpropParams {
   uint8_t widx[kMaxTaps];
 };
 
-template <int BLOCK_N, int STAGES, bool IM2COL>
-__global__ void __launch_bounds__(kTcThreads, 1)
+// MINB = CTAs that should co-reside on one SM.  Layers with a short reduction loop (1x1 convs with
+// few input channels: one or two k-blocks per tile) are latency-bound per CTA — load, 4..8 MMAs,
+// epilogue, store, with nothing to overlap — so they run a 2-stage ring with 2..3 CTAs per SM and
+// let the CTAs overlap each other; deep loops (3x3, wide 1x1) keep a deep ring and one CTA per SM.
+template <int BLOCK_N, int STAGES, bool IM2COL, int MINB>
+__global__ void __launch_bounds__(kTcThreads, MINB)
 conv_fprop_tc_k(const __grid_constant__ FpropParams p) {
   constexpr int B_TILE_BYTES = BLOCK_N * TILE_K * 2;
   constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
@@ -540,12 +544,12 @@ struct FpropLaunch {
   bool tiled2d;                  // pure GEMM: A is the [M, C] matrix itself
 };
 
-template <int BLOCK_N, int STAGES, bool IM2COL>
+template <int BLOCK_N, int STAGES, bool IM2COL, int MINB>
 static int launch_fprop_inst(const FpropParams& prm, int grid, cudaStream_t st) {
   constexpr int STAGE_BYTES = A_TILE_BYTES + BLOCK_N * TILE_K * 2;
   constexpr size_t smem = (size_t)STAGES * STAGE_BYTES + (2 * STAGES + 1) * 8 + 16 + 1024;
   static bool attr_done = false;
-  auto kern = conv_fprop_tc_k<BLOCK_N, STAGES, IM2COL>;
+  auto kern = conv_fprop_tc_k<BLOCK_N, STAGES, IM2COL, MINB>;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cudaFuncSetAttribute(fprop): %s",
@@ -603,14 +607,25 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
   const int64_t grid64 = ceil_div(M, TILE_M) * prm.n_tiles;
   CNB_REQUIRE(grid64 < (1ll << 31), CNB_ERR_UNSUPPORTED, "conv_tc: grid too large");
   const int grid = (int)grid64;
+  const bool shallow = prm.num_taps * prm.num_cblk <= 4;
   if (L.tiled2d) {
-    if (BLOCK_N == 64) return launch_fprop_inst<64, 6, false>(prm, grid, st);
-    if (BLOCK_N == 128) return launch_fprop_inst<128, 5, false>(prm, grid, st);
-    return launch_fprop_inst<256, 4, false>(prm, grid, st);
+    if (shallow) {
+      if (BLOCK_N == 64) return launch_fprop_inst<64, 2, false, 3>(prm, grid, st);
+      if (BLOCK_N == 128) return launch_fprop_inst<128, 2, false, 3>(prm, grid, st);
+      return launch_fprop_inst<256, 2, false, 2>(prm, grid, st);
+    }
+    if (BLOCK_N == 64) return launch_fprop_inst<64, 6, false, 1>(prm, grid, st);
+    if (BLOCK_N == 128) return launch_fprop_inst<128, 5, false, 1>(prm, grid, st);
+    return launch_fprop_inst<256, 4, false, 1>(prm, grid, st);
   }
-  if (BLOCK_N == 64) return launch_fprop_inst<64, 6, true>(prm, grid, st);
-  if (BLOCK_N == 128) return launch_fprop_inst<128, 5, true>(prm, grid, st);
-  return launch_fprop_inst<256, 4, true>(prm, grid, st);
+  if (shallow) {
+    if (BLOCK_N == 64) return launch_fprop_inst<64, 2, true, 3>(prm, grid, st);
+    if (BLOCK_N == 128) return launch_fprop_inst<128, 2, true, 3>(prm, grid, st);
+    return launch_fprop_inst<256, 2, true, 2>(prm, grid, st);
+  }
+  if (BLOCK_N == 64) return launch_fprop_inst<64, 6, true, 1>(prm, grid, st);
+  if (BLOCK_N == 128) return launch_fprop_inst<128, 5, true, 1>(prm, grid, st);
+  return launch_fprop_inst<256, 4, true, 1>(prm, grid, st);
 }
 
 static bool corners_ok(int v) { return v >= -128 && v <= 127; }

@@ -111,6 +111,45 @@ __global__ void nchw_to_nhwc_k(const float* __restrict__ src, T* __restrict__ ds
   }
 }
 
+// Explicit im2col of the fp32 NCHW network input: dst[m][(r*S + s)*C + c] = x[n][c][h][w] with
+// m = (n*P + i)*Q + j, h = i*sh - ph + r*dh, w = j*sw - pw + s*dw; zero for padding taps and for
+// the alignment columns >= R*S*C.  One thread writes one 16-byte column vector.
+struct Im2colP {
+  int N, C, H, W, R, S, P, Q, sh, sw, ph, pw, dh, dw, Kd;
+};
+template <typename T, int V>
+__global__ void im2col_nchw_k(const float* __restrict__ src, T* __restrict__ dst, Im2colP p,
+                              int64_t total_vec) {
+  const int kv = p.Kd / V;
+  const int RSC = p.R * p.S * p.C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int cv = (int)(i % kv);
+    const int64_t m = i / kv;
+    const int j = (int)(m % p.Q);
+    const int64_t t = m / p.Q;
+    const int ii = (int)(t % p.P);
+    const int n = (int)(t / p.P);
+    Pack<T, V> o;
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+      const int col = cv * V + e;
+      float v = 0.f;
+      if (col < RSC) {
+        const int c = col % p.C;
+        const int rs = col / p.C;
+        const int s_ = rs % p.S, r = rs / p.S;
+        const int h = ii * p.sh - p.ph + r * p.dh;
+        const int w = j * p.sw - p.pw + s_ * p.dw;
+        if (h >= 0 && h < p.H && w >= 0 && w < p.W)
+          v = __ldg(src + (((int64_t)n * p.C + c) * p.H + h) * p.W + w);
+      }
+      o.v[e] = from_f<T>(v);
+    }
+    st_pack<T, V>(dst + i * V, o);
+  }
+}
+
 // ------------------------------------------------------------------ channel shuffle / slab copy
 // y[m, j*g + i] = x[m, i*(C/g) + j]; one thread per output element pair is fine: rows are short
 // and both sides stay within one row (L1/L2 absorb the permutation), traffic = 2 * numel.
@@ -458,6 +497,32 @@ int cnb_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t 
   size_t smem = (size_t)C * 33 * sizeof(float);
   CNB_DISPATCH_T(dtype, (nchw_to_nhwc_k<T><<<grid, 256, smem, (cudaStream_t)stream>>>(src, (T*)dst, C, C_dst, HW)));
   return check_launch("nchw_to_nhwc");
+}
+
+int cnb_im2col_nchw(const cnb_conv_desc* d, const float* src, void* dst, int32_t K_dst,
+                    void* stream) {
+  CNB_REQUIRE(d && src && dst, CNB_ERR_INVALID, "cnb_im2col_nchw: null pointer");
+  CNB_REQUIRE(d->N > 0 && d->H > 0 && d->W > 0 && d->C > 0 && d->R > 0 && d->S > 0 &&
+                  d->stride_h > 0 && d->stride_w > 0 && d->dil_h > 0 && d->dil_w > 0 &&
+                  d->pad_h >= 0 && d->pad_w >= 0 && valid_dtype(d->dtype),
+              CNB_ERR_INVALID, "cnb_im2col_nchw: bad descriptor");
+  int P, Q;
+  conv_out_dims(*d, P, Q);
+  CNB_REQUIRE(P > 0 && Q > 0, CNB_ERR_INVALID, "cnb_im2col_nchw: empty output");
+  const int v = (int)(16 / dtype_size(d->dtype));
+  CNB_REQUIRE(K_dst >= d->R * d->S * d->C && K_dst % v == 0 && (uintptr_t)dst % 16 == 0,
+              CNB_ERR_INVALID, "cnb_im2col_nchw: K_dst=%d must be >= R*S*C=%d, a multiple of %d, dst 16B-aligned",
+              K_dst, d->R * d->S * d->C, v);
+  Im2colP p{d->N, d->C, d->H, d->W, d->R, d->S, P, Q, d->stride_h, d->stride_w, d->pad_h, d->pad_w,
+            d->dil_h, d->dil_w, K_dst};
+  const int64_t total = (int64_t)d->N * P * Q * (K_dst / v);
+  if (d->dtype == CNB_BF16)
+    im2col_nchw_k<bf16, 8><<<grid_for(total, kThreads, 16), kThreads, 0, (cudaStream_t)stream>>>(
+        src, (bf16*)dst, p, total);
+  else
+    im2col_nchw_k<float, 4><<<grid_for(total, kThreads, 16), kThreads, 0, (cudaStream_t)stream>>>(
+        src, (float*)dst, p, total);
+  return check_launch("im2col_nchw");
 }
 
 int cnb_channel_shuffle(const void* x, void* y, int64_t M, int32_t C, int32_t groups, int dtype,

@@ -192,6 +192,72 @@ def conv2d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, wpac
                            int(groups), int(algo))
 
 
+class _InputConvFn(torch.autograd.Function):
+    """First layer of a network on the tensor-core path: explicit im2col of the fp32 NCHW batch
+    (cnb_im2col_nchw) followed by a [N*P*Q, Kd] x [Kd, K] GEMM through cnb_conv2d_fwd with a 1x1
+    descriptor.  The im2col matrix is kept for the weight gradient; the input gets no gradient."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride, padding, dilation, dtype):
+        _cuda(x, weight, bias)
+        lib = _L.load()
+        if x.dtype != torch.float32 or not x.is_contiguous():
+            x = x.float().contiguous()
+        n, c, h, w = x.shape
+        k, cw, r, s = weight.shape
+        if cw != c:
+            raise RuntimeError(f"expected input with {cw} channels, got {c}")
+        code = _L.CNB_BF16 if dtype == torch.bfloat16 else _L.CNB_F32
+        d0 = _L.ConvDesc(n, h, w, c, k, r, s, stride[0], stride[1], padding[0], padding[1],
+                         dilation[0], dilation[1], 1, code, 0, _L.CNB_ALGO_AUTO)
+        P, Q = C.c_int32(), C.c_int32()
+        _L.check(lib.cnb_conv2d_out_dims(C.byref(d0), C.byref(P), C.byref(Q)), "cnb_conv2d_out_dims")
+        P, Q = P.value, Q.value
+        rsc = r * s * c
+        kd = (rsc + 7) // 8 * 8
+        col = _empty_nhwc(n, kd, P, Q, dtype, x.device)
+        _L.check(lib.cnb_im2col_nchw(C.byref(d0), _p(x), _p(col), kd, _stream()), "cnb_im2col_nchw")
+        # weight [K, C, R, S] (any layout) -> [K, (r, s, c)] zero-padded to kd columns
+        wcol = torch.zeros((k, kd), dtype=torch.float32, device=x.device)
+        wcol[:, :rsc] = weight.detach().permute(0, 2, 3, 1).reshape(k, rsc)
+        wcol = wcol.to(dtype).view(k, kd, 1, 1)
+        flags = _L.CNB_CONV_BIAS if bias is not None else 0
+        d1 = _L.ConvDesc(n, P, Q, kd, k, 1, 1, 1, 1, 0, 0, 1, 1, 1, code, flags, _L.CNB_ALGO_AUTO)
+        y = _empty_nhwc(n, k, P, Q, dtype, x.device)
+        ws = _workspace(lib.cnb_conv2d_workspace_bytes(C.byref(d1), _L.CNB_FWD), x.device)
+        b32 = None if bias is None else bias.detach().float().contiguous()
+        _L.check(lib.cnb_conv2d_fwd(C.byref(d1), _p(col), _p(wcol), _p(b32), _p(y), _p(ws), ws.numel(),
+                                    _stream()), "cnb_conv2d_fwd(input)")
+        ctx.save_for_backward(col)
+        ctx.desc = d1
+        ctx.geom = (k, c, r, s, rsc, kd)
+        ctx.has_bias = bias is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _L.load()
+        (col,) = ctx.saved_tensors
+        d = ctx.desc
+        k, c, r, s, rsc, kd = ctx.geom
+        dy = _nhwc(dy)
+        if dy.dtype != col.dtype:
+            dy = dy.to(col.dtype)
+        dwc = torch.empty((k, kd), dtype=torch.float32, device=col.device)
+        db = torch.empty(k, dtype=torch.float32, device=col.device) if ctx.has_bias else None
+        ws = _workspace(lib.cnb_conv2d_workspace_bytes(C.byref(d), _L.CNB_WGRAD), col.device)
+        _L.check(lib.cnb_conv2d_wgrad(C.byref(d), _p(col), _p(dy), _p(dwc), _p(db), _p(ws), ws.numel(),
+                                      _stream()), "cnb_conv2d_wgrad(input)")
+        dw = dwc[:, :rsc].view(k, r, s, c).permute(0, 3, 1, 2)
+        return None, dw, db, None, None, None, None
+
+
+def conv2d_input(x, weight, bias=None, stride=1, padding=0, dilation=1, dtype=torch.bfloat16):
+    """The network's first convolution applied to the fp32 NCHW batch (reference
+    src/basemodel.py:185-188 feeds `self(inputs)` with it); see _InputConvFn."""
+    return _InputConvFn.apply(x, weight, bias, _pair(stride), _pair(padding), _pair(dilation), dtype)
+
+
 def conv2d_uses_tc(x_shape, w_shape, stride, padding, dilation, groups, dtype, direction) -> bool:
     """Which path a conv would take: True = tcgen05 implicit GEMM, False = CUDA cores."""
     code = _L.CNB_BF16 if dtype == torch.bfloat16 else _L.CNB_F32

@@ -36,15 +36,16 @@ class Conv2d(nn.Conv2d):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if self.padding_mode != "zeros" or isinstance(self.padding, str):
             raise NotImplementedError("convnets_b200.Conv2d supports integer zero padding only")
-        c_dst = None
         if self.cast_input and self.compute_dtype is not None and not x.requires_grad:
-            # network entry: fp32 NCHW batch -> compute dtype NHWC; an RGB stem is zero-padded to 8
-            # channels so that it qualifies for the tensor-core path (16-byte TMA rows)
+            # network entry: fp32 NCHW batch -> compute dtype NHWC.  A stem whose channel count
+            # cannot feed the tensor-core path (RGB: 16-byte TMA rows need C % 8 == 0) goes through
+            # an explicit im2col + GEMM instead of the CUDA-core kernel.
             if self.compute_dtype == torch.bfloat16 and self.groups == 1 and x.shape[1] % 8:
-                c_dst = (x.shape[1] + 7) // 8 * 8
-            x = F_.to_nhwc(x, self.compute_dtype, c_dst)
+                return F_.conv2d_input(x, self.weight, self.bias, self.stride, self.padding,
+                                       self.dilation, self.compute_dtype)
+            x = F_.to_nhwc(x, self.compute_dtype)
         return F_.conv2d(x, self.weight, self.bias, self.stride, self.padding, self.dilation,
-                         self.groups, wpack=self._packed(x.dtype, c_dst), algo=self.algo)
+                         self.groups, wpack=self._packed(x.dtype), algo=self.algo)
 
 
 class BatchNorm2d(nn.BatchNorm2d):

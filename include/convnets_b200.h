@@ -171,6 +171,13 @@ int cnb_copy_channels(const void* src, int32_t src_C, int32_t src_off, void* dst
  * tensor-core path, whose TMA rows must be multiples of 16 bytes) */
 int cnb_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t H, int32_t W,
                      int32_t C_dst, int dtype, void* stream);
+/* explicit im2col of the network input for a first layer whose channel count cannot feed the
+ * tensor-core path (RGB stems: reference src/resnet.py:66 7x7 s2; src/vggnet.py 3x3; ...):
+ * src fp32 NCHW [N,C,H,W] -> dst `d->dtype` [N*P*Q, K_dst], column (r*S + s)*C + c, zero for padding
+ * taps and for columns >= R*S*C.  The conv then runs as cnb_conv2d_{fwd,wgrad} with a 1x1
+ * descriptor over C = K_dst "channels" (no data-grad: the network input needs none). */
+int cnb_im2col_nchw(const cnb_conv_desc* d, const float* src, void* dst, int32_t K_dst,
+                    void* stream);
 /* element-wise precision conversion (fp32 master weights -> bf16 operand copy, etc.) */
 int cnb_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n, void* stream);
 

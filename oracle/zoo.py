@@ -22,18 +22,27 @@ class Net:
     """Execution context: parameters/buffers by state_dict key, train/eval mode, and the BN
     running-stat updates produced by a training forward."""
 
-    def __init__(self, sd: Dict[str, torch.Tensor], training: bool = True):
+    def __init__(self, sd: Dict[str, torch.Tensor], training: bool = True, storage=None):
         self.sd = sd
         self.training = training
+        self.storage = storage  # None = exact; torch.bfloat16 = model the library's bf16 mode
         self.new_buffers: Dict[str, torch.Tensor] = {}
+
+    def q(self, t):
+        """Storage rounding of the library's bf16 mode: feature maps and the conv operand copy of
+        the weights live in bf16, arithmetic and accumulation are wider.  Value-only (the gradient
+        passes straight through), so the oracle stays differentiable."""
+        if self.storage is None:
+            return t
+        return t + (t.detach().to(self.storage).to(t.dtype) - t.detach())
 
     def has(self, key: str) -> bool:
         return key in self.sd
 
     # nn.Conv2d (reference src/basemodel.py:966-997): bias present iff batch_norm=False
     def conv(self, key, x, stride=1, padding=0, dilation=1, groups=1):
-        return F.conv2d(x, self.sd[key + ".weight"], self.sd.get(key + ".bias"), stride, padding,
-                        dilation, groups)
+        return self.q(F.conv2d(x, self.q(self.sd[key + ".weight"]), self.sd.get(key + ".bias"),
+                               stride, padding, dilation, groups))
 
     # nn.BatchNorm2d (reference src/basemodel.py:1008,1061)
     def bn(self, key, x):
@@ -50,11 +59,16 @@ class Net:
 
     # conv2d_block (reference src/basemodel.py:999-1015): Sequential(conv[, bn][, relu]) with
     # integer child names 0, 1, 2
-    def block(self, key, x, activation=True, **conv_kw):
+    def block(self, key, x, activation=True, residual=None, **conv_kw):
+        """`residual`: the block's output is the last term of `output += identity; relu`
+        (src/resnet.py:151-154).  In bf16 mode bn(x) is materialised in the storage dtype before
+        the add, as the reference's module chain would do, and the sum is rounded after the ReLU."""
         y = self.conv(key + ".0", x, **conv_kw)
         if self.has(key + ".1.weight"):
             y = self.bn(key + ".1", y)
-        return F.relu(y) if activation else y
+        if residual is not None:
+            return self.q(F.relu(self.q(y) + residual))
+        return self.q(F.relu(y) if activation else y)
 
     def linear(self, key, x):
         return F.linear(x, self.sd[key + ".weight"], self.sd.get(key + ".bias"))
@@ -70,7 +84,7 @@ _RESNET = {  # kind -> (bottleneck, blocks per stage)   src/resnet.py:29-36
 
 def resnet(net: Net, x, kind="50"):
     bottleneck, depths = _RESNET[str(kind)]
-    x = net.block("features.0", x, stride=2, padding=3)            # 7x7 s2 stem, src/resnet.py:66
+    x = net.block("features.0", net.q(x), stride=2, padding=3)     # 7x7 s2 stem, src/resnet.py:66
     x = F.max_pool2d(x, 3, 2, 1)                                   # src/resnet.py:67
     idx = 2
     for stage, depth in enumerate(depths):
@@ -78,18 +92,17 @@ def resnet(net: Net, x, kind="50"):
             stride = 2 if (i == 0 and stage > 0) else 1           # src/resnet.py:70-79
             p = f"features.{idx}"
             identity = x
+            if net.has(p + ".dim_synch.0.weight"):                 # src/resnet.py:90-93
+                identity = net.block(p + ".dim_synch", x, activation=False, stride=stride)
             if bottleneck:                                         # src/resnet.py:158-196
                 b = p + ".res_bottleneck"
                 y = net.block(b + ".0", x)
                 y = net.block(b + ".1", y, stride=stride, padding=1)
-                y = net.block(b + ".2", y, activation=False)
+                x = net.block(b + ".2", y, residual=identity)      # += identity; relu  (:191-194)
             else:                                                  # src/resnet.py:119-156
                 b = p + ".res_block"
                 y = net.block(b + ".0", x, stride=stride, padding=1)
-                y = net.block(b + ".1", y, activation=False, padding=1)
-            if net.has(p + ".dim_synch.0.weight"):                 # src/resnet.py:90-93
-                identity = net.block(p + ".dim_synch", x, activation=False, stride=stride)
-            x = F.relu(y + identity)
+                x = net.block(b + ".1", y, residual=identity, padding=1)
             idx += 1
     x = F.adaptive_avg_pool2d(x, 1)                                # src/resnet.py:81
     x = torch.flatten(x, 1)
@@ -99,8 +112,8 @@ def resnet(net: Net, x, kind="50"):
 MODELS = {"ResNet": resnet}
 
 
-def forward(name: str, sd, x, kind, training=True):
-    net = Net(sd, training)
+def forward(name: str, sd, x, kind, training=True, storage=None):
+    net = Net(sd, training, storage)
     return MODELS[name](net, x, kind), net
 
 
@@ -110,11 +123,11 @@ def is_param(key: str) -> bool:
     return not key.endswith(("running_mean", "running_var", "num_batches_tracked"))
 
 
-def loss_and_grads(name, sd, x, y, kind):
+def loss_and_grads(name, sd, x, y, kind, storage=None):
     """CrossEntropyLoss(reduction='sum') (src/basemodel.py:46) and its gradients with respect to
     every parameter.  Returns (logits, loss, grads by key, new BN buffers)."""
     leaf = {k: (v.detach().clone().requires_grad_(True) if is_param(k) else v) for k, v in sd.items()}
-    logits, net = forward(name, leaf, x, kind, training=True)
+    logits, net = forward(name, leaf, x, kind, training=True, storage=storage)
     loss = F.cross_entropy(logits, y, reduction="sum")
     keys = [k for k in leaf if is_param(k)]
     grads = torch.autograd.grad(loss, [leaf[k] for k in keys], allow_unused=True)

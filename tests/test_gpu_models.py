@@ -7,8 +7,14 @@ the fp64 oracle next to the noise floor of the reference's own fp32 execution on
 (whole-network gradients are conditioning-limited, Appendix D), and pass when
 ours <= max(tolerance, 2 x noise floor).
   fp32-IO mode : logits rel-L2 <= 1e-4
-  bf16 mode    : logits rel-L2 <= 3e-2 over a whole network (each LAYER meets 1e-2 on identical
-                 inputs, tests/test_gpu_conv.py and test_gpu_ops.py; rounding compounds over depth)
+  bf16 mode    : logits rel-L2 <= 2e-2 against the fp64 oracle run with the library's storage
+                 rounding (bf16 feature maps / operand weights, Net.q in oracle/zoo.py) — the same
+                 "inputs pre-rounded, only accumulation differs" rule as the per-layer tests;
+                 against the un-rounded fp64 oracle the whole-network figure is printed and only
+                 bounded loosely (rounding compounds over depth; each LAYER meets 1e-2 on
+                 identical inputs in tests/test_gpu_conv.py and test_gpu_ops.py).  2e-2 rather than
+                 the per-layer 1e-2: a 1-ulp bf16 rounding flip in one layer (fp32 vs fp64
+                 accumulation) is an input perturbation for every later layer.
 """
 import pytest
 import torch
@@ -18,7 +24,7 @@ from oracle import zoo as Z
 
 CASES = [
     # family, kind, hw, batch
-    ("ResNet", "18", 32, 8),
+    ("ResNet", "18", 64, 16),
     ("ResNet", "50", 64, 4),
 ]
 
@@ -50,6 +56,10 @@ def test_train_step_parity(family, kind, hw, batch, dtype):
     sd64 = {k: (v.double() if v.is_floating_point() else v) for k, v in sd.items()}
     lg64, loss64, g64, buf64 = Z.loss_and_grads(family, sd64, x.double(), y, kind)
     lg32, loss32, g32, _ = Z.loss_and_grads(family, sd, x, y, kind)
+    if dtype == torch.bfloat16:
+        exact = lg64
+        lg64, loss64, g64, buf64 = Z.loss_and_grads(family, sd64, x.double(), y, kind,
+                                                    storage=torch.bfloat16)
 
     n0 = L.launch_count()
     model.train()
@@ -59,9 +69,13 @@ def test_train_step_parity(family, kind, hw, batch, dtype):
     torch.cuda.synchronize()
     assert L.launch_count() > n0, "the CUDA library did not run"
 
-    tol = 1e-4 if dtype == torch.float32 else 3e-2
+    tol = 1e-4 if dtype == torch.float32 else 2e-2
     e_logits = O.rel_l2(out, lg64)
     assert e_logits <= tol, f"logits rel-L2 {e_logits}"
+    if dtype == torch.bfloat16:
+        e_exact = O.rel_l2(out, exact)
+        print(f"bf16 logits vs un-rounded fp64 oracle: {e_exact:.3e}")
+        assert e_exact <= 0.15
     assert abs(loss.item() - loss64.item()) <= tol * max(1.0, abs(loss64.item()))
     # BatchNorm running statistics and step counters
     new = model.state_dict()

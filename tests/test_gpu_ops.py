@@ -277,3 +277,31 @@ def test_errors_are_loud():
     assert L.cnb_conv2d_uses_tc(C.byref(d), 0) == -2
     with pytest.raises(RuntimeError):
         F_().relu(torch.randn(4))  # CPU tensor: no fallback
+
+
+# ------------------------------------------------------------------ network-input convolution
+@pytest.mark.parametrize("case", [
+    dict(n=3, c=3, hw=33, k=64, r=7, stride=2, pad=3, bias=False),   # ResNet-family stem
+    dict(n=2, c=3, hw=18, k=24, r=3, stride=1, pad=1, bias=True),    # VGG first layer, no BN
+    dict(n=2, c=1, hw=12, k=16, r=5, stride=1, pad=2, bias=False),   # single-channel input
+])
+def test_conv2d_input_im2col(case):
+    """cnb_im2col_nchw + 1x1-descriptor GEMM == conv2d of the fp32 NCHW batch (bf16 mode)."""
+    torch.manual_seed(5)
+    n, c, hw, k, r = case["n"], case["c"], case["hw"], case["k"], case["r"]
+    x = torch.randn(n, c, hw, hw)
+    w = torch.randn(k, c, r, r) / (c * r * r) ** 0.5
+    b = torch.randn(k) if case["bias"] else None
+    xq, wq = x.bfloat16(), w.bfloat16()
+    y_ref = O.conv2d(xq, wq, b, case["stride"], case["pad"])
+    dy = torch.randn(y_ref.shape).bfloat16()
+    _, dw_ref, db_ref = O.conv2d_grads(xq, wq, b, dy, case["stride"], case["pad"])
+    wd = w.cuda().contiguous(memory_format=CL).requires_grad_(True)
+    bd = None if b is None else b.cuda().requires_grad_(True)
+    y = F_().conv2d_input(x.cuda(), wd, bd, case["stride"], case["pad"], 1, torch.bfloat16)
+    assert y.dtype == torch.bfloat16 and y.is_contiguous(memory_format=CL)
+    y.backward(dy.cuda().contiguous(memory_format=CL))
+    assert O.rel_l2(y, y_ref) <= 1e-2
+    assert O.rel_l2(wd.grad, dw_ref) <= 1e-2
+    if b is not None:
+        assert O.rel_l2(bd.grad, db_ref) <= 1e-2
