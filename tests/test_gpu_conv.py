@@ -38,6 +38,11 @@ TC_CASES = [
     c(4, 512, 7, 7, 512, 3, pad=1),                   # deep K loop (72 k-blocks), NT=256 wgrad
     c(8, 64, 56, 56, 64, 3, pad=1),                   # many m-tiles, split-K wgrad
     c(8, 256, 28, 28, 128, 1),                        # wgrad NT=256 x 2 cout tiles? (K=128: 1 tile)
+    c(4, 512, 2, 2, 2048, 1),                         # M = 16: one ragged m-tile (ResNet-50 @64x64 tail)
+    c(4, 2048, 2, 2, 512, 1),                         # M = 16, 32 k-blocks
+    c(4, 512, 2, 2, 512, 3, pad=1),                   # 3x3 on a 2x2 map: most taps are padding
+    c(4, 512, 4, 4, 512, 3, pad=1, stride=2),         # strided 3x3, 4x4 -> 2x2
+    c(4, 1024, 4, 4, 2048, 1, stride=2),              # strided projection, 4x4 -> 2x2
 ]
 
 # CUDA-core cases: fp32-IO mode, grouped, tiny channel counts, stems
