@@ -1,0 +1,90 @@
+"""CPU: the C-ABI library loads and exports exactly what include/convnets_b200.h declares; the
+ctypes table in convnets_b200/lib.py matches the header; descriptor validation (no compute) works
+without a GPU; the product path refuses to run without CUDA instead of falling back."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "convnets_b200.h")
+
+
+def _declared():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return re.findall(r"\b(cnb_[a-z0-9_]+)\s*\(", src)
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from convnets_b200 import build, lib as L
+    build.build()
+    return L
+
+
+def test_header_matches_ctypes_table(lib):
+    names = _declared()
+    assert len(names) == len(set(names)) and len(names) >= 30
+    assert set(names) == set(lib.SIGNATURES), set(names) ^ set(lib.SIGNATURES)
+
+
+def test_shared_library_exports_every_declared_symbol(lib):
+    out = subprocess.run(["nm", "-D", "--defined-only", lib.LIB_PATH], capture_output=True, text=True,
+                         check=True).stdout
+    exported = set(re.findall(r" T (cnb_[a-z0-9_]+)", out))
+    assert set(_declared()) <= exported, set(_declared()) - exported
+    h = lib.load()
+    for name in _declared():
+        assert getattr(h._cdll, name) is not None
+    assert "sm_100a" in lib.version()
+
+
+def test_library_is_sm100a_only(lib):
+    out = subprocess.run(["cuobjdump", "-lelf", lib.LIB_PATH], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_\d+a?", out))
+    assert archs == {"sm_100a"}, archs
+
+
+def test_descriptor_validation_without_a_gpu(lib):
+    h = lib.load()
+    d = lib.ConvDesc(2, 56, 56, 64, 128, 3, 3, 2, 2, 1, 1, 1, 1, 1, lib.CNB_BF16, 0, lib.CNB_ALGO_AUTO)
+    P, Q = C.c_int32(), C.c_int32()
+    assert h.cnb_conv2d_out_dims(C.byref(d), C.byref(P), C.byref(Q)) == 0
+    assert (P.value, Q.value) == (28, 28)
+    assert h.cnb_conv2d_uses_tc(C.byref(d), lib.CNB_FWD) == 1
+    d.groups = 32  # grouped -> CUDA cores
+    assert h.cnb_conv2d_uses_tc(C.byref(d), lib.CNB_FWD) == 0
+    d.groups = 3   # 64 % 3 != 0 -> invalid, with torch's wording
+    assert h.cnb_conv2d_out_dims(C.byref(d), C.byref(P), C.byref(Q)) == -1
+    assert "divisible by groups" in lib.last_error()
+    d.groups, d.R, d.H = 1, 9, 4  # kernel larger than padded input
+    assert h.cnb_conv2d_out_dims(C.byref(d), C.byref(P), C.byref(Q)) == -1
+    d2 = lib.ConvDesc(2, 8, 8, 64, 64, 3, 3, 1, 1, 1, 1, 1, 1, 32, lib.CNB_BF16, 0, lib.CNB_ALGO_TC)
+    assert h.cnb_conv2d_uses_tc(C.byref(d2), lib.CNB_FWD) == -2  # forced TC on a grouped conv
+
+
+def test_no_cpu_fallback():
+    if torch.cuda.is_available():
+        pytest.skip("CPU-only check")
+    from convnets_b200 import functional as F_
+    x = torch.randn(1, 8, 4, 4)
+    w = torch.randn(8, 8, 1, 1)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        F_.conv2d(x, w)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        F_.relu(x)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        F_.max_pool2d(x, 2)
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "convnets_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
