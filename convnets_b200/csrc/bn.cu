@@ -25,14 +25,18 @@ struct BnGeom {
   int64_t rows_per_split;
 };
 
-// `waves`: target resident CTAs per SM.  The reduction kernels use few, fat CTAs (their partials
-// are merged by the last CTA of each channel block); the streaming kernels use more.
-static BnGeom bn_geom(int64_t M, int C, int V, int waves) {
+// `waves`: target resident CTAs per SM.  `max_cx`: cap on the threads along channels.
+// Streaming kernels (apply, dx) use full 512-byte row segments (max_cx = 32) and many CTAs.
+// Reduction kernels use 128-byte row segments (max_cx = 8 -> at most 64 channels per CTA): their
+// partials are merged by the last CTA of each channel block, and that serial tail is proportional
+// to (CTAs per channel block) x (channels per CTA) / 256 threads — narrow channel blocks keep it
+// to a few microseconds where a 256-channel-wide CTA column spent ~70 us in it.
+static BnGeom bn_geom(int64_t M, int C, int V, int waves, int max_cx = 32) {
   BnGeom g;
   g.V = V;
   int cvs = C / V;
   int p = 1;
-  while (p * 2 <= cvs && p * 2 <= 32) p *= 2;
+  while (p * 2 <= cvs && p * 2 <= max_cx) p *= 2;
   g.cx = p;
   g.ry = kBnThreads / g.cx;
   g.cblocks = (int)ceil_div(cvs, g.cx);
@@ -50,7 +54,7 @@ static BnGeom bn_geom(int64_t M, int C, int V, int waves) {
 // Arrival counters for the "last CTA of a channel block merges the partials" step.  Library-owned,
 // zero-initialised once per device and left at zero by every kernel that uses them; each call
 // takes the next of kCounterSlots slots so that calls in flight on different streams do not share.
-constexpr int kCounterSlots = 64, kCountersPerSlot = 64;
+constexpr int kCounterSlots = 64, kCountersPerSlot = 1024;
 static int* bn_counters(int cblocks) {
   static int* base[64] = {nullptr};
   static std::atomic<unsigned> next{0};
@@ -131,11 +135,23 @@ __device__ __forceinline__ bool bn_block_merge(float (&s)[V], float (&q)[V], flo
   const int col = t % W, lane = t / W;
   const int c = cbase + col;
   double a = 0.0, b = 0.0;
-  if (c < C)
-    for (int sp = lane; sp < splits; sp += lanes) {
-      a += (double)__ldcg(part + ((int64_t)sp * 2 + 0) * C + c);
-      b += (double)__ldcg(part + ((int64_t)sp * 2 + 1) * C + c);
+  if (c < C) {
+    constexpr int MU = 8;  // independent L2 loads in flight per thread; summation order is fixed
+    for (int sp = lane; sp < splits; sp += lanes * MU) {
+      float va[MU], vb[MU];
+#pragma unroll
+      for (int u = 0; u < MU; ++u) {
+        const int si = sp + u * lanes;
+        va[u] = si < splits ? __ldcg(part + ((int64_t)si * 2 + 0) * C + c) : 0.f;
+        vb[u] = si < splits ? __ldcg(part + ((int64_t)si * 2 + 1) * C + c) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < MU; ++u) {
+        a += (double)va[u];
+        b += (double)vb[u];
+      }
     }
+  }
   __syncthreads();
   dred[(lane * 2 + 0) * W + col] = a;
   dred[(lane * 2 + 1) * W + col] = b;
@@ -391,7 +407,7 @@ bn_bwd_dx_k(const T* __restrict__ x, const T* __restrict__ y, const T* __restric
   }
 }
 
-constexpr int kReduceWaves = 4, kStreamWaves = 8;
+constexpr int kReduceWaves = 4, kStreamWaves = 8, kReduceCx = 8;
 static size_t bn_ws_bytes(int C) {
   // partials: splits <= min(2048, kReduceWaves*SMs) rows of 2*C floats, then 5*C coefficients
   int64_t splits = (int64_t)sm_count() * kReduceWaves;
@@ -435,7 +451,7 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
   const int C = d->C;
   const int64_t M = d->M;
   int v = pick_vec(C, dtype_size(d->dtype), x, y, add ? residual : nullptr);
-  BnGeom g = bn_geom(M, C, v, kReduceWaves);
+  BnGeom g = bn_geom(M, C, v, kReduceWaves, kReduceCx);
   float* part = (float*)workspace;
   float* scale = part + (size_t)2 * C * g.splits;
   float* shift = scale + C;
@@ -514,7 +530,7 @@ int cnb_bn_bwd(const cnb_bn_desc* d, const void* x, const void* y, const void* d
   int v = pick_vec(C, dtype_size(d->dtype), x, dy, dx, relu ? y : nullptr);
   if (d_residual)
     while (v > 1 && (uintptr_t)d_residual % (v * dtype_size(d->dtype)) != 0) v >>= 1;
-  BnGeom g = bn_geom(M, C, v, kReduceWaves);
+  BnGeom g = bn_geom(M, C, v, kReduceWaves, kReduceCx);
   float* part = (float*)workspace;
   float* c1 = part + (size_t)2 * C * g.splits;
   float* c2 = c1 + C;

@@ -21,6 +21,7 @@
 // warps 2..5 = epilogue (warp_id % 4 selects the TMEM lane quarter).  mbarrier full/empty rings
 // between producer and MMA; tcgen05.commit releases smem slots and signals the epilogue.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "sm100.cuh"
@@ -126,6 +127,7 @@ struct FpropParams {
   int num_cblk;     // ceil(C / 64)
   int num_taps;
   int n_tiles;      // ceil(Kout / BLOCK_N)
+  int num_tiles;    // m-tiles * n-tiles (persistent kernel)
   int Kout;
   int flags;
   int16_t off_h[kMaxTaps], off_w[kMaxTaps];
@@ -280,6 +282,190 @@ conv_fprop_tc_k(const __grid_constant__ FpropParams p) {
       tma_store_commit();
       tma_store_wait0();
     }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, TMEM_COLS);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Persistent variant: one CTA per SM walks the (m-tile, n-tile) list with a static stride.  The
+// TMA producer runs ahead across tile boundaries (the smem ring never drains), the accumulator is
+// double-buffered in TMEM (2 x BLOCK_N columns) and the epilogue of tile i — tcgen05.ld, bias /
+// ReLU, bf16 pack, swizzled staging, TMA store — overlaps the MMAs of tile i+1.  The per-tile fixed
+// costs of the one-tile-per-CTA kernel above (barrier init, TMEM alloc, descriptor prefetch,
+// pipeline fill, exposed epilogue) are paid once per SM instead of once per tile, which is what
+// the short-reduction layers (1x1 with few channels, 3x3 on 64 channels) were bound by.
+template <int BLOCK_N, int STAGES, bool IM2COL>
+__global__ void __launch_bounds__(kTcThreads, 1)
+conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
+  constexpr int B_TILE_BYTES = BLOCK_N * TILE_K * 2;
+  constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
+  constexpr int OUT_BYTES = TILE_M * BLOCK_N * 2;
+  constexpr uint32_t TMEM_COLS = 2 * BLOCK_N < 32 ? 32 : 2 * BLOCK_N;
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~(uintptr_t)1023);
+  uint8_t* stage_out = smem + STAGES * STAGE_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_out + OUT_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;   // [2]
+  uint64_t* tmem_empty_bar = tmem_full_bar + 2;   // [2]
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+
+  const int warp = threadIdx.x / 32;
+  const int lane = threadIdx.x % 32;
+  const int num_iters = p.num_taps * p.num_cblk;
+  const int num_tiles = p.num_tiles;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmA);
+    tma_prefetch_desc(&p.tmB);
+    tma_prefetch_desc(&p.tmD);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tmem_full_bar[b], 1);
+      mbar_init(&tmem_empty_bar[b], 128);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc(tmem_ptr, TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile / p.n_tiles) * TILE_M;
+        const int n0 = (tile % p.n_tiles) * BLOCK_N;
+        int bn = 0, bh = 0, bw = 0;
+        if (IM2COL) {
+          int j = m0 % p.outQ;
+          int t = m0 / p.outQ;
+          int i = t % p.outP;
+          bn = t / p.outP;
+          bh = p.lower_h + i * p.trav_h;
+          bw = p.lower_w + j * p.trav_w;
+        }
+        for (int tap = 0; tap < p.num_taps; ++tap) {
+          for (int cb = 0; cb < p.num_cblk; ++cb, ++it) {
+            const int s = it % STAGES;
+            const uint32_t use = it / STAGES;
+            mbar_wait(&empty_bar[s], (use & 1) ^ 1);
+            uint8_t* sa = smem + s * STAGE_BYTES;
+            uint8_t* sb = sa + A_TILE_BYTES;
+            mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+            if (IM2COL)
+              tma_load_im2col_4d(&p.tmA, &full_bar[s], sa, cb * TILE_K, bw, bh, bn,
+                                 (uint16_t)p.off_w[tap], (uint16_t)p.off_h[tap]);
+            else
+              tma_load_2d(&p.tmA, &full_bar[s], sa, cb * TILE_K, m0);
+            tma_load_3d(&p.tmB, &full_bar[s], sb, cb * TILE_K, (int)p.widx[tap], n0);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BLOCK_N, 0, 0);
+    uint32_t it = 0, lt = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+      const uint32_t buf = lt & 1;
+      mbar_wait(&tmem_empty_bar[buf], ((lt >> 1) & 1) ^ 1);  // epilogue has drained this buffer
+      tc_fence_after();
+      const uint32_t acc = tmem_base + buf * BLOCK_N;
+      for (int k_it = 0; k_it < num_iters; ++k_it, ++it) {
+        const int s = it % STAGES;
+        const uint32_t use = it / STAGES;
+        mbar_wait(&full_bar[s], use & 1);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t a_base = smem_u32(smem + s * STAGE_BYTES);
+          const uint32_t b_base = a_base + A_TILE_BYTES;
+#pragma unroll
+          for (int k = 0; k < TILE_K / 16; ++k) {
+            uint64_t da = make_smem_desc_sw128(a_base + k * 32, 0, 1024);
+            uint64_t db = make_smem_desc_sw128(b_base + k * 32, 0, 1024);
+            umma_bf16(acc, da, db, idesc, (k_it | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[s]);
+          if (k_it == num_iters - 1) umma_commit(&tmem_full_bar[buf]);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int quarter = warp % 4;
+    const int row = quarter * 32 + lane;
+    const bool storer = (warp == 2 && lane == 0);
+    uint32_t lt = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+      const int m0 = (tile / p.n_tiles) * TILE_M;
+      const int n0 = (tile % p.n_tiles) * BLOCK_N;
+      const uint32_t buf = lt & 1;
+      mbar_wait(&tmem_full_bar[buf], (lt >> 1) & 1);
+      tc_fence_after();
+      // the previous tile's TMA store must have finished READING the staging buffer
+      if (storer) tma_store_wait_read0();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll 1
+      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * BLOCK_N + (uint32_t)c0, v);
+        tmem_ld_wait();
+        uint8_t* box = stage_out + (c0 / 64) * (TILE_M * 128);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint32_t packed[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float f0 = __uint_as_float(v[j * 8 + e * 2 + 0]);
+            float f1 = __uint_as_float(v[j * 8 + e * 2 + 1]);
+            const int col = n0 + c0 + j * 8 + e * 2;
+            if (p.flags & CNB_CONV_BIAS) {
+              f0 += (col < p.Kout) ? p.bias[col] : 0.f;
+              f1 += (col + 1 < p.Kout) ? p.bias[col + 1] : 0.f;
+            }
+            if (p.flags & CNB_CONV_RELU) {
+              f0 = (f0 > 0.f || f0 != f0) ? f0 : 0.f;
+              f1 = (f1 > 0.f || f1 != f1) ? f1 : 0.f;
+            }
+            __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);
+            packed[e] = *reinterpret_cast<uint32_t*>(&h);
+          }
+          const int chunk = (c0 % 64) / 8 + j;
+          uint4* dst = reinterpret_cast<uint4*>(box + row * 128 + ((chunk ^ (row & 7)) * 16));
+          *dst = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+        }
+      }
+      // accumulator buffer fully read: hand it back to the MMA warp
+      tc_fence_before();
+      mbar_arrive(&tmem_empty_bar[buf]);
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (storer) {
+        for (int b = 0; b < BLOCK_N / 64; ++b) {
+          if (n0 + b * 64 < p.Kout)
+            tma_store_2d(&p.tmD, stage_out + b * (TILE_M * 128), n0 + b * 64, m0);
+        }
+        tma_store_commit();
+      }
+    }
+    if (storer) tma_store_wait0();
   }
   __syncthreads();
   if (warp == 1) {
@@ -560,6 +746,35 @@ static int launch_fprop_inst(const FpropParams& prm, int grid, cudaStream_t st) 
   return check_launch("conv_fprop_tc");
 }
 
+template <int BLOCK_N, int STAGES, bool IM2COL>
+static int launch_fprop_persist_inst(const FpropParams& prm, cudaStream_t st) {
+  constexpr int STAGE_BYTES = A_TILE_BYTES + BLOCK_N * TILE_K * 2;
+  constexpr size_t smem = (size_t)STAGES * STAGE_BYTES + (size_t)TILE_M * BLOCK_N * 2 +
+                          (2 * STAGES + 4) * 8 + 16 + 1024;
+  static_assert(smem <= 232448, "exceeds the 227 KB dynamic shared memory limit");
+  static bool attr_done = false;
+  auto kern = conv_fprop_tc_persist_k<BLOCK_N, STAGES, IM2COL>;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cudaFuncSetAttribute(fprop persistent): %s",
+                cudaGetErrorString(e));
+    attr_done = true;
+  }
+  const int grid = prm.num_tiles < sm_count() ? prm.num_tiles : sm_count();
+  kern<<<grid, kTcThreads, smem, st>>>(prm);
+  return check_launch("conv_fprop_tc_persist");
+}
+
+// CNB_CONV_PERSIST=0 selects the one-tile-per-CTA kernel (kept for A/B measurement only).
+static bool use_persistent() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("CNB_CONV_PERSIST");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
   CNB_TRY(load_driver_fns());
   FpropParams prm;
@@ -607,6 +822,17 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
   const int64_t grid64 = ceil_div(M, TILE_M) * prm.n_tiles;
   CNB_REQUIRE(grid64 < (1ll << 31), CNB_ERR_UNSUPPORTED, "conv_tc: grid too large");
   const int grid = (int)grid64;
+  prm.num_tiles = grid;
+  if (use_persistent()) {
+    if (L.tiled2d) {
+      if (BLOCK_N == 64) return launch_fprop_persist_inst<64, 8, false>(prm, st);
+      if (BLOCK_N == 128) return launch_fprop_persist_inst<128, 5, false>(prm, st);
+      return launch_fprop_persist_inst<256, 3, false>(prm, st);
+    }
+    if (BLOCK_N == 64) return launch_fprop_persist_inst<64, 8, true>(prm, st);
+    if (BLOCK_N == 128) return launch_fprop_persist_inst<128, 5, true>(prm, st);
+    return launch_fprop_persist_inst<256, 3, true>(prm, st);
+  }
   const bool shallow = prm.num_taps * prm.num_cblk <= 4;
   if (L.tiled2d) {
     if (shallow) {

@@ -17,7 +17,9 @@ struct PoolP {
 
 // PyTorch rule (aten/src/ATen/native/cuda/DilatedMaxPool2d.cu): scan the window row-major over
 // in-bounds positions only, take `val > max || isnan(val)`; index = h*W + w.
-template <typename T, int V>
+// K > 0: the window is at most K x K — all K*K loads are issued before the first compare so
+// that each thread keeps K*K independent 16-byte requests in flight; K == 0: runtime loops.
+template <typename T, int V, int K>
 __global__ void maxpool_fwd_k(const T* __restrict__ x, T* __restrict__ y, int32_t* __restrict__ idx,
                               PoolP p, int64_t total_vec) {
   const int Cv = p.C / V;
@@ -41,18 +43,42 @@ __global__ void maxpool_fwd_k(const T* __restrict__ x, T* __restrict__ y, int32_
       bi[j] = h0 * p.W + w0;
     }
     const T* base = x + (int64_t)n * p.H * p.W * p.C + cv * V;
-    for (int h = h0; h < h1; ++h)
-      for (int w = w0; w < w1; ++w) {
-        Pack<T, V> a = ld_pack<T, V>(base + ((int64_t)h * p.W + w) * p.C);
+    if (K > 0) {
+      Pack<T, V> a[K > 0 ? K * K : 1];
 #pragma unroll
-        for (int j = 0; j < V; ++j) {
-          float f = to_f(a.v[j]);
-          if (f > best[j] || f != f) {
-            best[j] = f;
-            bi[j] = h * p.W + w;
+      for (int dh = 0; dh < K; ++dh)
+#pragma unroll
+        for (int dw = 0; dw < K; ++dw)
+          if (h0 + dh < h1 && w0 + dw < w1)
+            a[dh * K + dw] = ld_pack<T, V>(base + ((int64_t)(h0 + dh) * p.W + w0 + dw) * p.C);
+#pragma unroll
+      for (int dh = 0; dh < K; ++dh)
+#pragma unroll
+        for (int dw = 0; dw < K; ++dw)
+          if (h0 + dh < h1 && w0 + dw < w1) {
+#pragma unroll
+            for (int j = 0; j < V; ++j) {
+              float f = to_f(a[dh * K + dw].v[j]);
+              if (f > best[j] || f != f) {
+                best[j] = f;
+                bi[j] = (h0 + dh) * p.W + w0 + dw;
+              }
+            }
+          }
+    } else {
+      for (int h = h0; h < h1; ++h)
+        for (int w = w0; w < w1; ++w) {
+          Pack<T, V> a = ld_pack<T, V>(base + ((int64_t)h * p.W + w) * p.C);
+#pragma unroll
+          for (int j = 0; j < V; ++j) {
+            float f = to_f(a.v[j]);
+            if (f > best[j] || f != f) {
+              best[j] = f;
+              bi[j] = h * p.W + w;
+            }
           }
         }
-      }
+    }
     Pack<T, V> o;
     Pack<int32_t, V> oi;
 #pragma unroll
@@ -66,7 +92,9 @@ __global__ void maxpool_fwd_k(const T* __restrict__ x, T* __restrict__ y, int32_
 }
 
 // dx[n,h,w,c] = sum over output windows containing (h,w) of dy * (idx == h*W+w)
-template <typename T, int V>
+// NW > 0: at most NW x NW output windows contain an input pixel (NW = ceil(k / stride)); their
+// index / gradient loads are all issued before the compares.  NW == 0: runtime loops.
+template <typename T, int V, int NW>
 __global__ void maxpool_bwd_k(const T* __restrict__ dy, const int32_t* __restrict__ idx,
                               T* __restrict__ dx, PoolP p, int64_t total_vec) {
   const int Cv = p.C / V;
@@ -89,15 +117,38 @@ __global__ void maxpool_bwd_k(const T* __restrict__ dy, const int32_t* __restric
     float acc[V];
 #pragma unroll
     for (int j = 0; j < V; ++j) acc[j] = 0.f;
-    for (int oh = oh_lo; oh <= oh_hi; ++oh)
-      for (int ow = ow_lo; ow <= ow_hi; ++ow) {
-        int64_t o = (((int64_t)n * p.P + oh) * p.Q + ow) * p.C + cv * V;
-        Pack<int32_t, V> ii = ld_pack<int32_t, V>(idx + o);
-        Pack<T, V> g = ld_pack<T, V>(dy + o);
+    if (NW > 0) {
+      Pack<int32_t, V> ii[NW > 0 ? NW * NW : 1];
+      Pack<T, V> g[NW > 0 ? NW * NW : 1];
 #pragma unroll
-        for (int j = 0; j < V; ++j)
-          if (ii.v[j] == me) acc[j] += to_f(g.v[j]);
-      }
+      for (int a = 0; a < NW; ++a)
+#pragma unroll
+        for (int b = 0; b < NW; ++b)
+          if (oh_lo + a <= oh_hi && ow_lo + b <= ow_hi) {
+            int64_t o = (((int64_t)n * p.P + oh_lo + a) * p.Q + ow_lo + b) * p.C + cv * V;
+            ii[a * NW + b] = ld_pack<int32_t, V>(idx + o);
+            g[a * NW + b] = ld_pack<T, V>(dy + o);
+          }
+#pragma unroll
+      for (int a = 0; a < NW; ++a)
+#pragma unroll
+        for (int b = 0; b < NW; ++b)
+          if (oh_lo + a <= oh_hi && ow_lo + b <= ow_hi) {
+#pragma unroll
+            for (int j = 0; j < V; ++j)
+              if (ii[a * NW + b].v[j] == me) acc[j] += to_f(g[a * NW + b].v[j]);
+          }
+    } else {
+      for (int oh = oh_lo; oh <= oh_hi; ++oh)
+        for (int ow = ow_lo; ow <= ow_hi; ++ow) {
+          int64_t o = (((int64_t)n * p.P + oh) * p.Q + ow) * p.C + cv * V;
+          Pack<int32_t, V> ii = ld_pack<int32_t, V>(idx + o);
+          Pack<T, V> g = ld_pack<T, V>(dy + o);
+#pragma unroll
+          for (int j = 0; j < V; ++j)
+            if (ii.v[j] == me) acc[j] += to_f(g.v[j]);
+        }
+    }
     Pack<T, V> out;
 #pragma unroll
     for (int j = 0; j < V; ++j) out.v[j] = from_f<T>(acc[j]);
@@ -207,9 +258,15 @@ int cnb_maxpool_fwd(const cnb_pool_desc* d, const void* x, void* y, int32_t* idx
   if (v > 4) v = 4;
   while (v > 1 && (uintptr_t)idx % (v * 4) != 0) v >>= 1;
   int64_t total = (int64_t)p.N * p.P * p.Q * (p.C / v);
-  CNB_DISPATCH_TV(d->dtype, v,
-                  (maxpool_fwd_k<T, V><<<grid_for(total, kPoolThreads), kPoolThreads, 0,
-                                         (cudaStream_t)stream>>>((const T*)x, (T*)y, idx, p, total)));
+  const int k = p.kh > p.kw ? p.kh : p.kw;
+  const int grid = grid_for(total, kPoolThreads, 16);
+  cudaStream_t st = (cudaStream_t)stream;
+#define MPF(KK) CNB_DISPATCH_TV(d->dtype, v, (maxpool_fwd_k<T, V, KK><<<grid, kPoolThreads, 0, st>>>( \
+                                   (const T*)x, (T*)y, idx, p, total)))
+  if (k <= 2) MPF(2);
+  else if (k == 3) MPF(3);
+  else MPF(0);
+#undef MPF
   return check_launch("maxpool_fwd");
 }
 
@@ -222,9 +279,17 @@ int cnb_maxpool_bwd(const cnb_pool_desc* d, const void* dy, const int32_t* idx, 
   if (v > 4) v = 4;
   while (v > 1 && (uintptr_t)idx % (v * 4) != 0) v >>= 1;
   int64_t total = (int64_t)p.N * p.H * p.W * (p.C / v);
-  CNB_DISPATCH_TV(d->dtype, v,
-                  (maxpool_bwd_k<T, V><<<grid_for(total, kPoolThreads), kPoolThreads, 0,
-                                         (cudaStream_t)stream>>>((const T*)dy, idx, (T*)dx, p, total)));
+  const int nwh = (p.kh + p.sh - 1) / p.sh, nww = (p.kw + p.sw - 1) / p.sw;
+  const int nw = nwh > nww ? nwh : nww;
+  const int grid = grid_for(total, kPoolThreads, 16);
+  cudaStream_t st = (cudaStream_t)stream;
+#define MPB(NN) CNB_DISPATCH_TV(d->dtype, v, (maxpool_bwd_k<T, V, NN><<<grid, kPoolThreads, 0, st>>>( \
+                                   (const T*)dy, idx, (T*)dx, p, total)))
+  if (nw == 1) MPB(1);
+  else if (nw == 2) MPB(2);
+  else if (nw == 3) MPB(3);
+  else MPB(0);
+#undef MPB
   return check_launch("maxpool_bwd");
 }
 

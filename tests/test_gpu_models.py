@@ -80,7 +80,10 @@ def test_train_step_parity(family, kind, hw, batch, dtype):
     if dtype == torch.bfloat16:
         e_exact = O.rel_l2(out, exact)
         print(f"bf16 logits vs un-rounded fp64 oracle: {e_exact:.3e}")
-        assert e_exact <= 0.15
+        # bf16 storage rounding alone (fp64 arithmetic) moves the logits this far from exact:
+        e_storage = O.rel_l2(lg64, exact)
+        print(f"bf16-storage fp64 oracle vs un-rounded fp64 oracle: {e_storage:.3e}")
+        assert e_exact <= max(0.15, 2 * e_storage)
     assert abs(loss.item() - loss64.item()) <= max(tol, 2 * lfloor) * max(1.0, abs(loss64.item()))
     # BatchNorm running statistics and step counters
     new = model.state_dict()
