@@ -48,27 +48,79 @@ def _tail(last: nn.Module):
     return conv, bn
 
 
-def _residual_forward(body_name: str):
-    def forward(self, x):
-        """body(x) += shortcut(x); relu — the residual add and the ReLU run inside the last
-        BatchNorm kernel of the body (reference src/resnet.py:139-156,176-196)."""
-        blocks = list(getattr(self, body_name).children())
+_BODY_NAMES = ("res_block", "res_bottleneck", "se_bottleneck", "sk_bottleneck")
+
+
+def _residual_forward(self, x):
+    """body(x) += shortcut(x); relu.  When the body ends in a conv block, the residual add and the
+    ReLU run inside that block's BatchNorm kernel; when it ends in an SE unit they are one
+    add+ReLU kernel (reference src/resnet.py:139-156,176-196; src/se_resnet.py:199-211;
+    src/sknet.py:160-171)."""
+    body = next(getattr(self, n) for n in _BODY_NAMES if hasattr(self, n))
+    blocks = list(body.children())
+    identity = x if self.dim_synch is None else self.dim_synch(x)
+    last = blocks[-1]
+    if isinstance(last, nn.Sequential) and isinstance(next(iter(last.children()), None), nn.Conv2d):
         out = x
         for blk in blocks[:-1]:
             out = blk(out)
-        identity = x if self.dim_synch is None else self.dim_synch(x)
-        conv, bn = _tail(blocks[-1])
+        conv, bn = _tail(last)
         out = conv(out)
         if bn is not None:
             return bn(out, residual=identity, relu=True)
         return F_.add_relu(out, identity)
-    return forward
+    return F_.add_relu(body(x), identity)
 
 
-_BLOCK_FORWARDS = {
-    "ResBlock": _residual_forward("res_block"),
-    "ResBottleneck": _residual_forward("res_bottleneck"),
-}
+def _se_unit_forward(self, x):
+    """GAP -> excitation MLP (fp32, two tiny bias-free Linears) -> x * s  (src/se_resnet.py:244-255)"""
+    b, c = x.size(0), x.size(1)
+    s = self.excitation(F_.global_avg_pool2d(x).view(b, c))
+    return F_.se_scale(x, s.view(b, c, 1, 1))
+
+
+def _sk_conv_forward(self, x):
+    """Two grouped paths -> fused sum+GAP -> descriptor -> attention logits -> fused softmax-select
+    (src/sknet.py:222-242).  The descriptor / attention convs see [B, C, 1, 1] fp32 vectors."""
+    if self.num_paths != 2:
+        raise NotImplementedError("convnets_b200 SKConv: two paths (the reference's configuration)")
+    u0, u1 = self.kernels[0](x), self.kernels[1](x)
+    z = self.descriptor(F_.sk_fuse_gap(u0, u1))
+    logits = torch.cat([att(z) for att in self.attentions], dim=1)
+    return F_.sk_select(u0, u1, logits)
+
+
+def _shuffle_unit_forward(self, x):
+    """src/shufflenet_v1.py:150-171 with the shuffle, concat and add+ReLU in library kernels."""
+    out = self.conv1x1_group_compress(x)
+    out = F_.channel_shuffle(out, self.groups)
+    out = self.conv3x3_depthwise(out)
+    out = self.conv1x1_group_expand(out)
+    if self.downsample:
+        return F_.relu(F_.cat_channels([self.avg_pool(x), out]))
+    return F_.add_relu(out, x)
+
+
+def _fire_forward(self, x):
+    x = self.squeeze(x)
+    return F_.cat_channels([self.expand_1x1(x), self.expand_3x3(x)])
+
+
+def _inception_forward(self, x):
+    return F_.cat_channels([self.branch1(x), self.branch2(x), self.branch3(x), self.branch4(x)])
+
+
+def _dense_layer_forward(self, x):
+    return F_.cat_channels([x, self.conv_block(self.bottleneck(x))])
+
+
+_BLOCK_FORWARDS = {name: _residual_forward for name in (
+    "ResBlock", "ResBottleneck", "SEResBlock", "SEResBottleneck", "SEBlock", "SEBottleneck",
+    "SKResBottleneck", "SKBottleneck")}
+_BLOCK_FORWARDS.update({
+    "SEUnit": _se_unit_forward, "SKConv": _sk_conv_forward, "ShuffleUnit": _shuffle_unit_forward,
+    "Fire": _fire_forward, "InceptionBlock": _inception_forward, "DenseLayer": _dense_layer_forward,
+})
 
 
 def register_block_forward(class_name: str, fn) -> None:
@@ -81,6 +133,8 @@ def _fuse_bn_relu(seq: nn.Sequential) -> None:
     names = list(seq._modules.keys())
     for a, b in zip(names, names[1:]):
         ma, mb = seq._modules[a], seq._modules[b]
+        if isinstance(ma, L.Conv2d) and isinstance(mb, L.BatchNorm2d):
+            ma.emit_bn_stats = True  # conv -> bn: statistics come out of the conv epilogue
         if isinstance(ma, L.BatchNorm2d) and type(mb) in (nn.ReLU, L.ReLU):
             ma.fuse_relu = True
             seq._modules[b] = L.Identity()
@@ -115,5 +169,11 @@ def convert(model: nn.Module, dtype: torch.dtype = torch.bfloat16, fuse: bool = 
             fn = _BLOCK_FORWARDS.get(type(m).__name__)
             if fn is not None:
                 m.forward = types.MethodType(fn, m)
+    head = getattr(model, "classifier", None)
+    if isinstance(head, nn.Module) and any(isinstance(m, nn.Linear) for m in head.modules()):
+        # the Linear head keeps fp32 parameters (stays torch); models without
+        # a global average pool (ResNeXt, src/resnext.py:66-80) hand it bf16 feature maps
+        head.register_forward_pre_hook(lambda mod, args: tuple(
+            a.float() if torch.is_tensor(a) and a.dtype == torch.bfloat16 else a for a in args))
     model._cnb_dtype = dtype
     return model

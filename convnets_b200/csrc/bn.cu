@@ -166,6 +166,27 @@ __device__ __forceinline__ bool bn_block_merge(float (&s)[V], float (&q)[V], flo
   return true;
 }
 
+// Per-channel epilogue of the forward statistics: S = sum(x - K), Q = sum((x - K)^2).
+__device__ __forceinline__ void bn_finish_fwd(int c, double S, double Q, double K, int64_t M,
+                                              const BnFwdFin& f) {
+  const double ms = S / (double)M;
+  const double mean = K + ms;
+  double var = Q / (double)M - ms * ms;  // biased: used for normalisation
+  if (var < 0.0) var = 0.0;
+  const float rstd = (float)(1.0 / sqrt(var + (double)f.eps));
+  const float mu = (float)mean;
+  f.save_mean[c] = mu;
+  f.save_rstd[c] = rstd;
+  if (f.rmean) f.rmean[c] = (1.f - f.momentum) * f.rmean[c] + f.momentum * mu;
+  if (f.rvar) {
+    double unbiased = M > 1 ? var * (double)M / (double)(M - 1) : var;
+    f.rvar[c] = (1.f - f.momentum) * f.rvar[c] + f.momentum * (float)unbiased;
+  }
+  const float g = f.gamma ? f.gamma[c] : 1.f, b = f.beta ? f.beta[c] : 0.f;
+  f.scale[c] = g * rstd;
+  f.shift[c] = b - mu * g * rstd;
+}
+
 // ---------------------------------------------------------------- forward statistics
 // Shifted sums about the pivot K_c = x[row 0][c] (kills the mean^2/var cancellation of a raw
 // sum of squares): s = sum(x - K), q = sum((x - K)^2); mean = K + s/M, var = q/M - (s/M)^2.
@@ -211,23 +232,43 @@ bn_stats_k(const T* __restrict__ x, float* __restrict__ part, int64_t M, int C,
   int c;
   double S, Q;
   if (!bn_block_merge<V>(s, q, red, part, C, splits, counter, c, S, Q)) return;
-  const double K = (double)to_f(x[c]);
-  const double ms = S / (double)M;
-  const double mean = K + ms;
-  double var = Q / (double)M - ms * ms;  // biased: used for normalisation
-  if (var < 0.0) var = 0.0;
-  const float rstd = (float)(1.0 / sqrt(var + (double)f.eps));
-  const float mu = (float)mean;
-  f.save_mean[c] = mu;
-  f.save_rstd[c] = rstd;
-  if (f.rmean) f.rmean[c] = (1.f - f.momentum) * f.rmean[c] + f.momentum * mu;
-  if (f.rvar) {
-    double unbiased = M > 1 ? var * (double)M / (double)(M - 1) : var;
-    f.rvar[c] = (1.f - f.momentum) * f.rvar[c] + f.momentum * (float)unbiased;
+  bn_finish_fwd(c, S, Q, (double)to_f(x[c]), M, f);
+}
+
+// Statistics from per-tile partials written by the convolution epilogue (conv_tc.cu):
+// tiles[n][2][C] fp32 = column sums / sums of squares of 128-row tiles of the stored activations.
+// Same two-level, fixed-order merge as bn_stats_k (rows here are tiles, no pivot).
+__global__ void __launch_bounds__(kBnThreads)
+bn_partials_k(const float* __restrict__ tiles, float* __restrict__ part, int64_t ntiles, int64_t M,
+              int C, int64_t rows_per_split, int splits, int* __restrict__ counter, BnFwdFin f) {
+  extern __shared__ __align__(16) float red[];
+  const int c0 = blockIdx.x * blockDim.x + threadIdx.x;  // V = 1: one channel per thread column
+  const int64_t r0 = blockIdx.y * rows_per_split;
+  int64_t r1 = r0 + rows_per_split;
+  if (r1 > ntiles) r1 = ntiles;
+  float s[1] = {0.f}, q[1] = {0.f};
+  if (c0 < C) {
+    constexpr int U = 4;
+    const int64_t step = (int64_t)blockDim.y * U;
+    for (int64_t r = r0 + threadIdx.y; r < r1; r += step) {
+      float a[U], b[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t rr = r + (int64_t)u * blockDim.y;
+        a[u] = rr < r1 ? __ldg(tiles + (rr * 2 + 0) * C + c0) : 0.f;
+        b[u] = rr < r1 ? __ldg(tiles + (rr * 2 + 1) * C + c0) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        s[0] += a[u];
+        q[0] += b[u];
+      }
+    }
   }
-  const float g = f.gamma ? f.gamma[c] : 1.f, b = f.beta ? f.beta[c] : 0.f;
-  f.scale[c] = g * rstd;
-  f.shift[c] = b - mu * g * rstd;
+  int c;
+  double S, Q;
+  if (!bn_block_merge<1>(s, q, red, part, C, splits, counter, c, S, Q)) return;
+  bn_finish_fwd(c, S, Q, 0.0, M, f);
 }
 
 __global__ void bn_eval_coeff_k(const float* __restrict__ gamma, const float* __restrict__ beta,
@@ -247,8 +288,8 @@ __global__ void bn_eval_coeff_k(const float* __restrict__ gamma, const float* __
 template <typename T, int V, bool RELU, bool ADD>
 __global__ void __launch_bounds__(kBnThreads)
 bn_apply_k(const T* __restrict__ x, const T* __restrict__ res, const float* __restrict__ scale,
-           const float* __restrict__ shift, T* __restrict__ y, int64_t M, int C,
-           int64_t rows_per_split) {
+           const float* __restrict__ shift, T* __restrict__ y, uint8_t* __restrict__ mask, int64_t M,
+           int C, int64_t rows_per_split) {
   const int cv = blockIdx.x * blockDim.x + threadIdx.x;
   const int c0 = cv * V;
   if (c0 >= C) return;
@@ -277,6 +318,7 @@ bn_apply_k(const T* __restrict__ x, const T* __restrict__ res, const float* __re
       int64_t rr = r + (int64_t)u * blockDim.y;
       if (rr < r1) {
         Pack<T, V> o;
+        uint32_t bits = 0;
 #pragma unroll
         for (int j = 0; j < V; ++j) {
           float v = fmaf(to_f(a[u].v[j]), sc[j], sh[j]);
@@ -286,8 +328,11 @@ bn_apply_k(const T* __restrict__ x, const T* __restrict__ res, const float* __re
           }
           if (RELU) v = (v > 0.f || v != v) ? v : 0.f;
           o.v[j] = from_f<T>(v);
+          if (RELU && V == 8) bits |= (to_f(o.v[j]) > 0.f ? 1u : 0u) << j;
         }
         st_pack<T, V>(y + rr * C + c0, o);
+        // 1 bit per element (y > 0): backward reads this instead of y (1/16 of the bytes)
+        if (RELU && V == 8 && mask) mask[(rr * C + c0) >> 3] = (uint8_t)bits;
       }
     }
   }
@@ -299,8 +344,9 @@ bn_apply_k(const T* __restrict__ x, const T* __restrict__ res, const float* __re
 // c1 = gamma*rstd, c2 = s/M, c3 = rstd^2 * q / M
 template <typename T, int V, bool RELU>
 __global__ void __launch_bounds__(kBnThreads)
-bn_bwd_reduce_k(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy,
-                const float* __restrict__ mean, float* __restrict__ part, int64_t M, int C,
+bn_bwd_reduce_k(const T* __restrict__ x, const T* __restrict__ y, const uint8_t* __restrict__ mask,
+                const T* __restrict__ dy, const float* __restrict__ mean, float* __restrict__ part,
+                int64_t M, int C,
                 int64_t rows_per_split, int splits, int* __restrict__ counter, BnBwdFin f) {
   extern __shared__ __align__(16) float red[];
   const int cv = blockIdx.x * blockDim.x + threadIdx.x;
@@ -318,13 +364,17 @@ bn_bwd_reduce_k(const T* __restrict__ x, const T* __restrict__ y, const T* __res
     const int64_t step = (int64_t)blockDim.y * U;
     for (int64_t r = r0 + threadIdx.y; r < r1; r += step) {
       Pack<T, V> a[U], g[U], o[U];
+      uint32_t mb[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         int64_t rr = r + (int64_t)u * blockDim.y;
         if (rr < r1) {
           a[u] = ld_pack<T, V>(x + rr * C + c0);
           g[u] = ld_pack<T, V>(dy + rr * C + c0);
-          if (RELU) o[u] = ld_pack<T, V>(y + rr * C + c0);
+          if (RELU) {
+            if (V == 8 && mask) mb[u] = mask[(rr * C + c0) >> 3];
+            else o[u] = ld_pack<T, V>(y + rr * C + c0);
+          }
         }
       }
 #pragma unroll
@@ -334,7 +384,10 @@ bn_bwd_reduce_k(const T* __restrict__ x, const T* __restrict__ y, const T* __res
 #pragma unroll
           for (int j = 0; j < V; ++j) {
             float gf = to_f(g[u].v[j]);
-            if (RELU && !(to_f(o[u].v[j]) > 0.f)) gf = 0.f;
+            if (RELU) {
+              const bool pos = (V == 8 && mask) ? ((mb[u] >> j) & 1u) : (to_f(o[u].v[j]) > 0.f);
+              if (!pos) gf = 0.f;
+            }
             s[j] += gf;
             q[j] = fmaf(gf, to_f(a[u].v[j]) - mu[j], q[j]);
           }
@@ -356,8 +409,8 @@ bn_bwd_reduce_k(const T* __restrict__ x, const T* __restrict__ y, const T* __res
 
 template <typename T, int V, bool RELU, bool DRES>
 __global__ void __launch_bounds__(kBnThreads)
-bn_bwd_dx_k(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy,
-            const float* __restrict__ mean, const float* __restrict__ c1,
+bn_bwd_dx_k(const T* __restrict__ x, const T* __restrict__ y, const uint8_t* __restrict__ mask,
+            const T* __restrict__ dy, const float* __restrict__ mean, const float* __restrict__ c1,
             const float* __restrict__ c2, const float* __restrict__ c3, T* __restrict__ dx,
             T* __restrict__ dres, int64_t M, int C, int64_t rows_per_split) {
   const int cv = blockIdx.x * blockDim.x + threadIdx.x;
@@ -379,13 +432,17 @@ bn_bwd_dx_k(const T* __restrict__ x, const T* __restrict__ y, const T* __restric
   const int64_t step = (int64_t)blockDim.y * U;
   for (int64_t r = r0 + threadIdx.y; r < r1; r += step) {
     Pack<T, V> a[U], g[U], m[U];
+    uint32_t mb[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       int64_t rr = r + (int64_t)u * blockDim.y;
       if (rr < r1) {
         a[u] = ld_pack<T, V>(x + rr * C + c0);
         g[u] = ld_pack<T, V>(dy + rr * C + c0);
-        if (RELU) m[u] = ld_pack<T, V>(y + rr * C + c0);
+        if (RELU) {
+          if (V == 8 && mask) mb[u] = mask[(rr * C + c0) >> 3];
+          else m[u] = ld_pack<T, V>(y + rr * C + c0);
+        }
       }
     }
 #pragma unroll
@@ -396,7 +453,10 @@ bn_bwd_dx_k(const T* __restrict__ x, const T* __restrict__ y, const T* __restric
 #pragma unroll
         for (int j = 0; j < V; ++j) {
           float gf = to_f(g[u].v[j]);
-          if (RELU && !(to_f(m[u].v[j]) > 0.f)) gf = 0.f;
+          if (RELU) {
+            const bool pos = (V == 8 && mask) ? ((mb[u] >> j) & 1u) : (to_f(m[u].v[j]) > 0.f);
+            if (!pos) gf = 0.f;
+          }
           if (DRES) dr.v[j] = from_f<T>(gf);
           o.v[j] = from_f<T>(fmaf(k1[j], gf, fmaf(k3[j], to_f(a[u].v[j]), k0[j])));
         }
@@ -435,9 +495,15 @@ size_t cnb_bn_workspace_bytes(const cnb_bn_desc* d) {
 
 int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, const float* gamma,
                      const float* beta, float* running_mean, float* running_var, void* y,
-                     float* save_mean, float* save_rstd, void* workspace, size_t workspace_bytes,
+                     float* save_mean, float* save_rstd, const float* conv_partials,
+                     int32_t n_partials, void* relu_mask, void* workspace, size_t workspace_bytes,
                      void* stream) {
   CNB_TRY(validate_bn(d, "cnb_bn_fwd_train"));
+  CNB_REQUIRE(!conv_partials || n_partials > 0, CNB_ERR_INVALID,
+              "cnb_bn_fwd_train: conv_partials given with n_partials=%d", n_partials);
+  CNB_REQUIRE(!relu_mask || ((d->flags & CNB_BN_RELU) && d->dtype == CNB_BF16 && d->C % 8 == 0),
+              CNB_ERR_INVALID,
+              "cnb_bn_fwd_train: relu_mask needs CNB_BN_RELU, bf16 and C %% 8 == 0 (C=%d)", d->C);
   CNB_REQUIRE(x && y && save_mean && save_rstd && workspace, CNB_ERR_INVALID,
               "cnb_bn_fwd_train: null pointer");
   const bool add = d->flags & CNB_BN_ADD, relu = d->flags & CNB_BN_RELU;
@@ -451,30 +517,54 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
   const int C = d->C;
   const int64_t M = d->M;
   int v = pick_vec(C, dtype_size(d->dtype), x, y, add ? residual : nullptr);
-  BnGeom g = bn_geom(M, C, v, kReduceWaves, kReduceCx);
+  CNB_REQUIRE(!relu_mask || v == 8, CNB_ERR_INVALID,
+              "cnb_bn_fwd_train: relu_mask needs 16-byte aligned tensors");
+  BnFwdFin fin{gamma, beta, running_mean, running_var, save_mean, save_rstd, nullptr, nullptr,
+               d->eps, d->momentum};
   float* part = (float*)workspace;
-  float* scale = part + (size_t)2 * C * g.splits;
-  float* shift = scale + C;
-  int* counter = bn_counters(g.cblocks);
-  CNB_REQUIRE(counter, CNB_ERR_CUDA, "cnb_bn_fwd_train: cannot allocate the arrival counters");
-  {
+  float* scale;
+  if (conv_partials) {
+    // statistics were accumulated by the producing convolution's epilogue: merge its per-tile rows
+    BnGeom g;
+    g.V = 1; g.cx = 64; g.ry = kBnThreads / 64;
+    g.cblocks = (int)ceil_div(C, 64);
+    int64_t splits = ceil_div((int64_t)sm_count() * 2, g.cblocks);
+    int64_t max_splits = ceil_div((int64_t)n_partials, (int64_t)g.ry * 4);
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+    g.rows_per_split = ceil_div((int64_t)n_partials, splits);
+    g.splits = (int)ceil_div((int64_t)n_partials, g.rows_per_split);
+    scale = part + (size_t)2 * C * g.splits;
+    fin.scale = scale; fin.shift = scale + C;
+    int* counter = bn_counters(g.cblocks);
+    CNB_REQUIRE(counter, CNB_ERR_CUDA, "cnb_bn_fwd_train: cannot allocate the arrival counters");
+    dim3 grid(g.cblocks, g.splits), block(g.cx, g.ry);
+    bn_partials_k<<<grid, block, 4096, st>>>(conv_partials, part, n_partials, M, C, g.rows_per_split,
+                                             g.splits, counter, fin);
+    CNB_TRY(check_launch("bn_partials"));
+  } else {
+    BnGeom g = bn_geom(M, C, v, kReduceWaves, kReduceCx);
+    scale = part + (size_t)2 * C * g.splits;
+    fin.scale = scale; fin.shift = scale + C;
+    int* counter = bn_counters(g.cblocks);
+    CNB_REQUIRE(counter, CNB_ERR_CUDA, "cnb_bn_fwd_train: cannot allocate the arrival counters");
     dim3 grid(g.cblocks, g.splits), block(g.cx, g.ry);
     size_t smem = (size_t)g.ry * 2 * g.cx * v * sizeof(float);
     if (smem < 4096) smem = 4096;  // the merge step re-uses it for 256 x 2 doubles
-    BnFwdFin fin{gamma, beta, running_mean, running_var, save_mean, save_rstd, scale, shift,
-                 d->eps, d->momentum};
     CNB_DISPATCH_TV(d->dtype, v, (bn_stats_k<T, V><<<grid, block, smem, st>>>(
                                      (const T*)x, part, M, C, g.rows_per_split, g.splits, counter,
                                      fin)));
     CNB_TRY(check_launch("bn_stats"));
   }
+  float* shift = scale + C;
+  uint8_t* mask = (uint8_t*)relu_mask;
   BnGeom ga = bn_geom(M, C, v, kStreamWaves);
   dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
   const int64_t arows = ga.rows_per_split;
 #define APPLY(R, A)                                                                              \
   CNB_DISPATCH_TV(d->dtype, v, (bn_apply_k<T, V, R, A><<<agrid, ablock, 0, st>>>(                \
-                                   (const T*)x, (const T*)residual, scale, shift, (T*)y, d->M,  \
-                                   C, arows)))
+                                   (const T*)x, (const T*)residual, scale, shift, (T*)y, mask,  \
+                                   d->M, C, arows)))
   if (relu && add) APPLY(true, true);
   else if (relu) APPLY(true, false);
   else if (add) APPLY(false, true);
@@ -505,6 +595,7 @@ int cnb_bn_fwd_eval(const cnb_bn_desc* d, const void* x, const void* residual, c
   BnGeom ga = bn_geom(d->M, C, v, kStreamWaves);
   dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
   const int64_t arows = ga.rows_per_split;
+  uint8_t* mask = nullptr;
   if (relu && add) APPLY(true, true);
   else if (relu) APPLY(true, false);
   else if (add) APPLY(false, true);
@@ -513,23 +604,28 @@ int cnb_bn_fwd_eval(const cnb_bn_desc* d, const void* x, const void* residual, c
   return check_launch("bn_apply(eval)");
 }
 
-int cnb_bn_bwd(const cnb_bn_desc* d, const void* x, const void* y, const void* dy,
-               const float* gamma, const float* save_mean, const float* save_rstd, void* dx,
+int cnb_bn_bwd(const cnb_bn_desc* d, const void* x, const void* y, const void* relu_mask,
+               const void* dy, const float* gamma, const float* save_mean, const float* save_rstd, void* dx,
                void* d_residual, float* dgamma, float* dbeta, void* workspace,
                size_t workspace_bytes, void* stream) {
   CNB_TRY(validate_bn(d, "cnb_bn_bwd"));
   CNB_REQUIRE(x && dy && save_mean && save_rstd && dx && workspace, CNB_ERR_INVALID,
               "cnb_bn_bwd: null pointer");
   const bool relu = d->flags & CNB_BN_RELU;
-  CNB_REQUIRE(!relu || y, CNB_ERR_INVALID, "cnb_bn_bwd: CNB_BN_RELU needs the forward output y");
+  CNB_REQUIRE(!relu || y || relu_mask, CNB_ERR_INVALID,
+              "cnb_bn_bwd: CNB_BN_RELU needs the forward output y or the relu_mask");
+  CNB_REQUIRE(!relu_mask || (relu && d->dtype == CNB_BF16 && d->C % 8 == 0), CNB_ERR_INVALID,
+              "cnb_bn_bwd: relu_mask needs CNB_BN_RELU, bf16 and C %% 8 == 0 (C=%d)", d->C);
+  const uint8_t* mask = (const uint8_t*)relu_mask;
   CNB_REQUIRE(workspace_bytes >= bn_ws_bytes(d->C), CNB_ERR_WORKSPACE,
               "cnb_bn_bwd: workspace %zu < %zu", workspace_bytes, bn_ws_bytes(d->C));
   cudaStream_t st = (cudaStream_t)stream;
   const int C = d->C;
   const int64_t M = d->M;
-  int v = pick_vec(C, dtype_size(d->dtype), x, dy, dx, relu ? y : nullptr);
+  int v = pick_vec(C, dtype_size(d->dtype), x, dy, dx, (relu && !mask) ? y : nullptr);
   if (d_residual)
     while (v > 1 && (uintptr_t)d_residual % (v * dtype_size(d->dtype)) != 0) v >>= 1;
+  CNB_REQUIRE(!mask || v == 8, CNB_ERR_INVALID, "cnb_bn_bwd: relu_mask needs 16-byte aligned tensors");
   BnGeom g = bn_geom(M, C, v, kReduceWaves, kReduceCx);
   float* part = (float*)workspace;
   float* c1 = part + (size_t)2 * C * g.splits;
@@ -544,11 +640,11 @@ int cnb_bn_bwd(const cnb_bn_desc* d, const void* x, const void* y, const void* d
     BnBwdFin fin{gamma, save_rstd, dgamma, dbeta, c1, c2, c3};
     if (relu)
       CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_reduce_k<T, V, true><<<grid, block, smem, st>>>(
-                                       (const T*)x, (const T*)y, (const T*)dy, save_mean, part, M, C,
+                                       (const T*)x, (const T*)y, mask, (const T*)dy, save_mean, part, M, C,
                                        g.rows_per_split, g.splits, counter, fin)));
     else
       CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_reduce_k<T, V, false><<<grid, block, smem, st>>>(
-                                       (const T*)x, (const T*)y, (const T*)dy, save_mean, part, M, C,
+                                       (const T*)x, (const T*)y, mask, (const T*)dy, save_mean, part, M, C,
                                        g.rows_per_split, g.splits, counter, fin)));
     CNB_TRY(check_launch("bn_bwd_reduce"));
   }
@@ -557,8 +653,8 @@ int cnb_bn_bwd(const cnb_bn_desc* d, const void* x, const void* y, const void* d
   const int64_t arows = ga.rows_per_split;
 #define DX(R, D)                                                                                  \
   CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_dx_k<T, V, R, D><<<agrid, ablock, 0, st>>>(                \
-                                   (const T*)x, (const T*)y, (const T*)dy, save_mean, c1, c2, c3, \
-                                   (T*)dx, (T*)d_residual, M, C, arows)))
+                                   (const T*)x, (const T*)y, mask, (const T*)dy, save_mean, c1,   \
+                                   c2, c3, (T*)dx, (T*)d_residual, M, C, arows)))
   if (relu && d_residual) DX(true, true);
   else if (relu) DX(true, false);
   else if (d_residual) DX(false, true);

@@ -72,8 +72,16 @@ size_t cnb_conv2d_workspace_bytes(const cnb_conv_desc* d, int direction) {
   return direction == CNB_WGRAD ? conv_simt_wgrad_ws(*d) : 0;
 }
 
+int cnb_conv2d_bn_partial_rows(const cnb_conv_desc* d) {
+  CNB_TRY(validate_conv(d, "cnb_conv2d_bn_partial_rows"));
+  if (is_depthwise(*d)) return 0;
+  int a = pick_algo(*d, CNB_FWD, "cnb_conv2d_bn_partial_rows");
+  if (a < 0) return a;
+  return a == 1 ? conv_tc_stats_rows(*d) : 0;
+}
+
 int cnb_conv2d_fwd(const cnb_conv_desc* d, const void* x, const void* w, const float* bias, void* y,
-                   void* workspace, size_t workspace_bytes, void* stream) {
+                   float* bn_partials, void* workspace, size_t workspace_bytes, void* stream) {
   CNB_TRY(validate_conv(d, "cnb_conv2d_fwd"));
   CNB_REQUIRE(x && w && y, CNB_ERR_INVALID, "cnb_conv2d_fwd: null tensor pointer");
   CNB_REQUIRE(!(d->flags & CNB_CONV_BIAS) || bias, CNB_ERR_INVALID,
@@ -81,6 +89,7 @@ int cnb_conv2d_fwd(const cnb_conv_desc* d, const void* x, const void* w, const f
   cudaStream_t st = (cudaStream_t)stream;
   if (is_depthwise(*d)) {
     CNB_REQUIRE(d->algo != CNB_ALGO_TC, CNB_ERR_UNSUPPORTED, "cnb_conv2d_fwd: depthwise has no TC path");
+    CNB_REQUIRE(!bn_partials, CNB_ERR_UNSUPPORTED, "cnb_conv2d_fwd: bn_partials on a depthwise conv");
     return dwconv_fwd(*d, x, w, bias, y, st);
   }
   int a = pick_algo(*d, CNB_FWD, "cnb_conv2d_fwd");
@@ -88,8 +97,10 @@ int cnb_conv2d_fwd(const cnb_conv_desc* d, const void* x, const void* w, const f
   if (a == 1) {
     CNB_REQUIRE(((uintptr_t)x | (uintptr_t)w | (uintptr_t)y) % 16 == 0, CNB_ERR_INVALID,
                 "cnb_conv2d_fwd: tensor pointers must be 16-byte aligned for TMA");
-    return conv_tc_fwd(*d, x, w, bias, y, workspace, workspace_bytes, st);
+    return conv_tc_fwd(*d, x, w, bias, y, bn_partials, workspace, workspace_bytes, st);
   }
+  CNB_REQUIRE(!bn_partials, CNB_ERR_UNSUPPORTED,
+              "cnb_conv2d_fwd: bn_partials requested on the CUDA-core path (cnb_conv2d_bn_partial_rows() == 0)");
   return conv_simt_fwd(*d, x, w, (d->flags & CNB_CONV_BIAS) ? bias : nullptr, y, st);
 }
 

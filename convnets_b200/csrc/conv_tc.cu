@@ -121,6 +121,7 @@ struct FpropParams {
   CUtensorMap tmB;  // weights {Cg, RS, Kout}, box {64, 1, BLOCK_N}
   CUtensorMap tmD;  // output {Kout, M}, box {64, 128}
   const float* bias;
+  float* stats;     // optional [m-tiles][2][Kout] per-tile column sums / sums of squares of the stored output
   int M;            // output pixels in this launch
   int outP, outQ;   // output grid per image (pixel index -> (n, i, j))
   int lower_h, lower_w, trav_h, trav_w;
@@ -464,6 +465,29 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
         }
         tma_store_commit();
       }
+      if (p.stats != nullptr) {
+        // BatchNorm statistics of this tile from the staged (bf16-rounded, i.e. as stored) values:
+        // each thread owns a pair of adjacent columns and walks the rows of the swizzled boxes.
+        // One fp32 partial row per m-tile -> merged in fixed order by bn_partials_k (deterministic).
+        const int rows = min(TILE_M, p.M - m0);
+        float* dst = p.stats + (size_t)(tile / p.n_tiles) * 2 * p.Kout;
+        for (int pr = (int)threadIdx.x - 64; pr < BLOCK_N / 2; pr += 128) {
+          const int c = pr * 2;
+          const uint8_t* colp = stage_out + (c / 64) * (TILE_M * 128) + (c % 8) * 2;
+          const int chunk = (c % 64) / 8;
+          float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll 8
+          for (int r = 0; r < rows; ++r) {
+            const uint32_t w2 = *reinterpret_cast<const uint32_t*>(colp + r * 128 + ((chunk ^ (r & 7)) * 16));
+            const float a = __uint_as_float(w2 << 16), b = __uint_as_float(w2 & 0xffff0000u);
+            s0 += a; q0 = fmaf(a, a, q0);
+            s1 += b; q1 = fmaf(b, b, q1);
+          }
+          const int col = n0 + c;
+          if (col < p.Kout) { dst[col] = s0; dst[p.Kout + col] = q0; }
+          if (col + 1 < p.Kout) { dst[col + 1] = s1; dst[p.Kout + col + 1] = q1; }
+        }
+      }
     }
     if (storer) tma_store_wait0();
   }
@@ -726,6 +750,7 @@ struct FpropLaunch {
   int Kout, RS;
   void* out;                     // [aN*outP*outQ, Kout] bf16
   const float* bias;
+  float* stats;                  // optional BatchNorm partials (forward only)
   int flags;
   bool tiled2d;                  // pure GEMM: A is the [M, C] matrix itself
 };
@@ -805,6 +830,7 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
     CNB_TRY(make_tiled_map(&prm.tmD, L.out, 2, dims, str, box, "D(output)"));
   }
   prm.bias = L.bias;
+  prm.stats = L.stats;
   prm.M = M;
   prm.outP = L.outP; prm.outQ = L.outQ;
   prm.lower_h = L.lower_h; prm.lower_w = L.lower_w;
@@ -833,6 +859,8 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
     if (BLOCK_N == 128) return launch_fprop_persist_inst<128, 5, true>(prm, st);
     return launch_fprop_persist_inst<256, 3, true>(prm, st);
   }
+  CNB_REQUIRE(L.stats == nullptr, CNB_ERR_UNSUPPORTED,
+              "conv_tc: BatchNorm partials need the persistent kernel (unset CNB_CONV_PERSIST=0)");
   const bool shallow = prm.num_taps * prm.num_cblk <= 4;
   if (L.tiled2d) {
     if (shallow) {
@@ -897,12 +925,26 @@ static void wgrad_geometry(const cnb_conv_desc& d, int& NT, int& taps_per_cta, i
   const int64_t M = (int64_t)d.N * P * Q;
   const int64_t total_pb = ceil_div(M, 64);
   const int64_t tiles = (int64_t)tap_groups * cin_tiles * cout_tiles;
-  int64_t want = ceil_div((int64_t)sm_count() * 2, tiles);
-  int64_t maxs = ceil_div(total_pb, 8);  // at least 8 pixel blocks (512 pixels) per split
-  if (want > maxs) want = maxs;
-  if (want < 1) want = 1;
-  if (want > 512) want = 512;
-  pixblk_per_split = (int)ceil_div(total_pb, want);
+  // One CTA is resident per SM (the operand rings take > 114 KB), so the grid runs in waves of
+  // sm_count CTAs.  Pick the split count that minimises waves x per-CTA time: per-CTA time ~
+  // (pixel blocks per split) x (taps per CTA) MMA groups + a fixed prologue/epilogue cost; every
+  // extra split also adds one row to the second-stage sum.  At least 8 pixel blocks per split.
+  const int64_t sms = sm_count();
+  int64_t maxs = ceil_div(total_pb, 8);
+  if (maxs > 512) maxs = 512;
+  if (maxs < 1) maxs = 1;
+  int64_t best_s = 1;
+  double best_cost = 1e300;
+  for (int64_t sp = 1; sp <= maxs; ++sp) {
+    const int64_t waves = ceil_div(sp * tiles, sms);
+    const double per_cta = (double)ceil_div(total_pb, sp) * taps_per_cta + 12.0 + 2.0 * taps_per_cta;
+    const double cost = (double)waves * per_cta + 0.05 * (double)sp;
+    if (cost < best_cost * 0.999) {
+      best_cost = cost;
+      best_s = sp;
+    }
+  }
+  pixblk_per_split = (int)ceil_div(total_pb, best_s);
   splits = (int)ceil_div(total_pb, pixblk_per_split);
 }
 
@@ -923,8 +965,14 @@ size_t conv_tc_workspace(const cnb_conv_desc& d, int direction) {
   return (size_t)(splits > 1 ? splits : 0) * d.K * d.R * d.S * d.C * sizeof(float) + 1024;
 }
 
+int conv_tc_stats_rows(const cnb_conv_desc& d) {
+  int P, Q;
+  conv_out_dims(d, P, Q);
+  return (int)ceil_div((int64_t)d.N * P * Q, TILE_M);
+}
+
 int conv_tc_fwd(const cnb_conv_desc& d, const void* x, const void* w, const float* bias, void* y,
-                void* ws, size_t ws_bytes, cudaStream_t st) {
+                float* stats, void* ws, size_t ws_bytes, cudaStream_t st) {
   (void)ws; (void)ws_bytes;
   FpropLaunch L;
   memset(&L, 0, sizeof(L));
@@ -946,6 +994,7 @@ int conv_tc_fwd(const cnb_conv_desc& d, const void* x, const void* w, const floa
     }
   L.w = w; L.Kout = d.K; L.RS = d.R * d.S;
   L.out = y; L.bias = bias; L.flags = d.flags;
+  L.stats = stats;
   L.tiled2d = (d.R == 1 && d.S == 1 && d.stride_h == 1 && d.stride_w == 1 && d.pad_h == 0 &&
                d.pad_w == 0);
   return launch_fprop(L, st);

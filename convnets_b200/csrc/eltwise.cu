@@ -150,6 +150,58 @@ __global__ void im2col_nchw_k(const float* __restrict__ src, T* __restrict__ dst
   }
 }
 
+// Row-staged variant: one CTA per (image, output row).  The R (dilated) input rows that row needs
+// are loaded once, coalesced, into a zero-padded smem patch [C][R][W + 2*pad_w] already converted
+// to T, together with a column table (offset of every im2col column inside the patch, -1 for the
+// zero columns); each thread then assembles 16-byte output vectors from smem and the CTA writes
+// one contiguous Q x Kd row block.  No integer division or bounds check in the inner loop.
+template <typename T, int V>
+__global__ void __launch_bounds__(256)
+im2col_nchw_rows_k(const float* __restrict__ src, T* __restrict__ dst, Im2colP p) {
+  extern __shared__ __align__(16) uint8_t sm_raw[];
+  const int Wp = p.W + 2 * p.pw;
+  int* coltab = reinterpret_cast<int*>(sm_raw);                       // [Kd]
+  T* patch = reinterpret_cast<T*>(sm_raw + (size_t)((p.Kd * 4 + 15) / 16) * 16);  // [C][R][Wp]
+  const int ii = blockIdx.x % p.P;
+  const int n = blockIdx.x / p.P;
+  const int RSC = p.R * p.S * p.C;
+  for (int col = threadIdx.x; col < p.Kd; col += blockDim.x) {
+    int off = -1;
+    if (col < RSC) {
+      const int c = col % p.C, rs = col / p.C;
+      const int s_ = rs % p.S, r = rs / p.S;
+      off = (c * p.R + r) * Wp + s_ * p.dw;
+    }
+    coltab[col] = off;
+  }
+  const int h0 = ii * p.sh - p.ph;
+  const int rows = p.C * p.R;
+  for (int i = threadIdx.x; i < rows * Wp; i += blockDim.x) {
+    const int wp = i % Wp, cr = i / Wp;
+    const int r = cr % p.R, c = cr / p.R;
+    const int h = h0 + r * p.dh, w = wp - p.pw;
+    float v = 0.f;
+    if (h >= 0 && h < p.H && w >= 0 && w < p.W)
+      v = __ldg(src + (((int64_t)n * p.C + c) * p.H + h) * p.W + w);
+    patch[i] = from_f<T>(v);
+  }
+  __syncthreads();
+  const int kv = p.Kd / V;
+  T* out = dst + ((int64_t)n * p.P + ii) * p.Q * p.Kd;
+  const T zero = from_f<T>(0.f);
+  for (int i = threadIdx.x; i < p.Q * kv; i += blockDim.x) {
+    const int cv = i % kv, j = i / kv;
+    const int base = j * p.sw;
+    Pack<T, V> o;
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+      const int off = coltab[cv * V + e];
+      o.v[e] = off >= 0 ? patch[off + base] : zero;
+    }
+    st_pack<T, V>(out + (int64_t)i * V, o);
+  }
+}
+
 // ------------------------------------------------------------------ channel shuffle / slab copy
 // y[m, j*g + i] = x[m, i*(C/g) + j]; one thread per output element pair is fine: rows are short
 // and both sides stay within one row (L1/L2 absorb the permutation), traffic = 2 * numel.
@@ -516,6 +568,19 @@ int cnb_im2col_nchw(const cnb_conv_desc* d, const float* src, void* dst, int32_t
   Im2colP p{d->N, d->C, d->H, d->W, d->R, d->S, P, Q, d->stride_h, d->stride_w, d->pad_h, d->pad_w,
             d->dil_h, d->dil_w, K_dst};
   const int64_t total = (int64_t)d->N * P * Q * (K_dst / v);
+  {
+    // row-staged kernel when its smem patch fits the default 48 KB
+    const size_t smem = (size_t)((K_dst * 4 + 15) / 16) * 16 +
+                        (size_t)d->C * d->R * (d->W + 2 * d->pad_w) * dtype_size(d->dtype);
+    if (smem <= 48 * 1024 && (int64_t)d->N * P < (1ll << 31)) {
+      const unsigned grid = (unsigned)((int64_t)d->N * P);
+      if (d->dtype == CNB_BF16)
+        im2col_nchw_rows_k<bf16, 8><<<grid, 256, smem, (cudaStream_t)stream>>>(src, (bf16*)dst, p);
+      else
+        im2col_nchw_rows_k<float, 4><<<grid, 256, smem, (cudaStream_t)stream>>>(src, (float*)dst, p);
+      return check_launch("im2col_nchw_rows");
+    }
+  }
   if (d->dtype == CNB_BF16)
     im2col_nchw_k<bf16, 8><<<grid_for(total, kThreads, 16), kThreads, 0, (cudaStream_t)stream>>>(
         src, (bf16*)dst, p, total);

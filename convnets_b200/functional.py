@@ -131,7 +131,7 @@ def _conv_desc(x_shape, w_shape, stride, padding, dilation, groups, dtype_code, 
 
 class _Conv2dFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, wpack, stride, padding, dilation, groups, algo):
+    def forward(ctx, x, weight, bias, wpack, stride, padding, dilation, groups, algo, want_stats):
         _cuda(x, wpack, bias)
         lib = _L.load()
         x = _nhwc(x)
@@ -145,16 +145,20 @@ class _Conv2dFn(torch.autograd.Function):
         nws = lib.cnb_conv2d_workspace_bytes(C.byref(d), _L.CNB_FWD)
         ws = _workspace(nws, x.device)
         b32 = None if bias is None else bias.detach().float().contiguous()
-        _L.check(lib.cnb_conv2d_fwd(C.byref(d), _p(x), _p(wpack), _p(b32), _p(y), _p(ws), ws.numel(),
-                                    _stream()), "cnb_conv2d_fwd")
+        rows = lib.cnb_conv2d_bn_partial_rows(C.byref(d)) if want_stats else 0
+        part = torch.empty((max(rows, 0), 2, wpack.shape[0]), dtype=torch.float32, device=x.device)
+        _L.check(lib.cnb_conv2d_fwd(C.byref(d), _p(x), _p(wpack), _p(b32), _p(y),
+                                    _p(part) if rows > 0 else None, _p(ws), ws.numel(), _stream()),
+                 "cnb_conv2d_fwd")
         ctx.save_for_backward(x, wpack)
         ctx.desc = d
         ctx.has_bias = bias is not None
         ctx.wshape = tuple(weight.shape)
-        return y
+        ctx.mark_non_differentiable(part)
+        return y, part
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, _dpart=None):
         lib = _L.load()
         x, wpack = ctx.saved_tensors
         d = ctx.desc
@@ -179,17 +183,22 @@ class _Conv2dFn(torch.autograd.Function):
                                           ws.numel(), _stream()), "cnb_conv2d_wgrad")
             if tuple(dw.shape) != ctx.wshape:  # zero-padded input channels (RGB stem)
                 dw = dw[:, :ctx.wshape[1]].contiguous(memory_format=_CL)
-        return dx, dw, db, None, None, None, None, None, None
+        return dx, dw, db, None, None, None, None, None, None, None
 
 
 def conv2d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, wpack=None,
-           algo=_L.CNB_ALGO_AUTO):
+           algo=_L.CNB_ALGO_AUTO, bn_stats=False):
     """Drop-in for F.conv2d as reached from nn.Conv2d (reference src/basemodel.py:974,992).
-    `weight` is the fp32 master parameter; `wpack` an optional pre-packed operand copy."""
+    `weight` is the fp32 master parameter; `wpack` an optional pre-packed operand copy.
+    With `bn_stats` returns (y, partials): the per-tile BatchNorm partial sums emitted by the
+    forward epilogue (None when this conv runs on a path that cannot produce them)."""
     if wpack is None:
         wpack = pack_weight(weight, x.dtype)
-    return _Conv2dFn.apply(x, weight, bias, wpack, _pair(stride), _pair(padding), _pair(dilation),
-                           int(groups), int(algo))
+    y, part = _Conv2dFn.apply(x, weight, bias, wpack, _pair(stride), _pair(padding),
+                              _pair(dilation), int(groups), int(algo), bool(bn_stats))
+    if bn_stats:
+        return y, (part if part.shape[0] > 0 else None)
+    return y
 
 
 class _InputConvFn(torch.autograd.Function):
@@ -198,7 +207,7 @@ class _InputConvFn(torch.autograd.Function):
     descriptor.  The im2col matrix is kept for the weight gradient; the input gets no gradient."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, padding, dilation, dtype):
+    def forward(ctx, x, weight, bias, stride, padding, dilation, dtype, want_stats):
         _cuda(x, weight, bias)
         lib = _L.load()
         if x.dtype != torch.float32 or not x.is_contiguous():
@@ -226,16 +235,20 @@ class _InputConvFn(torch.autograd.Function):
         y = _empty_nhwc(n, k, P, Q, dtype, x.device)
         ws = _workspace(lib.cnb_conv2d_workspace_bytes(C.byref(d1), _L.CNB_FWD), x.device)
         b32 = None if bias is None else bias.detach().float().contiguous()
-        _L.check(lib.cnb_conv2d_fwd(C.byref(d1), _p(col), _p(wcol), _p(b32), _p(y), _p(ws), ws.numel(),
-                                    _stream()), "cnb_conv2d_fwd(input)")
+        rows = lib.cnb_conv2d_bn_partial_rows(C.byref(d1)) if want_stats else 0
+        part = torch.empty((max(rows, 0), 2, k), dtype=torch.float32, device=x.device)
+        _L.check(lib.cnb_conv2d_fwd(C.byref(d1), _p(col), _p(wcol), _p(b32), _p(y),
+                                    _p(part) if rows > 0 else None, _p(ws), ws.numel(), _stream()),
+                 "cnb_conv2d_fwd(input)")
         ctx.save_for_backward(col)
         ctx.desc = d1
         ctx.geom = (k, c, r, s, rsc, kd)
         ctx.has_bias = bias is not None
-        return y
+        ctx.mark_non_differentiable(part)
+        return y, part
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, _dpart=None):
         lib = _L.load()
         (col,) = ctx.saved_tensors
         d = ctx.desc
@@ -249,13 +262,18 @@ class _InputConvFn(torch.autograd.Function):
         _L.check(lib.cnb_conv2d_wgrad(C.byref(d), _p(col), _p(dy), _p(dwc), _p(db), _p(ws), ws.numel(),
                                       _stream()), "cnb_conv2d_wgrad(input)")
         dw = dwc[:, :rsc].view(k, r, s, c).permute(0, 3, 1, 2)
-        return None, dw, db, None, None, None, None
+        return None, dw, db, None, None, None, None, None
 
 
-def conv2d_input(x, weight, bias=None, stride=1, padding=0, dilation=1, dtype=torch.bfloat16):
+def conv2d_input(x, weight, bias=None, stride=1, padding=0, dilation=1, dtype=torch.bfloat16,
+                 bn_stats=False):
     """The network's first convolution applied to the fp32 NCHW batch (reference
     src/basemodel.py:185-188 feeds `self(inputs)` with it); see _InputConvFn."""
-    return _InputConvFn.apply(x, weight, bias, _pair(stride), _pair(padding), _pair(dilation), dtype)
+    y, part = _InputConvFn.apply(x, weight, bias, _pair(stride), _pair(padding), _pair(dilation),
+                                 dtype, bool(bn_stats))
+    if bn_stats:
+        return y, (part if part.shape[0] > 0 else None)
+    return y
 
 
 def conv2d_uses_tc(x_shape, w_shape, stride, padding, dilation, groups, dtype, direction) -> bool:
@@ -273,7 +291,7 @@ def conv2d_uses_tc(x_shape, w_shape, stride, padding, dilation, groups, dtype, d
 class _BatchNormFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps,
-                relu):
+                relu, partials):
         _cuda(x, residual, gamma, beta)
         lib = _L.load()
         x = _nhwc(x)
@@ -294,10 +312,21 @@ class _BatchNormFn(torch.autograd.Function):
                     f"Expected more than 1 value per channel when training, got input size {list(x.shape)}")
             mean = torch.empty(c, dtype=torch.float32, device=x.device)
             rstd = torch.empty(c, dtype=torch.float32, device=x.device)
+            nparts = 0
+            if partials is not None:
+                if tuple(partials.shape[1:]) != (2, c) or partials.dtype != torch.float32:
+                    raise RuntimeError("batch_norm: conv partials do not belong to this input")
+                nparts = partials.shape[0]
+            # ReLU mask: 1 bit per element instead of re-reading y in backward
+            mask = None
+            if relu and x.dtype == torch.bfloat16 and c % 8 == 0:
+                mask = torch.empty(n * h * w * c // 8, dtype=torch.uint8, device=x.device)
             _L.check(lib.cnb_bn_fwd_train(C.byref(d), _p(x), _p(residual), _p(g32), _p(b32),
                                           _p(running_mean), _p(running_var), _p(y), _p(mean),
-                                          _p(rstd), _p(ws), ws.numel(), _stream()), "cnb_bn_fwd_train")
-            ctx.save_for_backward(x, y if relu else None, g32, mean, rstd)
+                                          _p(rstd), _p(partials), nparts, _p(mask), _p(ws),
+                                          ws.numel(), _stream()), "cnb_bn_fwd_train")
+            ctx.save_for_backward(x, (y if mask is None else None) if relu else None, mask, g32,
+                                  mean, rstd)
         else:
             _L.check(lib.cnb_bn_fwd_eval(C.byref(d), _p(x), _p(residual), _p(g32), _p(b32),
                                          _p(running_mean), _p(running_var), _p(y), _p(ws), ws.numel(),
@@ -316,7 +345,7 @@ class _BatchNormFn(torch.autograd.Function):
                 "backward through inference-mode BatchNorm is not part of the reference hot path "
                 "(valid_model runs under no_grad, src/basemodel.py:304)")
         lib = _L.load()
-        x, y, gamma, mean, rstd = ctx.saved_tensors
+        x, y, mask, gamma, mean, rstd = ctx.saved_tensors
         d = ctx.desc
         dy = _nhwc(dy)
         if dy.dtype != x.dtype:
@@ -327,17 +356,19 @@ class _BatchNormFn(torch.autograd.Function):
         dgamma = torch.empty(c, dtype=torch.float32, device=x.device) if ctx.affine else None
         dbeta = torch.empty(c, dtype=torch.float32, device=x.device) if ctx.affine else None
         ws = _workspace(lib.cnb_bn_workspace_bytes(C.byref(d)), x.device)
-        _L.check(lib.cnb_bn_bwd(C.byref(d), _p(x), _p(y), _p(dy), _p(gamma), _p(mean), _p(rstd),
-                                _p(dx), _p(dres), _p(dgamma), _p(dbeta), _p(ws), ws.numel(),
+        _L.check(lib.cnb_bn_bwd(C.byref(d), _p(x), _p(y), _p(mask), _p(dy), _p(gamma), _p(mean),
+                                _p(rstd), _p(dx), _p(dres), _p(dgamma), _p(dbeta), _p(ws), ws.numel(),
                                 _stream()), "cnb_bn_bwd")
-        return dx, dres, dgamma, dbeta, None, None, None, None, None, None
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None
 
 
 def batch_norm(x, gamma, beta, running_mean, running_var, training, momentum=0.1, eps=1e-5,
-               relu=False, residual=None):
-    """Drop-in for F.batch_norm on NCHW feature maps (+ optional fused residual add / ReLU)."""
+               relu=False, residual=None, partials=None):
+    """Drop-in for F.batch_norm on NCHW feature maps (+ optional fused residual add / ReLU).
+    `partials`: the per-tile sums the producing conv2d(..., bn_stats=True) emitted for x."""
     return _BatchNormFn.apply(x, residual, gamma, beta, running_mean, running_var, bool(training),
-                              float(momentum), float(eps), bool(relu))
+                              float(momentum), float(eps), bool(relu),
+                              partials if training else None)
 
 
 # ----------------------------------------------------------------------------- element-wise

@@ -23,6 +23,18 @@ class Conv2d(nn.Conv2d):
     # network entry (its fp32 NCHW input batch is converted to `compute_dtype` NHWC first)
     compute_dtype = None
     cast_input = False
+    # set by convert() when the next module is a BatchNorm2d: the forward epilogue then also emits
+    # the per-tile sums that BatchNorm's statistics pass would otherwise re-read the output for
+    emit_bn_stats = False
+
+    @staticmethod
+    def _tag(out):
+        if isinstance(out, tuple):
+            y, part = out
+            if part is not None:
+                y._cnb_bn_partials = part
+            return y
+        return out
 
     def _packed(self, dtype: torch.dtype, c_dst=None) -> torch.Tensor:
         w = self.weight
@@ -36,16 +48,18 @@ class Conv2d(nn.Conv2d):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if self.padding_mode != "zeros" or isinstance(self.padding, str):
             raise NotImplementedError("convnets_b200.Conv2d supports integer zero padding only")
+        stats = self.emit_bn_stats and self.training
         if self.cast_input and self.compute_dtype is not None and not x.requires_grad:
             # network entry: fp32 NCHW batch -> compute dtype NHWC.  A stem whose channel count
             # cannot feed the tensor-core path (RGB: 16-byte TMA rows need C % 8 == 0) goes through
             # an explicit im2col + GEMM instead of the CUDA-core kernel.
             if self.compute_dtype == torch.bfloat16 and self.groups == 1 and x.shape[1] % 8:
-                return F_.conv2d_input(x, self.weight, self.bias, self.stride, self.padding,
-                                       self.dilation, self.compute_dtype)
+                return self._tag(F_.conv2d_input(x, self.weight, self.bias, self.stride, self.padding,
+                                                 self.dilation, self.compute_dtype, bn_stats=stats))
             x = F_.to_nhwc(x, self.compute_dtype)
-        return F_.conv2d(x, self.weight, self.bias, self.stride, self.padding, self.dilation,
-                         self.groups, wpack=self._packed(x.dtype), algo=self.algo)
+        return self._tag(F_.conv2d(x, self.weight, self.bias, self.stride, self.padding,
+                                   self.dilation, self.groups, wpack=self._packed(x.dtype),
+                                   algo=self.algo, bn_stats=stats))
 
 
 class BatchNorm2d(nn.BatchNorm2d):
@@ -65,8 +79,10 @@ class BatchNorm2d(nn.BatchNorm2d):
                 momentum = 1.0 / float(self.num_batches_tracked)
         rm = self.running_mean if (not training or self.track_running_stats) else None
         rv = self.running_var if (not training or self.track_running_stats) else None
+        partials = getattr(x, "_cnb_bn_partials", None) if training else None
         return F_.batch_norm(x, self.weight, self.bias, rm, rv, training, momentum, self.eps,
-                             relu=self.fuse_relu if relu is None else relu, residual=residual)
+                             relu=self.fuse_relu if relu is None else relu, residual=residual,
+                             partials=partials)
 
 
 class ReLU(nn.ReLU):

@@ -49,13 +49,15 @@ SIGNATURES = {
     "cnb_conv2d_out_dims": (_I, [C.POINTER(ConvDesc), C.POINTER(_I32), C.POINTER(_I32)]),
     "cnb_conv2d_uses_tc": (_I, [C.POINTER(ConvDesc), _I]),
     "cnb_conv2d_workspace_bytes": (_SZ, [C.POINTER(ConvDesc), _I]),
-    "cnb_conv2d_fwd": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _SZ, _P]),
+    "cnb_conv2d_bn_partial_rows": (_I, [C.POINTER(ConvDesc)]),
+    "cnb_conv2d_fwd": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_conv2d_dgrad": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _SZ, _P]),
     "cnb_conv2d_wgrad": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_bn_workspace_bytes": (_SZ, [C.POINTER(BnDesc)]),
-    "cnb_bn_fwd_train": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
+    "cnb_bn_fwd_train": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _P,
+                              _SZ, _P]),
     "cnb_bn_fwd_eval": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
-    "cnb_bn_bwd": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
+    "cnb_bn_bwd": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_relu_fwd": (_I, [_P, _P, _I64, _I, _P]),
     "cnb_relu_bwd": (_I, [_P, _P, _P, _I64, _I, _P]),
     "cnb_add_relu_fwd": (_I, [_P, _P, _P, _I64, _I, _P]),
@@ -137,7 +139,8 @@ class _Calls:
 
 
 _NO_STREAM = {"cnb_version", "cnb_last_error", "cnb_launch_count", "cnb_conv2d_out_dims",
-              "cnb_conv2d_uses_tc", "cnb_conv2d_workspace_bytes", "cnb_bn_workspace_bytes"}
+              "cnb_conv2d_uses_tc", "cnb_conv2d_workspace_bytes", "cnb_bn_workspace_bytes",
+              "cnb_conv2d_bn_partial_rows"}
 
 
 def _describe(args):

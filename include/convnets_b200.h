@@ -102,9 +102,15 @@ int cnb_conv2d_out_dims(const cnb_conv_desc* d, int32_t* P, int32_t* Q);
 /* 1 if the tcgen05 tensor-core path would run for this direction, 0 for CUDA cores, <0 error */
 int cnb_conv2d_uses_tc(const cnb_conv_desc* d, int direction);
 size_t cnb_conv2d_workspace_bytes(const cnb_conv_desc* d, int direction);
-/* y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R,S,C/g]) (+ bias[K] fp32) (ReLU) */
+/* rows of the BatchNorm partial-sum table the forward epilogue can emit for this problem (one row
+ * per 128-pixel output tile), or 0 when this conv runs on a path that cannot (CUDA cores). */
+int cnb_conv2d_bn_partial_rows(const cnb_conv_desc* d);
+/* y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R,S,C/g]) (+ bias[K] fp32) (ReLU).
+ * bn_partials (may be NULL): fp32 [rows][2][K] receives, per output tile, the per-channel sum and
+ * sum of squares of the STORED (rounded) outputs — the statistics pass of the BatchNorm2d that
+ * follows the conv in conv2d_block (reference src/basemodel.py:1004-1010), fused into the epilogue. */
 int cnb_conv2d_fwd(const cnb_conv_desc* d, const void* x, const void* w, const float* bias, void* y,
-                   void* workspace, size_t workspace_bytes, void* stream);
+                   float* bn_partials, void* workspace, size_t workspace_bytes, void* stream);
 /* dx[N,H,W,C] = conv_transpose(dy[N,P,Q,K], w) */
 int cnb_conv2d_dgrad(const cnb_conv_desc* d, const void* dy, const void* w, void* dx,
                      void* workspace, size_t workspace_bytes, void* stream);
@@ -116,19 +122,24 @@ int cnb_conv2d_wgrad(const cnb_conv_desc* d, const void* x, const void* dy, floa
 size_t cnb_bn_workspace_bytes(const cnb_bn_desc* d);
 /* training forward: batch statistics (biased var for normalisation, unbiased for running_var),
  * running-stat update, y = [relu]((x-mean)*rstd*gamma + beta [+ residual]).
- * save_mean / save_rstd: fp32 [C] outputs kept for backward. */
+ * save_mean / save_rstd: fp32 [C] outputs kept for backward.
+ * conv_partials / n_partials (may be NULL / 0): the table written by cnb_conv2d_fwd for x; when
+ *   given, x is not read for the statistics.
+ * relu_mask (may be NULL; needs CNB_BN_RELU, bf16, C % 8 == 0): M*C/8 bytes, bit j of byte
+ *   (m*C + c)/8 = (y[m][c + j] > 0); backward can take it instead of y. */
 int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, const float* gamma,
                      const float* beta, float* running_mean, float* running_var, void* y,
-                     float* save_mean, float* save_rstd, void* workspace, size_t workspace_bytes,
+                     float* save_mean, float* save_rstd, const float* conv_partials,
+                     int32_t n_partials, void* relu_mask, void* workspace, size_t workspace_bytes,
                      void* stream);
 /* inference forward with running statistics */
 int cnb_bn_fwd_eval(const cnb_bn_desc* d, const void* x, const void* residual, const float* gamma,
                     const float* beta, const float* running_mean, const float* running_var, void* y,
                     void* workspace, size_t workspace_bytes, void* stream);
-/* backward of the training forward.  y is the forward output (needed only with CNB_BN_RELU, for
- * the mask y > 0); d_residual (may be NULL) receives the masked upstream gradient. */
-int cnb_bn_bwd(const cnb_bn_desc* d, const void* x, const void* y, const void* dy,
-               const float* gamma, const float* save_mean, const float* save_rstd, void* dx,
+/* backward of the training forward.  With CNB_BN_RELU the mask y > 0 comes from relu_mask when it
+ * is given (1 bit per element), else from the forward output y; d_residual (may be NULL) receives the masked upstream gradient. */
+int cnb_bn_bwd(const cnb_bn_desc* d, const void* x, const void* y, const void* relu_mask,
+               const void* dy, const float* gamma, const float* save_mean, const float* save_rstd, void* dx,
                void* d_residual, float* dgamma, float* dbeta, void* workspace,
                size_t workspace_bytes, void* stream);
 

@@ -305,3 +305,42 @@ def test_conv2d_input_im2col(case):
     assert O.rel_l2(wd.grad, dw_ref) <= 1e-2
     if b is not None:
         assert O.rel_l2(bd.grad, db_ref) <= 1e-2
+
+
+# ------------------------------------------------------------------ conv-epilogue statistics
+@pytest.mark.parametrize("shape,k,ks,stride", [((4, 64, 14, 14), 256, 1, 1), ((3, 128, 9, 9), 96, 3, 1),
+                                              ((2, 64, 15, 15), 64, 3, 2), ((8, 256, 7, 7), 512, 1, 1)])
+@pytest.mark.parametrize("relu,res", [(True, False), (True, True), (False, False)])
+def test_conv_bn_partials_and_relu_mask(shape, k, ks, stride, relu, res):
+    """conv2d(bn_stats=True) emits per-tile sums of the stored output; BatchNorm fed with them
+    (and using the 1-bit ReLU mask in backward) must agree with the oracle on the same conv
+    output, forward and backward."""
+    f = F_()
+    dt = torch.bfloat16
+    n, c, h, w = shape
+    x = rnd(*shape, dtype=dt)
+    wt = rnd(k, c, ks, ks, scale=(2.0 / (c * ks * ks)) ** 0.5)
+    xd, wd = dev(x), dev(wt)
+    y, part = f.conv2d(xd, wd, None, stride, ks // 2, 1, 1, wpack=f.pack_weight(wd, dt), bn_stats=True)
+    assert part is not None and part.shape[1:] == (2, k)
+    yf = y.float()
+    assert O.rel_l2(part[:, 0].sum(0), yf.sum(dim=(0, 2, 3))) <= 1e-4
+    assert O.rel_l2(part[:, 1].sum(0), (yf * yf).sum(dim=(0, 2, 3))) <= 1e-4
+    g, b = 1.0 + 0.2 * torch.randn(k), 0.1 * torch.randn(k)
+    rm, rv = torch.zeros(k), torch.ones(k)
+    r = rnd(*y.shape, dtype=dt) if res else None
+    yin = y.detach().clone().requires_grad_(True)
+    gd, bd = dev(g, True), dev(b, True)
+    rd = dev(r, True) if res else None
+    rmd, rvd = rm.cuda(), rv.cuda()
+    out = f.batch_norm(yin, gd, bd, rmd, rvd, True, 0.1, 1e-5, relu=relu, residual=rd, partials=part)
+    want, rm2, rv2, _, _ = O.batch_norm_train(y, g, b, rm, rv, relu=relu, residual=r, storage=dt)
+    assert O.rel_l2(out, want) <= 1e-2
+    assert O.rel_l2(rmd, rm2) <= 1e-3 and O.rel_l2(rvd, rv2) <= 1e-3
+    dy = rnd(*y.shape, dtype=dt)
+    out.backward(dev(dy))
+    dx, dg, db, dr = O.batch_norm_train_grads(y, g, b, dy, relu=relu, residual=r, storage=dt)
+    assert O.rel_l2(yin.grad, dx) <= 1e-2
+    assert O.rel_l2(gd.grad, dg) <= 1e-2 and O.rel_l2(bd.grad, db) <= 1e-2
+    if res:
+        assert O.rel_l2(rd.grad, dr) <= 1e-2
