@@ -293,7 +293,9 @@ bn_apply_k(const T* __restrict__ x, const T* __restrict__ res, const float* __re
   const int cv = blockIdx.x * blockDim.x + threadIdx.x;
   const int c0 = cv * V;
   if (c0 >= C) return;
-  const int64_t r0 = blockIdx.y * rows_per_split;
+  // Row blocks are walked from the END of the tensor: x was just written front-to-back by the
+  // producing kernel, so its tail is what the 126 MB L2 still holds when this kernel starts.
+  const int64_t r0 = (int64_t)(gridDim.y - 1 - blockIdx.y) * rows_per_split;
   int64_t r1 = r0 + rows_per_split;
   if (r1 > M) r1 = M;
   float sc[V], sh[V];
@@ -351,7 +353,9 @@ bn_bwd_reduce_k(const T* __restrict__ x, const T* __restrict__ y, const uint8_t*
   extern __shared__ __align__(16) float red[];
   const int cv = blockIdx.x * blockDim.x + threadIdx.x;
   const int c0 = cv * V;
-  const int64_t r0 = blockIdx.y * rows_per_split;
+  // reversed walk: dy was just written front-to-back (its tail is in L2), and the rows this pass
+  // touches last — the front — are the ones bn_bwd_dx_k, walking forward, asks for first
+  const int64_t r0 = (int64_t)(gridDim.y - 1 - blockIdx.y) * rows_per_split;
   int64_t r1 = r0 + rows_per_split;
   if (r1 > M) r1 = M;
   float s[V], q[V], mu[V];

@@ -168,8 +168,8 @@ size_t conv_tc_workspace(const cnb_conv_desc& d, int direction);
 int conv_tc_fwd(const cnb_conv_desc& d, const void* x, const void* w, const float* bias, void* y,
                 float* stats, void* ws, size_t ws_bytes, cudaStream_t st);
 int conv_tc_stats_rows(const cnb_conv_desc& d);
-int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, void* dx, void* ws,
-                  size_t ws_bytes, cudaStream_t st);
+int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const void* w_t, void* dx,
+                  void* ws, size_t ws_bytes, cudaStream_t st);
 int conv_tc_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* dw, void* ws,
                   size_t ws_bytes, cudaStream_t st);
 

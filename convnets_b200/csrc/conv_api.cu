@@ -104,7 +104,7 @@ int cnb_conv2d_fwd(const cnb_conv_desc* d, const void* x, const void* w, const f
   return conv_simt_fwd(*d, x, w, (d->flags & CNB_CONV_BIAS) ? bias : nullptr, y, st);
 }
 
-int cnb_conv2d_dgrad(const cnb_conv_desc* d, const void* dy, const void* w, void* dx,
+int cnb_conv2d_dgrad(const cnb_conv_desc* d, const void* dy, const void* w, const void* w_t, void* dx,
                      void* workspace, size_t workspace_bytes, void* stream) {
   CNB_TRY(validate_conv(d, "cnb_conv2d_dgrad"));
   CNB_REQUIRE(dy && w && dx, CNB_ERR_INVALID, "cnb_conv2d_dgrad: null tensor pointer");
@@ -115,7 +115,9 @@ int cnb_conv2d_dgrad(const cnb_conv_desc* d, const void* dy, const void* w, void
   if (a == 1) {
     CNB_REQUIRE(((uintptr_t)dy | (uintptr_t)w | (uintptr_t)dx) % 16 == 0, CNB_ERR_INVALID,
                 "cnb_conv2d_dgrad: tensor pointers must be 16-byte aligned for TMA");
-    return conv_tc_dgrad(*d, dy, w, dx, workspace, workspace_bytes, st);
+    CNB_REQUIRE(!w_t || (uintptr_t)w_t % 16 == 0, CNB_ERR_INVALID,
+                "cnb_conv2d_dgrad: w_t must be 16-byte aligned");
+    return conv_tc_dgrad(*d, dy, w, w_t, dx, workspace, workspace_bytes, st);
   }
   return conv_simt_dgrad(*d, dy, w, dx, st);
 }

@@ -31,6 +31,7 @@ using namespace sm100;
 
 constexpr int kMaxTaps = 49;
 constexpr int kTcThreads = 192;
+constexpr int kPersistThreads = 320;  // persistent fprop: producer, MMA and 8 epilogue warps
 constexpr int TILE_M = 128;   // pixels per CTA tile (fprop) / out-channels per CTA tile (wgrad)
 constexpr int TILE_K = 64;    // bf16 elements per 128-byte swizzle row
 constexpr int A_TILE_BYTES = TILE_M * TILE_K * 2;  // 16 KB
@@ -300,7 +301,7 @@ conv_fprop_tc_k(const __grid_constant__ FpropParams p) {
 // pipeline fill, exposed epilogue) are paid once per SM instead of once per tile, which is what
 // the short-reduction layers (1x1 with few channels, 3x3 on 64 channels) were bound by.
 template <int BLOCK_N, int STAGES, bool IM2COL>
-__global__ void __launch_bounds__(kTcThreads, 1)
+__global__ void __launch_bounds__(kPersistThreads, 1)
 conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
   constexpr int B_TILE_BYTES = BLOCK_N * TILE_K * 2;
   constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
@@ -332,7 +333,7 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tmem_full_bar[b], 1);
-      mbar_init(&tmem_empty_bar[b], 128);
+      mbar_init(&tmem_empty_bar[b], kPersistThreads - 64);
     }
     fence_barrier_init();
   }
@@ -409,8 +410,12 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
       }
     }
   } else {
-    // ===================== epilogue (warps 2..5) =====================
+    // ===================== epilogue (warps 2..9) =====================
+    // A warp can only read the TMEM lane quarter (warp % 4); two warps share each quarter and
+    // take one half of the tile's columns each, so the drain keeps up with one-k-block tiles.
     const int quarter = warp % 4;
+    const int chalf = (warp - 2) / 4;
+    constexpr int HALF_N = BLOCK_N / 2;
     const int row = quarter * 32 + lane;
     const bool storer = (warp == 2 && lane == 0);
     uint32_t lt = 0;
@@ -422,9 +427,9 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
       tc_fence_after();
       // the previous tile's TMA store must have finished READING the staging buffer
       if (storer) tma_store_wait_read0();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
 #pragma unroll 1
-      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
+      for (int c0 = chalf * HALF_N; c0 < (chalf + 1) * HALF_N; c0 += 32) {
         uint32_t v[32];
         tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * BLOCK_N + (uint32_t)c0, v);
         tmem_ld_wait();
@@ -457,7 +462,7 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
       tc_fence_before();
       mbar_arrive(&tmem_empty_bar[buf]);
       fence_proxy_async_smem();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync 1, 256;" ::: "memory");
       if (storer) {
         for (int b = 0; b < BLOCK_N / 64; ++b) {
           if (n0 + b * 64 < p.Kout)
@@ -469,15 +474,18 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
         // BatchNorm statistics of this tile from the staged (bf16-rounded, i.e. as stored) values:
         // each thread owns a pair of adjacent columns and walks the rows of the swizzled boxes.
         // One fp32 partial row per m-tile -> merged in fixed order by bn_partials_k (deterministic).
-        const int rows = min(TILE_M, p.M - m0);
-        float* dst = p.stats + (size_t)(tile / p.n_tiles) * 2 * p.Kout;
-        for (int pr = (int)threadIdx.x - 64; pr < BLOCK_N / 2; pr += 128) {
+        // Two partial rows per m-tile: threads 0..127 sum tile rows 0..63, threads 128..255 rows 64..127.
+        const int e = (int)threadIdx.x - 64;
+        const int rbeg = (e / 128) * (TILE_M / 2);
+        const int rows = min(rbeg + TILE_M / 2, p.M - m0);
+        float* dst = p.stats + ((size_t)(tile / p.n_tiles) * 2 + (e / 128)) * 2 * p.Kout;
+        for (int pr = e % 128; pr < BLOCK_N / 2; pr += 128) {
           const int c = pr * 2;
           const uint8_t* colp = stage_out + (c / 64) * (TILE_M * 128) + (c % 8) * 2;
           const int chunk = (c % 64) / 8;
           float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll 8
-          for (int r = 0; r < rows; ++r) {
+          for (int r = rbeg; r < rows; ++r) {
             const uint32_t w2 = *reinterpret_cast<const uint32_t*>(colp + r * 128 + ((chunk ^ (r & 7)) * 16));
             const float a = __uint_as_float(w2 << 16), b = __uint_as_float(w2 & 0xffff0000u);
             s0 += a; q0 = fmaf(a, a, q0);
@@ -504,6 +512,7 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
 struct WgradParams {
   CUtensorMap tmDy;  // {K, M} tiled, box {64 out-ch, 64 pixels}
   CUtensorMap tmX;   // im2col {C,W,H,N}, box 64 ch x 64 pixels (or tiled {C, M} for 1x1 s1 p0)
+  CUtensorMap tmOut; // fp32 {Cg, RS, K, splits}, box {32, 1, 128, 1}: coalesced epilogue stores
   float* out;        // [splits][K][RS][Cg] partials (or dw itself when splits == 1)
   int M;             // output pixels N*P*Q
   int outP, outQ, lower_h, lower_w, trav_h, trav_w;
@@ -558,6 +567,7 @@ conv_wgrad_tc_k(const __grid_constant__ WgradParams p) {
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmDy);
     tma_prefetch_desc(&p.tmX);
+    tma_prefetch_desc(&p.tmOut);
     for (int s = 0; s < SA; ++s) { mbar_init(&fullA[s], 1); mbar_init(&emptyA[s], 1); }
     for (int s = 0; s < SB; ++s) { mbar_init(&fullB[s], 1); mbar_init(&emptyB[s], 1); }
     mbar_init(tmem_full_bar, 1);
@@ -641,16 +651,22 @@ conv_wgrad_tc_k(const __grid_constant__ WgradParams p) {
       }
     }
   } else {
+    // Epilogue: TMEM -> registers -> swizzled fp32 staging (the operand rings are idle by now:
+    // every load has landed and every MMA that read them has completed) -> TMA stores.  One
+    // [128 out-ch x 32 in-ch] box per store: full 128-byte rows instead of the 4-byte scattered
+    // writes a row-per-thread store pattern would issue; rows >= K and columns >= Cg are clipped
+    // by the tensor map.
     const int quarter = warp % 4;
     const int row = quarter * 32 + lane;  // out-channel within the tile
-    const int ko = cout0 + row;
+    const bool storer = (warp == 2 && lane == 0);
     if (npb > 0) {
       mbar_wait(tmem_full_bar, 0);
       tc_fence_after();
     }
-    const int64_t wsz = (int64_t)p.K * p.RS * p.Cg;
-    float* outp = p.out + (int64_t)split * wsz;
+    uint8_t* staging = smem;
     for (int tp = 0; tp < ntap; ++tp) {
+      if (storer) tma_store_wait_read0();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
 #pragma unroll 1
       for (int c0 = 0; c0 < NT; c0 += 32) {
         uint32_t v[32];
@@ -661,14 +677,24 @@ conv_wgrad_tc_k(const __grid_constant__ WgradParams p) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = 0u;
         }
-        if (ko < p.K) {
-          float* dst = outp + ((int64_t)ko * p.RS + (tap0 + tp)) * p.Cg + cin0 + c0;
+        uint8_t* box = staging + (c0 / 32) * (TILE_M * 128);
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (cin0 + c0 + j < p.Cg) dst[j] = __uint_as_float(v[j]);
+        for (int j = 0; j < 8; ++j) {
+          uint4* dst = reinterpret_cast<uint4*>(box + row * 128 + ((j ^ (row & 7)) * 16));
+          *dst = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
         }
       }
+      fence_proxy_async_smem();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (storer) {
+        for (int c0 = 0; c0 < NT; c0 += 32)
+          if (cin0 + c0 < p.Cg)
+            tma_store_4d(&p.tmOut, staging + (c0 / 32) * (TILE_M * 128), cin0 + c0, tap0 + tp, cout0,
+                         split);
+        tma_store_commit();
+      }
     }
+    if (storer) tma_store_wait0();
     tc_fence_before();
   }
   __syncthreads();
@@ -786,7 +812,7 @@ static int launch_fprop_persist_inst(const FpropParams& prm, cudaStream_t st) {
     attr_done = true;
   }
   const int grid = prm.num_tiles < sm_count() ? prm.num_tiles : sm_count();
-  kern<<<grid, kTcThreads, smem, st>>>(prm);
+  kern<<<grid, kPersistThreads, smem, st>>>(prm);
   return check_launch("conv_fprop_tc_persist");
 }
 
@@ -968,7 +994,7 @@ size_t conv_tc_workspace(const cnb_conv_desc& d, int direction) {
 int conv_tc_stats_rows(const cnb_conv_desc& d) {
   int P, Q;
   conv_out_dims(d, P, Q);
-  return (int)ceil_div((int64_t)d.N * P * Q, TILE_M);
+  return 2 * (int)ceil_div((int64_t)d.N * P * Q, TILE_M);  // two half-tile rows per 128-pixel tile
 }
 
 int conv_tc_fwd(const cnb_conv_desc& d, const void* x, const void* w, const float* bias, void* y,
@@ -1000,21 +1026,23 @@ int conv_tc_fwd(const cnb_conv_desc& d, const void* x, const void* w, const floa
   return launch_fprop(L, st);
 }
 
-int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, void* dx, void* ws,
-                  size_t ws_bytes, cudaStream_t st) {
+int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const void* w_t, void* dx,
+                  void* ws, size_t ws_bytes, cudaStream_t st) {
   CNB_REQUIRE(ws && ws_bytes >= conv_tc_workspace(d, CNB_DGRAD), CNB_ERR_WORKSPACE,
               "conv_tc_dgrad: workspace %zu < %zu", ws_bytes, conv_tc_workspace(d, CNB_DGRAD));
   int P, Q;
   conv_out_dims(d, P, Q);
   const int RS = d.R * d.S;
   // transposed filter wt[C][RS][K]
-  bf16* wt = reinterpret_cast<bf16*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
-  {
+  bf16* wt_ws = reinterpret_cast<bf16*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
+  const bf16* wt = reinterpret_cast<const bf16*>(w_t);
+  if (!wt) {  // no pre-transposed copy from cnb_pack_filter: build it in the workspace
     int64_t total = (int64_t)d.K * RS * d.C;
-    transpose_filter_k<<<grid_for(total, 256), 256, 0, st>>>((const bf16*)w, wt, d.K, RS, d.C);
+    transpose_filter_k<<<grid_for(total, 256), 256, 0, st>>>((const bf16*)w, wt_ws, d.K, RS, d.C);
     CNB_TRY(check_launch("transpose_filter"));
+    wt = wt_ws;
   }
-  uint8_t* tmp_base = reinterpret_cast<uint8_t*>(wt) + align_up((size_t)d.K * RS * d.C * 2, 1024);
+  uint8_t* tmp_base = reinterpret_cast<uint8_t*>(wt_ws) + align_up((size_t)d.K * RS * d.C * 2, 1024);
 
   if (d.stride_h == 1 && d.stride_w == 1) {
     FpropLaunch L;
@@ -1161,6 +1189,18 @@ int conv_tc_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* 
                             d.stride_w, d.stride_h, 64, "x(im2col)"));
   }
   prm.out = part;
+  {
+    cuuint64_t gdim[4] = {(cuuint64_t)d.C, (cuuint64_t)RS, (cuuint64_t)d.K,
+                          (cuuint64_t)(prm.splits > 1 ? prm.splits : 1)};
+    cuuint64_t gstr[3] = {(cuuint64_t)d.C * 4, (cuuint64_t)RS * d.C * 4, (cuuint64_t)wsz * 4};
+    cuuint32_t box[4] = {32, 1, (cuuint32_t)TILE_M, 1};
+    cuuint32_t es[4] = {1, 1, 1, 1};
+    CUresult r = g_encodeTiled(&prm.tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, part, gdim, gstr, box, es,
+                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CNB_REQUIRE(r == CUDA_SUCCESS, CNB_ERR_CUDA, "cuTensorMapEncodeTiled(wgrad out) failed: CUresult %d",
+                (int)r);
+  }
   prm.M = M;
   prm.outP = P; prm.outQ = Q;
   prm.lower_h = -d.pad_h; prm.lower_w = -d.pad_w;
@@ -1176,14 +1216,17 @@ int conv_tc_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* 
   CNB_REQUIRE(grid64 < (1ll << 31), CNB_ERR_UNSUPPORTED, "conv_tc_wgrad: grid too large");
   const int grid = (int)grid64;
   int s;
+  // Ring depths <dy stages, x stages>.  The producer is one thread walking pixel blocks in order
+  // (dy tile, then one x tile per tap), so it runs ahead by min(dy stages x taps per CTA, x stages)
+  // MMA groups: 1x1 layers (one tap per block) need as many dy stages as x stages.
   if (tiled2d) {
-    if (NT == 64) s = launch_wgrad_inst<64, 3, 4, false>(prm, grid, st);
-    else if (NT == 128) s = launch_wgrad_inst<128, 3, 4, false>(prm, grid, st);
-    else s = launch_wgrad_inst<256, 3, 3, false>(prm, grid, st);
+    if (NT == 64) s = launch_wgrad_inst<64, 8, 8, false>(prm, grid, st);
+    else if (NT == 128) s = launch_wgrad_inst<128, 6, 6, false>(prm, grid, st);
+    else s = launch_wgrad_inst<256, 4, 4, false>(prm, grid, st);
   } else {
-    if (NT == 64) s = launch_wgrad_inst<64, 3, 6, true>(prm, grid, st);
-    else if (NT == 128) s = launch_wgrad_inst<128, 3, 4, true>(prm, grid, st);
-    else s = launch_wgrad_inst<256, 3, 3, true>(prm, grid, st);
+    if (NT == 64) s = launch_wgrad_inst<64, 3, 16, true>(prm, grid, st);
+    else if (NT == 128) s = launch_wgrad_inst<128, 3, 10, true>(prm, grid, st);
+    else s = launch_wgrad_inst<256, 3, 5, true>(prm, grid, st);
   }
   CNB_TRY(s);
   if (prm.splits > 1) {

@@ -461,6 +461,26 @@ static RedGeom red_geom(int N, int C, int V, int planes) {
   return g;
 }
 
+// fp32 master filter [K][RS][C] -> bf16 operand copy in the same layout and, optionally, the copy
+// with in/out channels exchanged [C][RS][K] that data-grad consumes: one pass over the weights
+// per optimiser step instead of a cast kernel plus a transpose inside every data-grad call.
+__global__ void pack_filter_k(const float* __restrict__ w, bf16* __restrict__ wb, bf16* __restrict__ wt,
+                              int K, int RS, int C) {
+  const int64_t total = (int64_t)K * RS * C;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const bf16 v = __float2bfloat16_rn(w[i]);
+    wb[i] = v;
+    if (wt) {
+      const int c = (int)(i % C);
+      const int64_t t = i / C;
+      const int rs = (int)(t % RS);
+      const int k = (int)(t / RS);
+      wt[((int64_t)c * RS + rs) * K + k] = v;
+    }
+  }
+}
+
 }  // namespace cnb
 
 using namespace cnb;
@@ -515,6 +535,15 @@ int cnb_add(const void* a, const void* b, void* y, int64_t n, int dtype, void* s
                   (add_k<T, V, false><<<grid_for(n / V, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
                       (const T*)a, (const T*)b, (T*)y, n / V)));
   return check_launch("add");
+}
+
+int cnb_pack_filter(const float* w, void* w_bf16, void* wt_bf16, int32_t K, int32_t RS, int32_t C,
+                    void* stream) {
+  CNB_REQUIRE(w && w_bf16 && K > 0 && RS > 0 && C > 0, CNB_ERR_INVALID, "cnb_pack_filter: bad args");
+  const int64_t n = (int64_t)K * RS * C;
+  pack_filter_k<<<grid_for(n, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
+      w, (bf16*)w_bf16, (bf16*)wt_bf16, K, RS, C);
+  return check_launch("pack_filter");
 }
 
 int cnb_cast(const void* src, int sdt, void* dst, int ddt, int64_t n, void* stream) {

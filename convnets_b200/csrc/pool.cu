@@ -21,7 +21,7 @@ struct PoolP {
 // that each thread keeps K*K independent 16-byte requests in flight; K == 0: runtime loops.
 template <typename T, int V, int K>
 __global__ void maxpool_fwd_k(const T* __restrict__ x, T* __restrict__ y, int32_t* __restrict__ idx,
-                              PoolP p, int64_t total_vec) {
+                              uint8_t* __restrict__ code, PoolP p, int64_t total_vec) {
   const int Cv = p.C / V;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
        i += (int64_t)gridDim.x * blockDim.x) {
@@ -32,6 +32,7 @@ __global__ void maxpool_fwd_k(const T* __restrict__ x, T* __restrict__ y, int32_
     int oh = (int)(t % p.P);
     int n = (int)(t / p.P);
     int h0 = oh * p.sh - p.ph, w0 = q * p.sw - p.pw;
+    const int hs = h0, ws = w0;  // un-clamped window origin (the 1-byte code is relative to it)
     int h1 = min(h0 + p.kh, p.H), w1 = min(w0 + p.kw, p.W);
     h0 = max(h0, 0);
     w0 = max(w0, 0);
@@ -80,14 +81,28 @@ __global__ void maxpool_fwd_k(const T* __restrict__ x, T* __restrict__ y, int32_
         }
     }
     Pack<T, V> o;
-    Pack<int32_t, V> oi;
 #pragma unroll
-    for (int j = 0; j < V; ++j) {
-      o.v[j] = from_f<T>(best[j]);
-      oi.v[j] = bi[j];
-    }
+    for (int j = 0; j < V; ++j) o.v[j] = from_f<T>(best[j]);
     st_pack<T, V>(y + i * V, o);
-    st_pack<int32_t, V>(idx + i * V, oi);
+    if (idx) {
+#pragma unroll
+      for (int j0 = 0; j0 < V; j0 += 4) {
+        constexpr int W4 = V < 4 ? V : 4;
+        Pack<int32_t, W4> oi;
+#pragma unroll
+        for (int j = 0; j < W4; ++j) oi.v[j] = bi[j0 + j];
+        st_pack<int32_t, W4>(idx + i * V + j0, oi);
+      }
+    }
+    if (code) {
+      Pack<uint8_t, V> oc;
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        const int bh = bi[j] / p.W, bw = bi[j] - bh * p.W;
+        oc.v[j] = (uint8_t)((bh - hs) * p.kw + (bw - ws));
+      }
+      st_pack<uint8_t, V>(code + i * V, oc);
+    }
   }
 }
 
@@ -96,7 +111,8 @@ __global__ void maxpool_fwd_k(const T* __restrict__ x, T* __restrict__ y, int32_
 // index / gradient loads are all issued before the compares.  NW == 0: runtime loops.
 template <typename T, int V, int NW>
 __global__ void maxpool_bwd_k(const T* __restrict__ dy, const int32_t* __restrict__ idx,
-                              T* __restrict__ dx, PoolP p, int64_t total_vec) {
+                              const uint8_t* __restrict__ code, T* __restrict__ dx, PoolP p,
+                              int64_t total_vec) {
   const int Cv = p.C / V;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
        i += (int64_t)gridDim.x * blockDim.x) {
@@ -118,35 +134,52 @@ __global__ void maxpool_bwd_k(const T* __restrict__ dy, const int32_t* __restric
 #pragma unroll
     for (int j = 0; j < V; ++j) acc[j] = 0.f;
     if (NW > 0) {
-      Pack<int32_t, V> ii[NW > 0 ? NW * NW : 1];
+      Pack<uint8_t, V> cc[NW > 0 ? NW * NW : 1];
       Pack<T, V> g[NW > 0 ? NW * NW : 1];
+      if (code) {
+        // 1-byte window-relative argmax codes: this pixel is position
+        // (h - (oh*sh - ph)) * kw + (w - (ow*sw - pw)) of window (oh, ow)
 #pragma unroll
-      for (int a = 0; a < NW; ++a)
+        for (int a = 0; a < NW; ++a)
 #pragma unroll
-        for (int b = 0; b < NW; ++b)
-          if (oh_lo + a <= oh_hi && ow_lo + b <= ow_hi) {
-            int64_t o = (((int64_t)n * p.P + oh_lo + a) * p.Q + ow_lo + b) * p.C + cv * V;
-            ii[a * NW + b] = ld_pack<int32_t, V>(idx + o);
-            g[a * NW + b] = ld_pack<T, V>(dy + o);
-          }
+          for (int b = 0; b < NW; ++b)
+            if (oh_lo + a <= oh_hi && ow_lo + b <= ow_hi) {
+              int64_t o = (((int64_t)n * p.P + oh_lo + a) * p.Q + ow_lo + b) * p.C + cv * V;
+              cc[a * NW + b] = ld_pack<uint8_t, V>(code + o);
+              g[a * NW + b] = ld_pack<T, V>(dy + o);
+            }
 #pragma unroll
-      for (int a = 0; a < NW; ++a)
+        for (int a = 0; a < NW; ++a)
 #pragma unroll
-        for (int b = 0; b < NW; ++b)
-          if (oh_lo + a <= oh_hi && ow_lo + b <= ow_hi) {
+          for (int b = 0; b < NW; ++b)
+            if (oh_lo + a <= oh_hi && ow_lo + b <= ow_hi) {
+              const int mine = (h - ((oh_lo + a) * p.sh - p.ph)) * p.kw + (w - ((ow_lo + b) * p.sw - p.pw));
 #pragma unroll
-            for (int j = 0; j < V; ++j)
-              if (ii[a * NW + b].v[j] == me) acc[j] += to_f(g[a * NW + b].v[j]);
-          }
+              for (int j = 0; j < V; ++j)
+                if ((int)cc[a * NW + b].v[j] == mine) acc[j] += to_f(g[a * NW + b].v[j]);
+            }
+      } else {
+#pragma unroll
+        for (int a = 0; a < NW; ++a)
+#pragma unroll
+          for (int b = 0; b < NW; ++b)
+            if (oh_lo + a <= oh_hi && ow_lo + b <= ow_hi) {
+              int64_t o = (((int64_t)n * p.P + oh_lo + a) * p.Q + ow_lo + b) * p.C + cv * V;
+#pragma unroll
+              for (int j = 0; j < V; ++j)
+                if (idx[o + j] == me) acc[j] += to_f(dy[o + j]);
+            }
+      }
     } else {
       for (int oh = oh_lo; oh <= oh_hi; ++oh)
         for (int ow = ow_lo; ow <= ow_hi; ++ow) {
           int64_t o = (((int64_t)n * p.P + oh) * p.Q + ow) * p.C + cv * V;
-          Pack<int32_t, V> ii = ld_pack<int32_t, V>(idx + o);
-          Pack<T, V> g = ld_pack<T, V>(dy + o);
+          const int mine = (h - (oh * p.sh - p.ph)) * p.kw + (w - (ow * p.sw - p.pw));
 #pragma unroll
-          for (int j = 0; j < V; ++j)
-            if (ii.v[j] == me) acc[j] += to_f(g.v[j]);
+          for (int j = 0; j < V; ++j) {
+            const bool hit = code ? ((int)code[o + j] == mine) : (idx[o + j] == me);
+            if (hit) acc[j] += to_f(dy[o + j]);
+          }
         }
     }
     Pack<T, V> out;
@@ -250,19 +283,22 @@ using namespace cnb;
 
 extern "C" {
 
-int cnb_maxpool_fwd(const cnb_pool_desc* d, const void* x, void* y, int32_t* idx, void* stream) {
+int cnb_maxpool_fwd(const cnb_pool_desc* d, const void* x, void* y, int32_t* idx, uint8_t* code,
+                    void* stream) {
   PoolP p;
   CNB_TRY(make_pool(d, p, "cnb_maxpool_fwd"));
-  CNB_REQUIRE(x && y && idx, CNB_ERR_INVALID, "cnb_maxpool_fwd: null pointer");
+  CNB_REQUIRE(x && y, CNB_ERR_INVALID, "cnb_maxpool_fwd: null pointer");
+  CNB_REQUIRE(!code || p.kh * p.kw <= 255, CNB_ERR_UNSUPPORTED,
+              "cnb_maxpool_fwd: 1-byte argmax codes need kh*kw <= 255");
   int v = pick_vec(p.C, dtype_size(d->dtype), x, y);
-  if (v > 4) v = 4;
-  while (v > 1 && (uintptr_t)idx % (v * 4) != 0) v >>= 1;
+  while (v > 1 && idx && (uintptr_t)idx % 16 != 0) v >>= 1;
+  while (v > 1 && code && (uintptr_t)code % v != 0) v >>= 1;
   int64_t total = (int64_t)p.N * p.P * p.Q * (p.C / v);
   const int k = p.kh > p.kw ? p.kh : p.kw;
   const int grid = grid_for(total, kPoolThreads, 16);
   cudaStream_t st = (cudaStream_t)stream;
 #define MPF(KK) CNB_DISPATCH_TV(d->dtype, v, (maxpool_fwd_k<T, V, KK><<<grid, kPoolThreads, 0, st>>>( \
-                                   (const T*)x, (T*)y, idx, p, total)))
+                                   (const T*)x, (T*)y, idx, code, p, total)))
   if (k <= 2) MPF(2);
   else if (k == 3) MPF(3);
   else MPF(0);
@@ -270,21 +306,21 @@ int cnb_maxpool_fwd(const cnb_pool_desc* d, const void* x, void* y, int32_t* idx
   return check_launch("maxpool_fwd");
 }
 
-int cnb_maxpool_bwd(const cnb_pool_desc* d, const void* dy, const int32_t* idx, void* dx,
-                    void* stream) {
+int cnb_maxpool_bwd(const cnb_pool_desc* d, const void* dy, const int32_t* idx, const uint8_t* code,
+                    void* dx, void* stream) {
   PoolP p;
   CNB_TRY(make_pool(d, p, "cnb_maxpool_bwd"));
-  CNB_REQUIRE(dy && idx && dx, CNB_ERR_INVALID, "cnb_maxpool_bwd: null pointer");
+  CNB_REQUIRE(dy && dx && (idx || code), CNB_ERR_INVALID,
+              "cnb_maxpool_bwd: null pointer (needs idx or code)");
   int v = pick_vec(p.C, dtype_size(d->dtype), dy, dx);
-  if (v > 4) v = 4;
-  while (v > 1 && (uintptr_t)idx % (v * 4) != 0) v >>= 1;
+  while (v > 1 && code && (uintptr_t)code % v != 0) v >>= 1;
   int64_t total = (int64_t)p.N * p.H * p.W * (p.C / v);
   const int nwh = (p.kh + p.sh - 1) / p.sh, nww = (p.kw + p.sw - 1) / p.sw;
   const int nw = nwh > nww ? nwh : nww;
   const int grid = grid_for(total, kPoolThreads, 16);
   cudaStream_t st = (cudaStream_t)stream;
 #define MPB(NN) CNB_DISPATCH_TV(d->dtype, v, (maxpool_bwd_k<T, V, NN><<<grid, kPoolThreads, 0, st>>>( \
-                                   (const T*)dy, idx, (T*)dx, p, total)))
+                                   (const T*)dy, code ? nullptr : idx, code, (T*)dx, p, total)))
   if (nw == 1) MPB(1);
   else if (nw == 2) MPB(2);
   else if (nw == 3) MPB(3);

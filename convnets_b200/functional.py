@@ -116,6 +116,23 @@ def pack_weight(weight: torch.Tensor, dtype: torch.dtype, c_dst: Optional[int] =
     return cast(w, dtype)
 
 
+def pack_filter(weight: torch.Tensor, transposed: bool = True):
+    """fp32 master weight [K, C, R, S] of a dense conv (KRSC storage) -> (bf16 KRSC operand copy,
+    bf16 [C, R*S, K] copy for data-grad or None) in one pass (cnb_pack_filter)."""
+    w = weight.detach()
+    _cuda(w)
+    if w.dtype != torch.float32:
+        raise TypeError("pack_filter expects the fp32 master weight")
+    if not w.is_contiguous(memory_format=_CL):
+        w = w.contiguous(memory_format=_CL)
+    k, c, r, s = w.shape
+    wb = torch.empty_like(w, dtype=torch.bfloat16)
+    wt = torch.empty((c, r * s, k), dtype=torch.bfloat16, device=w.device) if transposed else None
+    _L.check(_L.load().cnb_pack_filter(_p(w), _p(wb), _p(wt), k, r * s, c, _stream()),
+             "cnb_pack_filter")
+    return wb, wt
+
+
 # ----------------------------------------------------------------------------- convolution
 def _conv_desc(x_shape, w_shape, stride, padding, dilation, groups, dtype_code, flags, algo):
     n, c, h, w = x_shape
@@ -131,7 +148,8 @@ def _conv_desc(x_shape, w_shape, stride, padding, dilation, groups, dtype_code, 
 
 class _Conv2dFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, wpack, stride, padding, dilation, groups, algo, want_stats):
+    def forward(ctx, x, weight, bias, wpack, stride, padding, dilation, groups, algo, want_stats,
+                wpack_t=None):
         _cuda(x, wpack, bias)
         lib = _L.load()
         x = _nhwc(x)
@@ -150,7 +168,7 @@ class _Conv2dFn(torch.autograd.Function):
         _L.check(lib.cnb_conv2d_fwd(C.byref(d), _p(x), _p(wpack), _p(b32), _p(y),
                                     _p(part) if rows > 0 else None, _p(ws), ws.numel(), _stream()),
                  "cnb_conv2d_fwd")
-        ctx.save_for_backward(x, wpack)
+        ctx.save_for_backward(x, wpack, wpack_t)
         ctx.desc = d
         ctx.has_bias = bias is not None
         ctx.wshape = tuple(weight.shape)
@@ -160,7 +178,7 @@ class _Conv2dFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy, _dpart=None):
         lib = _L.load()
-        x, wpack = ctx.saved_tensors
+        x, wpack, wpack_t = ctx.saved_tensors
         d = ctx.desc
         dy = _nhwc(dy)
         if dy.dtype != x.dtype:
@@ -170,8 +188,8 @@ class _Conv2dFn(torch.autograd.Function):
             dx = torch.empty_like(x, memory_format=_CL)
             nws = lib.cnb_conv2d_workspace_bytes(C.byref(d), _L.CNB_DGRAD)
             ws = _workspace(nws, x.device)
-            _L.check(lib.cnb_conv2d_dgrad(C.byref(d), _p(dy), _p(wpack), _p(dx), _p(ws), ws.numel(),
-                                          _stream()), "cnb_conv2d_dgrad")
+            _L.check(lib.cnb_conv2d_dgrad(C.byref(d), _p(dy), _p(wpack), _p(wpack_t), _p(dx), _p(ws),
+                                          ws.numel(), _stream()), "cnb_conv2d_dgrad")
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
             dw = torch.empty(tuple(wpack.shape), dtype=torch.float32, device=x.device,
                              memory_format=_CL)
@@ -183,11 +201,11 @@ class _Conv2dFn(torch.autograd.Function):
                                           ws.numel(), _stream()), "cnb_conv2d_wgrad")
             if tuple(dw.shape) != ctx.wshape:  # zero-padded input channels (RGB stem)
                 dw = dw[:, :ctx.wshape[1]].contiguous(memory_format=_CL)
-        return dx, dw, db, None, None, None, None, None, None, None
+        return dx, dw, db, None, None, None, None, None, None, None, None
 
 
 def conv2d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, wpack=None,
-           algo=_L.CNB_ALGO_AUTO, bn_stats=False):
+           algo=_L.CNB_ALGO_AUTO, bn_stats=False, wpack_t=None):
     """Drop-in for F.conv2d as reached from nn.Conv2d (reference src/basemodel.py:974,992).
     `weight` is the fp32 master parameter; `wpack` an optional pre-packed operand copy.
     With `bn_stats` returns (y, partials): the per-tile BatchNorm partial sums emitted by the
@@ -195,7 +213,7 @@ def conv2d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, wpac
     if wpack is None:
         wpack = pack_weight(weight, x.dtype)
     y, part = _Conv2dFn.apply(x, weight, bias, wpack, _pair(stride), _pair(padding),
-                              _pair(dilation), int(groups), int(algo), bool(bn_stats))
+                              _pair(dilation), int(groups), int(algo), bool(bn_stats), wpack_t)
     if bn_stats:
         return y, (part if part.shape[0] > 0 else None)
     return y
@@ -469,9 +487,18 @@ class _MaxPoolFn(torch.autograd.Function):
         d, P, Q = _pool_desc(x, kernel_size, stride, padding)
         n, c = x.shape[0], x.shape[1]
         y = _empty_nhwc(n, c, P, Q, x.dtype, x.device)
-        idx = torch.empty((n, c, P, Q), dtype=torch.int32, device=x.device, memory_format=_CL)
-        _L.check(lib.cnb_maxpool_fwd(C.byref(d), _p(x), _p(y), _p(idx), _stream()), "cnb_maxpool_fwd")
-        ctx.save_for_backward(idx)
+        # int32 h*W+w indices only when the caller wants them; backward uses 1-byte window codes
+        idx = torch.empty((n, c, P, Q) if return_indices else (0,), dtype=torch.int32, device=x.device,
+                          **({"memory_format": _CL} if return_indices else {}))
+        kh, kw = _pair(kernel_size)
+        code = None if kh * kw > 255 else torch.empty((n, c, P, Q), dtype=torch.uint8,
+                                                      device=x.device, memory_format=_CL)
+        if code is None and not return_indices:
+            idx = torch.empty((n, c, P, Q), dtype=torch.int32, device=x.device, memory_format=_CL)
+        _L.check(lib.cnb_maxpool_fwd(C.byref(d), _p(x), _p(y), _p(idx) if idx.numel() else None,
+                                     _p(code), _stream()), "cnb_maxpool_fwd")
+        ctx.save_for_backward(idx if code is None else code)
+        ctx.coded = code is not None
         ctx.desc = d
         ctx.xshape = tuple(x.shape)
         ctx.mark_non_differentiable(idx)
@@ -480,11 +507,12 @@ class _MaxPoolFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy, _didx):
         lib = _L.load()
-        (idx,) = ctx.saved_tensors
+        (sel,) = ctx.saved_tensors
         dy = _nhwc(dy)
         n, c, h, w = ctx.xshape
         dx = _empty_nhwc(n, c, h, w, dy.dtype, dy.device)
-        _L.check(lib.cnb_maxpool_bwd(C.byref(ctx.desc), _p(dy), _p(idx), _p(dx), _stream()),
+        _L.check(lib.cnb_maxpool_bwd(C.byref(ctx.desc), _p(dy), None if ctx.coded else _p(sel),
+                                     _p(sel) if ctx.coded else None, _p(dx), _stream()),
                  "cnb_maxpool_bwd")
         return dx, None, None, None, None
 
@@ -492,7 +520,7 @@ class _MaxPoolFn(torch.autograd.Function):
 def max_pool2d(x, kernel_size, stride=None, padding=0, return_indices=False):
     """Drop-in for F.max_pool2d (reference src/basemodel.py:1017-1024).  Indices are int32
     h*W+w with PyTorch's first-maximum rule."""
-    y, idx = _MaxPoolFn.apply(x, kernel_size, stride, padding, True)
+    y, idx = _MaxPoolFn.apply(x, kernel_size, stride, padding, bool(return_indices))
     return (y, idx) if return_indices else y
 
 

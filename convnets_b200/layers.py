@@ -36,12 +36,20 @@ class Conv2d(nn.Conv2d):
             return y
         return out
 
-    def _packed(self, dtype: torch.dtype, c_dst=None) -> torch.Tensor:
+    def _packed(self, dtype: torch.dtype):
+        """(operand copy of the weight in `dtype`, [C, R*S, K] copy for data-grad or None), cached
+        until the parameter changes (optimizer.step() bumps its version counter)."""
         w = self.weight
-        key = (w._version, w.data_ptr(), dtype, c_dst)
+        key = (w._version, w.data_ptr(), dtype)
         cache = self.__dict__.get("_cnb_pack")
         if cache is None or cache[0] != key:
-            cache = (key, F_.pack_weight(w, dtype, c_dst))
+            dense_tc = (dtype == torch.bfloat16 and self.groups == 1 and w.dtype == torch.float32
+                        and w.shape[0] % 8 == 0 and w.shape[1] % 8 == 0)
+            if dense_tc:
+                pair = F_.pack_filter(w, transposed=not self.cast_input)
+            else:
+                pair = (F_.pack_weight(w, dtype), None)
+            cache = (key, pair)
             self.__dict__["_cnb_pack"] = cache
         return cache[1]
 
@@ -57,9 +65,10 @@ class Conv2d(nn.Conv2d):
                 return self._tag(F_.conv2d_input(x, self.weight, self.bias, self.stride, self.padding,
                                                  self.dilation, self.compute_dtype, bn_stats=stats))
             x = F_.to_nhwc(x, self.compute_dtype)
+        wpack, wpack_t = self._packed(x.dtype)
         return self._tag(F_.conv2d(x, self.weight, self.bias, self.stride, self.padding,
-                                   self.dilation, self.groups, wpack=self._packed(x.dtype),
-                                   algo=self.algo, bn_stats=stats))
+                                   self.dilation, self.groups, wpack=wpack, algo=self.algo,
+                                   bn_stats=stats, wpack_t=wpack_t))
 
 
 class BatchNorm2d(nn.BatchNorm2d):

@@ -51,7 +51,8 @@ SIGNATURES = {
     "cnb_conv2d_workspace_bytes": (_SZ, [C.POINTER(ConvDesc), _I]),
     "cnb_conv2d_bn_partial_rows": (_I, [C.POINTER(ConvDesc)]),
     "cnb_conv2d_fwd": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _SZ, _P]),
-    "cnb_conv2d_dgrad": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _SZ, _P]),
+    "cnb_conv2d_dgrad": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _SZ, _P]),
+    "cnb_pack_filter": (_I, [_P, _P, _P, _I32, _I32, _I32, _P]),
     "cnb_conv2d_wgrad": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_bn_workspace_bytes": (_SZ, [C.POINTER(BnDesc)]),
     "cnb_bn_fwd_train": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _P,
@@ -63,8 +64,8 @@ SIGNATURES = {
     "cnb_add_relu_fwd": (_I, [_P, _P, _P, _I64, _I, _P]),
     "cnb_add_relu_bwd": (_I, [_P, _P, _P, _I64, _I, _P]),
     "cnb_add": (_I, [_P, _P, _P, _I64, _I, _P]),
-    "cnb_maxpool_fwd": (_I, [C.POINTER(PoolDesc), _P, _P, _P, _P]),
-    "cnb_maxpool_bwd": (_I, [C.POINTER(PoolDesc), _P, _P, _P, _P]),
+    "cnb_maxpool_fwd": (_I, [C.POINTER(PoolDesc), _P, _P, _P, _P, _P]),
+    "cnb_maxpool_bwd": (_I, [C.POINTER(PoolDesc), _P, _P, _P, _P, _P]),
     "cnb_avgpool_fwd": (_I, [C.POINTER(PoolDesc), _P, _P, _P]),
     "cnb_avgpool_bwd": (_I, [C.POINTER(PoolDesc), _P, _P, _P]),
     "cnb_gap_fwd": (_I, [_P, _P, _I32, _I32, _I32, _I, _P]),

@@ -102,7 +102,7 @@ int cnb_conv2d_out_dims(const cnb_conv_desc* d, int32_t* P, int32_t* Q);
 /* 1 if the tcgen05 tensor-core path would run for this direction, 0 for CUDA cores, <0 error */
 int cnb_conv2d_uses_tc(const cnb_conv_desc* d, int direction);
 size_t cnb_conv2d_workspace_bytes(const cnb_conv_desc* d, int direction);
-/* rows of the BatchNorm partial-sum table the forward epilogue can emit for this problem (one row
+/* rows of the BatchNorm partial-sum table the forward epilogue can emit for this problem (two rows
  * per 128-pixel output tile), or 0 when this conv runs on a path that cannot (CUDA cores). */
 int cnb_conv2d_bn_partial_rows(const cnb_conv_desc* d);
 /* y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R,S,C/g]) (+ bias[K] fp32) (ReLU).
@@ -111,8 +111,10 @@ int cnb_conv2d_bn_partial_rows(const cnb_conv_desc* d);
  * follows the conv in conv2d_block (reference src/basemodel.py:1004-1010), fused into the epilogue. */
 int cnb_conv2d_fwd(const cnb_conv_desc* d, const void* x, const void* w, const float* bias, void* y,
                    float* bn_partials, void* workspace, size_t workspace_bytes, void* stream);
-/* dx[N,H,W,C] = conv_transpose(dy[N,P,Q,K], w) */
-int cnb_conv2d_dgrad(const cnb_conv_desc* d, const void* dy, const void* w, void* dx,
+/* dx[N,H,W,C] = conv_transpose(dy[N,P,Q,K], w).  w_t (may be NULL): the filter with in/out
+ * channels exchanged, [C][R*S][K], as written by cnb_pack_filter; without it the tensor-core path
+ * transposes w into the workspace on every call. */
+int cnb_conv2d_dgrad(const cnb_conv_desc* d, const void* dy, const void* w, const void* w_t, void* dx,
                      void* workspace, size_t workspace_bytes, void* stream);
 /* dw[K,R,S,C/g] (fp32) = x (*) dy ; dbias[K] (fp32, may be NULL) = sum over N,P,Q of dy */
 int cnb_conv2d_wgrad(const cnb_conv_desc* d, const void* x, const void* dy, float* dw, float* dbias,
@@ -157,9 +159,13 @@ int cnb_add(const void* a, const void* b, void* y, int64_t n, int dtype, void* s
 /* ---- pooling: aten::max_pool2d_with_indices / avg_pool2d / adaptive_avg_pool2d ------------ */
 /* idx[N,P,Q,C] int32 = h*W + w of the first maximum in row-major window scan (PyTorch's rule;
  * padding is never selected; NaN propagates). */
-int cnb_maxpool_fwd(const cnb_pool_desc* d, const void* x, void* y, int32_t* idx, void* stream);
-int cnb_maxpool_bwd(const cnb_pool_desc* d, const void* dy, const int32_t* idx, void* dx,
+/* code[N,P,Q,C] uint8 (may be NULL, as may idx): the same argmax as a window-relative position
+ * (h - (p*stride_h - pad_h)) * kw + (w - (q*stride_w - pad_w)) — 1 byte instead of 4 for the
+ * training path, where only backward consumes it.  Backward takes whichever is given (code wins). */
+int cnb_maxpool_fwd(const cnb_pool_desc* d, const void* x, void* y, int32_t* idx, uint8_t* code,
                     void* stream);
+int cnb_maxpool_bwd(const cnb_pool_desc* d, const void* dy, const int32_t* idx, const uint8_t* code,
+                    void* dx, void* stream);
 /* count_include_pad=True, ceil_mode=False (reference src/shufflenet_v1.py:148, densenet.py:188) */
 int cnb_avgpool_fwd(const cnb_pool_desc* d, const void* x, void* y, void* stream);
 int cnb_avgpool_bwd(const cnb_pool_desc* d, const void* dy, void* dx, void* stream);
@@ -188,6 +194,11 @@ int cnb_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t 
  * taps and for columns >= R*S*C.  The conv then runs as cnb_conv2d_{fwd,wgrad} with a 1x1
  * descriptor over C = K_dst "channels" (no data-grad: the network input needs none). */
 int cnb_im2col_nchw(const cnb_conv_desc* d, const float* src, void* dst, int32_t K_dst,
+                    void* stream);
+/* fp32 master filter w[K][R*S][C] (the KRSC storage of a dense nn.Conv2d weight) -> bf16 operand
+ * copies: w_bf16 in the same layout (forward / weight-grad) and, when wt_bf16 is not NULL,
+ * [C][R*S][K] (data-grad).  One pass per optimiser step. */
+int cnb_pack_filter(const float* w, void* w_bf16, void* wt_bf16, int32_t K, int32_t RS, int32_t C,
                     void* stream);
 /* element-wise precision conversion (fp32 master weights -> bf16 operand copy, etc.) */
 int cnb_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n, void* stream);

@@ -117,7 +117,7 @@ def test_train_step_parity(family, kind, hw, batch, dtype):
     # graph (fp32: the reference's own fp32 run; bf16: the storage-rounded graph accumulated in
     # fp32).  Whole-network gradients are conditioning-limited (two fp32
     # executions of the reference differ by 1e-3..3e-2), so the bar is statistical: the median
-    # error must be within 2x the median floor and no parameter beyond 6x its own floor.
+    # error must be within 2x the median floor and no parameter beyond 8x its own floor.
     gtol = (1e-3 if dtype == torch.float32 else 1e-1)
     gsum = sum(v.norm().item() for v in g64.values() if v is not None)
     ours_all, floor_all, worst = [], [], 0.0
@@ -130,7 +130,7 @@ def test_train_step_parity(family, kind, hw, batch, dtype):
         floor = O.rel_l2(g32[k], ref)
         if dtype == torch.float32:
             floor = max(floor, O.rel_l2(g32n[k], ref))
-        assert ours <= max(gtol, 6 * floor), f"{k}: ours {ours:.3e} floor {floor:.3e}"
+        assert ours <= max(gtol, 8 * floor), f"{k}: ours {ours:.3e} floor {floor:.3e}"
         ours_all.append(ours)
         floor_all.append(floor)
         worst = max(worst, ours)

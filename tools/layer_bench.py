@@ -75,7 +75,7 @@ def main():
             p = lambda t: C.c_void_p(t.data_ptr())
             fns = {
                 "fwd": lambda: L.check(lib.cnb_conv2d_fwd(C.byref(d), p(x), p(wp), None, p(y), None, p(ws), ws.numel(), st), "fwd"),
-                "dgrad": lambda: L.check(lib.cnb_conv2d_dgrad(C.byref(d), p(dy), p(wp), p(dx), p(ws), ws.numel(), st), "dgrad"),
+                "dgrad": lambda: L.check(lib.cnb_conv2d_dgrad(C.byref(d), p(dy), p(wp), None, p(dx), p(ws), ws.numel(), st), "dgrad"),
                 "wgrad": lambda: L.check(lib.cnb_conv2d_wgrad(C.byref(d), p(x), p(dy), p(dw), None, p(ws), ws.numel(), st), "wgrad"),
             }
             byts = (x.numel() + y.numel() + w.numel()) * 2
