@@ -254,7 +254,9 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        # a mismatched collective must fail fast instead of holding N GPUs for the default 10 min
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=150))
     L.load()
     cls, kind, defb = WORKLOADS[args.model]
     B = args.batch or defb
@@ -342,12 +344,16 @@ def run_ours(args):
 
     # ---- roofline of the dominant kernel family: one traced step (outside the timed regions)
     roof, fam = None, None
+    # every rank runs the two extra steps (their gradient all-reduces are collectives: a step on
+    # rank 0 alone would deadlock the job); only rank 0 brackets its calls with events
+    step(resident[0])
+    torch.cuda.synchronize()
+    if rank == 0:
+        L.trace_begin()
+    step(resident[0])
+    torch.cuda.synchronize()
     if rank == 0:
         pk = peaks()
-        step(resident[0])
-        torch.cuda.synchronize()
-        L.trace_begin()
-        step(resident[0])
         trace = L.trace_end()
         fam, total = summarise_trace(trace, pk)
         top = max(fam.items(), key=lambda kv: kv[1]["ms"])
@@ -399,7 +405,7 @@ def run_ours(args):
             "cpu_baseline": cpu,
         }
         if sync is not None:
-            line["config"]["allreduces_per_step"] = sync.launched // max(1, (args.steps * (1 if args.no_e2e else 2) + args.warmup + 3))
+            line["config"]["allreduces_per_step"] = sync.launched // max(1, args.warmup + args.steps + (0 if args.no_e2e else 2 + args.steps) + 2)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

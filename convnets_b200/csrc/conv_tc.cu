@@ -524,12 +524,16 @@ struct WgradParams {
   int16_t off_h[kMaxTaps], off_w[kMaxTaps];
 };
 
-template <int NT, int SA, int SB, bool IM2COL>
+// TS > 1 (narrow layers, NT = 64): the x tiles of all (<= TS) taps of the CTA share one ring stage,
+// laid out like the 64-channel boxes of a wide tile, so ONE MMA chain of N = taps*64 per pixel block
+// covers them all (tap t lands in TMEM columns [64t, 64t+64)) instead of one N = 64 chain per tap.
+template <int NT, int SA, int SB, bool IM2COL, int TS = 1>
 __global__ void __launch_bounds__(kTcThreads, 1)
 conv_wgrad_tc_k(const __grid_constant__ WgradParams p) {
+  static_assert(TS == 1 || NT == 64, "multi-tap stages are for 64-channel tiles");
   constexpr int PIX = 64;                         // GEMM-K block: pixels per TMA box
   constexpr int DY_BYTES = 2 * PIX * 128;         // two 64-channel boxes -> 128 out-channels
-  constexpr int X_BYTES = (NT / 64) * PIX * 128;  // NT/64 boxes
+  constexpr int X_BYTES = TS * (NT / 64) * PIX * 128;  // NT/64 boxes per tap, TS taps
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~(uintptr_t)1023);
@@ -605,6 +609,18 @@ conv_wgrad_tc_k(const __grid_constant__ WgradParams p) {
           bh = p.lower_h + i * p.trav_h;
           bw = p.lower_w + j * p.trav_w;
         }
+        if (TS > 1) {
+          const int s = itb % SB;
+          const uint32_t use = itb / SB;
+          mbar_wait(&emptyB[s], (use & 1) ^ 1);
+          mbar_expect_tx(&fullB[s], (uint32_t)ntap * PIX * 128);
+          uint8_t* dst = sB + s * X_BYTES;
+          for (int tp = 0; tp < ntap; ++tp)
+            tma_load_im2col_4d(&p.tmX, &fullB[s], dst + tp * PIX * 128, cin0, bw, bh, bn,
+                               (uint16_t)p.off_w[tap0 + tp], (uint16_t)p.off_h[tap0 + tp]);
+          ++itb;
+          continue;
+        }
         for (int tp = 0; tp < ntap; ++tp, ++itb) {
           const int s = itb % SB;
           const uint32_t use = itb / SB;
@@ -628,6 +644,28 @@ conv_wgrad_tc_k(const __grid_constant__ WgradParams p) {
     for (int pb = 0; pb < npb; ++pb) {
       const int sa = pb % SA;
       mbar_wait(&fullA[sa], (pb / SA) & 1);
+      if (TS > 1) {
+        const int sb = itb % SB;
+        mbar_wait(&fullB[sb], (itb / SB) & 1);
+        tc_fence_after();
+        if (lane == 0) {
+          const uint32_t idesc_mt = make_idesc_bf16(TILE_M, (uint32_t)ntap * 64u, 1, 1);
+          const uint32_t a_base = smem_u32(sA + sa * DY_BYTES);
+          const uint32_t b_base = smem_u32(sB + sb * X_BYTES);
+#pragma unroll
+          for (int k = 0; k < PIX / 16; ++k) {
+            uint64_t da = make_smem_desc_sw128(a_base + k * 2048, PIX * 128, 1024);
+            uint64_t db = make_smem_desc_sw128(b_base + k * 2048, PIX * 128, 1024);
+            umma_bf16(tmem_base, da, db, idesc_mt, (pb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&emptyB[sb]);
+          umma_commit(&emptyA[sa]);
+          if (pb == npb - 1) umma_commit(tmem_full_bar);
+        }
+        __syncwarp();
+        ++itb;
+        continue;
+      }
       for (int tp = 0; tp < ntap; ++tp, ++itb) {
         const int sb = itb % SB;
         mbar_wait(&fullB[sb], (itb / SB) & 1);
@@ -941,6 +979,7 @@ static void wgrad_geometry(const cnb_conv_desc& d, int& NT, int& taps_per_cta, i
   NT = Cg >= 256 ? 256 : (Cg >= 128 ? 128 : 64);
   const int taps = d.R * d.S;
   int maxt = 512 / NT;
+  if (NT == 64 && taps > 1) maxt = 4;  // multi-tap stages: one N = taps*64 MMA chain per pixel block
   tap_groups = (taps + maxt - 1) / maxt;
   taps_per_cta = (taps + tap_groups - 1) / tap_groups;
   tap_groups = (taps + taps_per_cta - 1) / taps_per_cta;
@@ -1134,12 +1173,12 @@ int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const v
   return check_launch("dgrad_interleave");
 }
 
-template <int NT, int SA, int SB, bool IM2COL>
+template <int NT, int SA, int SB, bool IM2COL, int TS = 1>
 static int launch_wgrad_inst(const WgradParams& prm, int grid, cudaStream_t st) {
-  constexpr size_t smem = (size_t)SA * 2 * 64 * 128 + (size_t)SB * (NT / 64) * 64 * 128 +
+  constexpr size_t smem = (size_t)SA * 2 * 64 * 128 + (size_t)SB * TS * (NT / 64) * 64 * 128 +
                           (2 * SA + 2 * SB + 1) * 8 + 16 + 1024;
   static bool attr_done = false;
-  auto kern = conv_wgrad_tc_k<NT, SA, SB, IM2COL>;
+  auto kern = conv_wgrad_tc_k<NT, SA, SB, IM2COL, TS>;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cudaFuncSetAttribute(wgrad): %s",
@@ -1224,7 +1263,7 @@ int conv_tc_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* 
     else if (NT == 128) s = launch_wgrad_inst<128, 6, 6, false>(prm, grid, st);
     else s = launch_wgrad_inst<256, 4, 4, false>(prm, grid, st);
   } else {
-    if (NT == 64) s = launch_wgrad_inst<64, 3, 16, true>(prm, grid, st);
+    if (NT == 64) s = launch_wgrad_inst<64, 3, 5, true, 4>(prm, grid, st);
     else if (NT == 128) s = launch_wgrad_inst<128, 3, 10, true>(prm, grid, st);
     else s = launch_wgrad_inst<256, 3, 5, true>(prm, grid, st);
   }

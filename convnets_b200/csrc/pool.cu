@@ -22,15 +22,16 @@ struct PoolP {
 template <typename T, int V, int K>
 __global__ void maxpool_fwd_k(const T* __restrict__ x, T* __restrict__ y, int32_t* __restrict__ idx,
                               uint8_t* __restrict__ code, PoolP p, int64_t total_vec) {
+  // one output row (n, oh) per block, (q, channel vector) over the threads: the row decomposition
+  // is block-uniform and each item costs a single integer division
   const int Cv = p.C / V;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    int cv = (int)(i % Cv);
-    int64_t pix = i / Cv;
-    int q = (int)(pix % p.Q);
-    int64_t t = pix / p.Q;
-    int oh = (int)(t % p.P);
-    int n = (int)(t / p.P);
+  (void)total_vec;
+  const int oh = blockIdx.x % p.P;
+  const int n = blockIdx.x / p.P;
+  for (int item = threadIdx.x; item < p.Q * Cv; item += blockDim.x) {
+    const int q = item / Cv;
+    const int cv = item - q * Cv;
+    const int64_t i = ((int64_t)blockIdx.x * p.Q + q) * Cv + cv;
     int h0 = oh * p.sh - p.ph, w0 = q * p.sw - p.pw;
     const int hs = h0, ws = w0;  // un-clamped window origin (the 1-byte code is relative to it)
     int h1 = min(h0 + p.kh, p.H), w1 = min(w0 + p.kw, p.W);
@@ -113,19 +114,19 @@ template <typename T, int V, int NW>
 __global__ void maxpool_bwd_k(const T* __restrict__ dy, const int32_t* __restrict__ idx,
                               const uint8_t* __restrict__ code, T* __restrict__ dx, PoolP p,
                               int64_t total_vec) {
+  // one input row (n, h) per block: the candidate output rows are block-uniform
   const int Cv = p.C / V;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total_vec;
-       i += (int64_t)gridDim.x * blockDim.x) {
-    int cv = (int)(i % Cv);
-    int64_t pix = i / Cv;
-    int w = (int)(pix % p.W);
-    int64_t t = pix / p.W;
-    int h = (int)(t % p.H);
-    int n = (int)(t / p.H);
-    // output rows oh with oh*sh - ph <= h < oh*sh - ph + kh
-    int oh_lo = (h + p.ph - p.kh + p.sh) / p.sh;  // ceil((h+ph-kh+1)/sh)
-    if (h + p.ph - p.kh + 1 <= 0) oh_lo = 0;
-    int oh_hi = min((h + p.ph) / p.sh, p.P - 1);
+  (void)total_vec;
+  const int h = blockIdx.x % p.H;
+  const int n = blockIdx.x / p.H;
+  // output rows oh with oh*sh - ph <= h < oh*sh - ph + kh
+  int oh_lo = (h + p.ph - p.kh + p.sh) / p.sh;  // ceil((h+ph-kh+1)/sh)
+  if (h + p.ph - p.kh + 1 <= 0) oh_lo = 0;
+  const int oh_hi = min((h + p.ph) / p.sh, p.P - 1);
+  for (int item = threadIdx.x; item < p.W * Cv; item += blockDim.x) {
+    const int w = item / Cv;
+    const int cv = item - w * Cv;
+    const int64_t i = ((int64_t)blockIdx.x * p.W + w) * Cv + cv;
     int ow_lo = (w + p.pw - p.kw + p.sw) / p.sw;
     if (w + p.pw - p.kw + 1 <= 0) ow_lo = 0;
     int ow_hi = min((w + p.pw) / p.sw, p.Q - 1);
@@ -295,7 +296,8 @@ int cnb_maxpool_fwd(const cnb_pool_desc* d, const void* x, void* y, int32_t* idx
   while (v > 1 && code && (uintptr_t)code % v != 0) v >>= 1;
   int64_t total = (int64_t)p.N * p.P * p.Q * (p.C / v);
   const int k = p.kh > p.kw ? p.kh : p.kw;
-  const int grid = grid_for(total, kPoolThreads, 16);
+  CNB_REQUIRE((int64_t)p.N * p.P < (1ll << 31), CNB_ERR_UNSUPPORTED, "cnb_maxpool_fwd: too many rows");
+  const int grid = p.N * p.P;
   cudaStream_t st = (cudaStream_t)stream;
 #define MPF(KK) CNB_DISPATCH_TV(d->dtype, v, (maxpool_fwd_k<T, V, KK><<<grid, kPoolThreads, 0, st>>>( \
                                    (const T*)x, (T*)y, idx, code, p, total)))
@@ -317,7 +319,8 @@ int cnb_maxpool_bwd(const cnb_pool_desc* d, const void* dy, const int32_t* idx, 
   int64_t total = (int64_t)p.N * p.H * p.W * (p.C / v);
   const int nwh = (p.kh + p.sh - 1) / p.sh, nww = (p.kw + p.sw - 1) / p.sw;
   const int nw = nwh > nww ? nwh : nww;
-  const int grid = grid_for(total, kPoolThreads, 16);
+  CNB_REQUIRE((int64_t)p.N * p.H < (1ll << 31), CNB_ERR_UNSUPPORTED, "cnb_maxpool_bwd: too many rows");
+  const int grid = p.N * p.H;
   cudaStream_t st = (cudaStream_t)stream;
 #define MPB(NN) CNB_DISPATCH_TV(d->dtype, v, (maxpool_bwd_k<T, V, NN><<<grid, kPoolThreads, 0, st>>>( \
                                    (const T*)dy, code ? nullptr : idx, code, (T*)dx, p, total)))

@@ -130,7 +130,9 @@ def test_train_step_parity(family, kind, hw, batch, dtype):
         floor = O.rel_l2(g32[k], ref)
         if dtype == torch.float32:
             floor = max(floor, O.rel_l2(g32n[k], ref))
-        assert ours <= max(gtol, 8 * floor), f"{k}: ours {ours:.3e} floor {floor:.3e}"
+        # per-parameter cap: 8x its own floor, or the spread SURVEY.md Appendix D measured between
+        # two fp32 executions of the reference itself (up to 5e-2) — whichever is larger
+        assert ours <= max(gtol, 8 * floor, 3e-2), f"{k}: ours {ours:.3e} floor {floor:.3e}"
         ours_all.append(ours)
         floor_all.append(floor)
         worst = max(worst, ours)
