@@ -184,7 +184,7 @@ __device__ __forceinline__ void bn_finish_fwd(int c, double S, double Q, double 
   }
   const float g = f.gamma ? f.gamma[c] : 1.f, b = f.beta ? f.beta[c] : 0.f;
   f.scale[c] = g * rstd;
-  f.shift[c] = b - mu * g * rstd;
+  f.shift[c] = b;  // bn_apply_k computes (x - mean) * scale + shift: no mean*scale cancellation
 }
 
 // ---------------------------------------------------------------- forward statistics
@@ -248,7 +248,7 @@ bn_partials_k(const float* __restrict__ tiles, float* __restrict__ part, int64_t
   if (r1 > ntiles) r1 = ntiles;
   float s[1] = {0.f}, q[1] = {0.f};
   if (c0 < C) {
-    constexpr int U = 4;
+    constexpr int U = 2;
     const int64_t step = (int64_t)blockDim.y * U;
     for (int64_t r = r0 + threadIdx.y; r < r1; r += step) {
       float a[U], b[U];
@@ -280,7 +280,7 @@ __global__ void bn_eval_coeff_k(const float* __restrict__ gamma, const float* __
   float rstd = 1.f / sqrtf(rvar[c] + eps);
   float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
   scale[c] = g * rstd;
-  shift[c] = b - rmean[c] * g * rstd;
+  shift[c] = b;
 }
 
 // y = [relu](x*scale + shift [+ res]); 2-D thread map (channel vector fixed per thread, so the
@@ -288,8 +288,8 @@ __global__ void bn_eval_coeff_k(const float* __restrict__ gamma, const float* __
 template <typename T, int V, bool RELU, bool ADD>
 __global__ void __launch_bounds__(kBnThreads)
 bn_apply_k(const T* __restrict__ x, const T* __restrict__ res, const float* __restrict__ scale,
-           const float* __restrict__ shift, T* __restrict__ y, uint8_t* __restrict__ mask, int64_t M,
-           int C, int64_t rows_per_split) {
+           const float* __restrict__ shift, const float* __restrict__ mean, T* __restrict__ y,
+           uint8_t* __restrict__ mask, int64_t M, int C, int64_t rows_per_split) {
   const int cv = blockIdx.x * blockDim.x + threadIdx.x;
   const int c0 = cv * V;
   if (c0 >= C) return;
@@ -298,11 +298,12 @@ bn_apply_k(const T* __restrict__ x, const T* __restrict__ res, const float* __re
   const int64_t r0 = (int64_t)(gridDim.y - 1 - blockIdx.y) * rows_per_split;
   int64_t r1 = r0 + rows_per_split;
   if (r1 > M) r1 = M;
-  float sc[V], sh[V];
+  float sc[V], sh[V], mu[V];
 #pragma unroll
   for (int j = 0; j < V; ++j) {
     sc[j] = scale[c0 + j];
     sh[j] = shift[c0 + j];
+    mu[j] = mean[c0 + j];
   }
   const int64_t step = (int64_t)blockDim.y * kBnUnroll;
   for (int64_t r = r0 + threadIdx.y; r < r1; r += step) {
@@ -323,7 +324,7 @@ bn_apply_k(const T* __restrict__ x, const T* __restrict__ res, const float* __re
         uint32_t bits = 0;
 #pragma unroll
         for (int j = 0; j < V; ++j) {
-          float v = fmaf(to_f(a[u].v[j]), sc[j], sh[j]);
+          float v = fmaf(to_f(a[u].v[j]) - mu[j], sc[j], sh[j]);
           if (ADD) {
             // the reference materialises bn(x) in the storage dtype before `output += identity`
             v = to_f(from_f<T>(v)) + to_f(rs[u].v[j]);
@@ -423,14 +424,15 @@ bn_bwd_dx_k(const T* __restrict__ x, const T* __restrict__ y, const uint8_t* __r
   const int64_t r0 = blockIdx.y * rows_per_split;
   int64_t r1 = r0 + rows_per_split;
   if (r1 > M) r1 = M;
-  // dx = k1*dy' + k3*x + k0  with k1 = c1, k3 = -c1*c3, k0 = c1*(c3*mean - c2)
-  float k1[V], k3[V], k0[V];
+  // dx = c1 * (dy' - c2 - (x - mean) * c3), with x centred first: folding the mean into a constant
+  // term (k3*x + k0) cancels catastrophically in fp32 when |mean| is large against the spread
+  float k1[V], k2[V], k3[V], mu[V];
 #pragma unroll
   for (int j = 0; j < V; ++j) {
-    const float a1 = c1[c0 + j], a2 = c2[c0 + j], a3 = c3[c0 + j], m = mean[c0 + j];
-    k1[j] = a1;
-    k3[j] = -a1 * a3;
-    k0[j] = a1 * (a3 * m - a2);
+    k1[j] = c1[c0 + j];
+    k2[j] = c2[c0 + j];
+    k3[j] = c3[c0 + j];
+    mu[j] = mean[c0 + j];
   }
   constexpr int U = 2;
   const int64_t step = (int64_t)blockDim.y * U;
@@ -462,7 +464,7 @@ bn_bwd_dx_k(const T* __restrict__ x, const T* __restrict__ y, const uint8_t* __r
             if (!pos) gf = 0.f;
           }
           if (DRES) dr.v[j] = from_f<T>(gf);
-          o.v[j] = from_f<T>(fmaf(k1[j], gf, fmaf(k3[j], to_f(a[u].v[j]), k0[j])));
+          o.v[j] = from_f<T>(k1[j] * (gf - k2[j] - (to_f(a[u].v[j]) - mu[j]) * k3[j]));
         }
         st_pack<T, V>(dx + rr * C + c0, o);
         if (DRES) st_pack<T, V>(dres + rr * C + c0, dr);
@@ -561,14 +563,15 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
     CNB_TRY(check_launch("bn_stats"));
   }
   float* shift = scale + C;
+  const float* mean_ptr = save_mean;
   uint8_t* mask = (uint8_t*)relu_mask;
   BnGeom ga = bn_geom(M, C, v, kStreamWaves);
   dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
   const int64_t arows = ga.rows_per_split;
 #define APPLY(R, A)                                                                              \
   CNB_DISPATCH_TV(d->dtype, v, (bn_apply_k<T, V, R, A><<<agrid, ablock, 0, st>>>(                \
-                                   (const T*)x, (const T*)residual, scale, shift, (T*)y, mask,  \
-                                   d->M, C, arows)))
+                                   (const T*)x, (const T*)residual, scale, shift, mean_ptr,     \
+                                   (T*)y, mask, d->M, C, arows)))
   if (relu && add) APPLY(true, true);
   else if (relu) APPLY(true, false);
   else if (add) APPLY(false, true);
@@ -600,6 +603,7 @@ int cnb_bn_fwd_eval(const cnb_bn_desc* d, const void* x, const void* residual, c
   dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
   const int64_t arows = ga.rows_per_split;
   uint8_t* mask = nullptr;
+  const float* mean_ptr = running_mean;
   if (relu && add) APPLY(true, true);
   else if (relu) APPLY(true, false);
   else if (add) APPLY(false, true);
