@@ -71,6 +71,18 @@ def test_train_step_parity(family, kind, hw, batch, dtype):
     # of oneDNN (SURVEY.md Appendix D uses the pair to measure the reference's own fp32 noise)
     with torch.backends.mkldnn.flags(enabled=False):
         _, _, g32n, _ = Z.loss_and_grads(family, sd, x, y, kind)
+    # third floor (fp32-IO mode): conditioning of the reference graph itself.  At test size (batch 8,
+    # 2x2 final feature maps -> 32 samples per BatchNorm channel) ONE pre-activation within a few
+    # ulps of zero flips its ReLU mask between two legitimate executions and moves a BatchNorm
+    # bias gradient — and everything upstream of it — by ~1e-2 (measured: DenseNet-121 features.9
+    # channel 514, y = 2.9e-6 on the GPU vs <= 0 in fp64).  The fp64 oracle re-run on the input
+    # scaled by (1 + 1e-6 * randn) — an ~8-ulp fp32 perturbation — measures exactly that spread.
+    gpert = []
+    if dtype == torch.float32:
+        for seed in (1, 2):
+            gp_ = torch.Generator().manual_seed(seed)
+            xp = x.double() * (1 + 1e-6 * torch.randn(x.shape, generator=gp_, dtype=torch.float64))
+            gpert.append(Z.loss_and_grads(family, sd64, xp, y, kind)[2])
     lfloor = 0.0
     if dtype == torch.bfloat16:
         exact = lg64
@@ -129,7 +141,7 @@ def test_train_step_parity(family, kind, hw, batch, dtype):
         ours = O.rel_l2(p.grad, ref)
         floor = O.rel_l2(g32[k], ref)
         if dtype == torch.float32:
-            floor = max(floor, O.rel_l2(g32n[k], ref))
+            floor = max([floor, O.rel_l2(g32n[k], ref)] + [O.rel_l2(gp[k], ref) for gp in gpert])
         # per-parameter cap: 8x its own floor, or the spread SURVEY.md Appendix D measured between
         # two fp32 executions of the reference itself (up to 5e-2) — whichever is larger
         assert ours <= max(gtol, 8 * floor, 3e-2), f"{k}: ours {ours:.3e} floor {floor:.3e}"
