@@ -537,6 +537,8 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
     int64_t splits = ceil_div((int64_t)sm_count() * 2, g.cblocks);
     int64_t max_splits = ceil_div((int64_t)n_partials, (int64_t)g.ry * 4);
     if (splits > max_splits) splits = max_splits;
+    // one row per persistent conv CTA (<= SM count): a single CTA per 64 channels sums them
+    if (n_partials <= 512) splits = 1;
     if (splits < 1) splits = 1;
     g.rows_per_split = ceil_div((int64_t)n_partials, splits);
     g.splits = (int)ceil_div((int64_t)n_partials, g.rows_per_split);

@@ -122,185 +122,35 @@ struct FpropParams {
   CUtensorMap tmB;  // weights {Cg, RS, Kout}, box {64, 1, BLOCK_N}
   CUtensorMap tmD;  // output {Kout, M}, box {64, 128}
   const float* bias;
-  float* stats;     // optional [m-tiles][2][Kout] per-tile column sums / sums of squares of the stored output
+  float* stats;     // optional [persistent CTAs / n_tiles][2][Kout] column sums / sums of squares of the stored output
   int M;            // output pixels in this launch
   int outP, outQ;   // output grid per image (pixel index -> (n, i, j))
   int lower_h, lower_w, trav_h, trav_w;
   int num_cblk;     // ceil(C / 64)
   int num_taps;
   int n_tiles;      // ceil(Kout / BLOCK_N)
-  int num_tiles;    // m-tiles * n-tiles (persistent kernel)
+  int m_tiles;      // ceil(M / 128)
+  int grp_out, grp_in;  // grouped conv: output / reduction channels per group (0 = dense)
   int Kout;
   int flags;
   int16_t off_h[kMaxTaps], off_w[kMaxTaps];
   uint8_t widx[kMaxTaps];
 };
 
-// MINB = CTAs that should co-reside on one SM.  Layers with a short reduction loop (1x1 convs with
-// few input channels: one or two k-blocks per tile) are latency-bound per CTA — load, 4..8 MMAs,
-// epilogue, store, with nothing to overlap — so they run a 2-stage ring with 2..3 CTAs per SM and
-// let the CTAs overlap each other; deep loops (3x3, wide 1x1) keep a deep ring and one CTA per SM.
-template <int BLOCK_N, int STAGES, bool IM2COL, int MINB>
-__global__ void __launch_bounds__(kTcThreads, MINB)
-conv_fprop_tc_k(const __grid_constant__ FpropParams p) {
-  constexpr int B_TILE_BYTES = BLOCK_N * TILE_K * 2;
-  constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
-  static_assert(STAGES * STAGE_BYTES >= TILE_M * BLOCK_N * 2, "output staging aliases the stages");
-  constexpr uint32_t TMEM_COLS = BLOCK_N < 32 ? 32 : BLOCK_N;
-
-  extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~(uintptr_t)1023);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
-  uint64_t* empty_bar = full_bar + STAGES;
-  uint64_t* tmem_full_bar = empty_bar + STAGES;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
-
-  const int warp = threadIdx.x / 32;
-  const int lane = threadIdx.x % 32;
-  const int n_tile = blockIdx.x % p.n_tiles;
-  const int m_tile = blockIdx.x / p.n_tiles;
-  const int m0 = m_tile * TILE_M;
-  const int n0 = n_tile * BLOCK_N;
-  const int num_iters = p.num_taps * p.num_cblk;
-
-  if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&p.tmA);
-    tma_prefetch_desc(&p.tmB);
-    tma_prefetch_desc(&p.tmD);
-    for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&full_bar[s], 1);
-      mbar_init(&empty_bar[s], 1);
-    }
-    mbar_init(tmem_full_bar, 1);
-    fence_barrier_init();
-  }
-  if (warp == 1) {
-    tmem_alloc(tmem_ptr, TMEM_COLS);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = *tmem_ptr;
-
-  if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      int bn = 0, bh = 0, bw = 0;
-      if (IM2COL) {
-        int j = m0 % p.outQ;
-        int t = m0 / p.outQ;
-        int i = t % p.outP;
-        bn = t / p.outP;
-        bh = p.lower_h + i * p.trav_h;
-        bw = p.lower_w + j * p.trav_w;
-      }
-      int it = 0;
-      for (int tap = 0; tap < p.num_taps; ++tap) {
-        for (int cb = 0; cb < p.num_cblk; ++cb, ++it) {
-          const int s = it % STAGES;
-          const uint32_t use = it / STAGES;
-          mbar_wait(&empty_bar[s], (use & 1) ^ 1);
-          uint8_t* sa = smem + s * STAGE_BYTES;
-          uint8_t* sb = sa + A_TILE_BYTES;
-          mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-          if (IM2COL)
-            tma_load_im2col_4d(&p.tmA, &full_bar[s], sa, cb * TILE_K, bw, bh, bn,
-                               (uint16_t)p.off_w[tap], (uint16_t)p.off_h[tap]);
-          else
-            tma_load_2d(&p.tmA, &full_bar[s], sa, cb * TILE_K, m0);
-          tma_load_3d(&p.tmB, &full_bar[s], sb, cb * TILE_K, (int)p.widx[tap], n0);
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BLOCK_N, 0, 0);
-    for (int it = 0; it < num_iters; ++it) {
-      const int s = it % STAGES;
-      const uint32_t use = it / STAGES;
-      mbar_wait(&full_bar[s], use & 1);
-      tc_fence_after();
-      if (lane == 0) {
-        const uint32_t a_base = smem_u32(smem + s * STAGE_BYTES);
-        const uint32_t b_base = a_base + A_TILE_BYTES;
-#pragma unroll
-        for (int k = 0; k < TILE_K / 16; ++k) {
-          uint64_t da = make_smem_desc_sw128(a_base + k * 32, 0, 1024);
-          uint64_t db = make_smem_desc_sw128(b_base + k * 32, 0, 1024);
-          umma_bf16(tmem_base, da, db, idesc, (it | k) != 0 ? 1u : 0u);
-        }
-        umma_commit(&empty_bar[s]);
-        if (it == num_iters - 1) umma_commit(tmem_full_bar);
-      }
-      __syncwarp();
-    }
-  } else {
-    // ===================== epilogue (warps 2..5) =====================
-    const int quarter = warp % 4;
-    const int row = quarter * 32 + lane;
-    mbar_wait(tmem_full_bar, 0);
-    tc_fence_after();
-    uint8_t* stage_out = smem;  // aliases the (now idle) pipeline stages
-#pragma unroll 1
-    for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
-      uint32_t v[32];
-      tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)c0, v);
-      tmem_ld_wait();
-      uint8_t* box = stage_out + (c0 / 64) * (TILE_M * 128);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        uint32_t packed[4];
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          float f0 = __uint_as_float(v[j * 8 + e * 2 + 0]);
-          float f1 = __uint_as_float(v[j * 8 + e * 2 + 1]);
-          const int col = n0 + c0 + j * 8 + e * 2;
-          if (p.flags & CNB_CONV_BIAS) {
-            f0 += (col < p.Kout) ? p.bias[col] : 0.f;
-            f1 += (col + 1 < p.Kout) ? p.bias[col + 1] : 0.f;
-          }
-          if (p.flags & CNB_CONV_RELU) {
-            f0 = (f0 > 0.f || f0 != f0) ? f0 : 0.f;
-            f1 = (f1 > 0.f || f1 != f1) ? f1 : 0.f;
-          }
-          __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);
-          packed[e] = *reinterpret_cast<uint32_t*>(&h);
-        }
-        const int chunk = (c0 % 64) / 8 + j;
-        uint4* dst = reinterpret_cast<uint4*>(box + row * 128 + ((chunk ^ (row & 7)) * 16));
-        *dst = make_uint4(packed[0], packed[1], packed[2], packed[3]);
-      }
-    }
-    tc_fence_before();
-    fence_proxy_async_smem();
-    asm volatile("bar.sync 1, 128;" ::: "memory");
-    if (warp == 2 && lane == 0) {
-      for (int b = 0; b < BLOCK_N / 64; ++b) {
-        if (n0 + b * 64 < p.Kout)
-          tma_store_2d(&p.tmD, stage_out + b * (TILE_M * 128), n0 + b * 64, m0);
-      }
-      tma_store_commit();
-      tma_store_wait0();
-    }
-  }
-  __syncthreads();
-  if (warp == 1) {
-    tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
-  }
-}
-
 // ------------------------------------------------------------------------------------------
-// Persistent variant: one CTA per SM walks the (m-tile, n-tile) list with a static stride.  The
-// TMA producer runs ahead across tile boundaries (the smem ring never drains), the accumulator is
-// double-buffered in TMEM (2 x BLOCK_N columns) and the epilogue of tile i — tcgen05.ld, bias /
-// ReLU, bf16 pack, swizzled staging, TMA store — overlaps the MMAs of tile i+1.  The per-tile fixed
-// costs of the one-tile-per-CTA kernel above (barrier init, TMEM alloc, descriptor prefetch,
-// pipeline fill, exposed epilogue) are paid once per SM instead of once per tile, which is what
-// the short-reduction layers (1x1 with few channels, 3x3 on 64 channels) were bound by.
-template <int BLOCK_N, int STAGES, bool IM2COL>
+// Persistent variant: one CTA per SM.  CTA b owns ONE n-tile (b % n_tiles) and walks the m-tiles
+// b / n_tiles, + grid / n_tiles, ... — CTAs that run side by side share the activation tile through
+// L2, and because a CTA's output columns never change, the BatchNorm column sums of all its tiles
+// accumulate in registers and leave the kernel as ONE partial row per CTA.  The TMA producer runs
+// ahead across tile boundaries (the smem ring never drains), the accumulator is double-buffered in
+// TMEM (2 x BLOCK_N columns) and the epilogue of tile i — tcgen05.ld, bf16 pack, swizzled staging,
+// TMA store, column sums — overlaps the MMAs of tile i+1.
+//   PLAIN : no bias / ReLU in the epilogue (every conv that feeds a BatchNorm, and data-grad);
+//           the generic variant reads the flags at run time.
+//   grouped convolutions (p.grp_out > 0): the n-tile selects the input-channel slice it reads
+//           (a_c0) and the filter operand is the block-diagonal expansion built by
+//           expand_grouped_filter_k, see "grouped convolutions" below.
+template <int BLOCK_N, int STAGES, bool IM2COL, bool PLAIN>
 __global__ void __launch_bounds__(kPersistThreads, 1)
 conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
   constexpr int B_TILE_BYTES = BLOCK_N * TILE_K * 2;
@@ -321,7 +171,10 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
   const int warp = threadIdx.x / 32;
   const int lane = threadIdx.x % 32;
   const int num_iters = p.num_taps * p.num_cblk;
-  const int num_tiles = p.num_tiles;
+  const int n_idx = blockIdx.x % p.n_tiles;
+  const int m_first = blockIdx.x / p.n_tiles;
+  const int m_step = gridDim.x / p.n_tiles;
+  const int n0 = n_idx * BLOCK_N;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
@@ -349,10 +202,10 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
+      const int a_c0 = p.grp_out > 0 ? (n0 / p.grp_out) * p.grp_in : 0;
       uint32_t it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile / p.n_tiles) * TILE_M;
-        const int n0 = (tile % p.n_tiles) * BLOCK_N;
+      for (int mt = m_first; mt < p.m_tiles; mt += m_step) {
+        const int m0 = mt * TILE_M;
         int bn = 0, bh = 0, bw = 0;
         if (IM2COL) {
           int j = m0 % p.outQ;
@@ -371,10 +224,10 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
             uint8_t* sb = sa + A_TILE_BYTES;
             mbar_expect_tx(&full_bar[s], STAGE_BYTES);
             if (IM2COL)
-              tma_load_im2col_4d(&p.tmA, &full_bar[s], sa, cb * TILE_K, bw, bh, bn,
+              tma_load_im2col_4d(&p.tmA, &full_bar[s], sa, a_c0 + cb * TILE_K, bw, bh, bn,
                                  (uint16_t)p.off_w[tap], (uint16_t)p.off_h[tap]);
             else
-              tma_load_2d(&p.tmA, &full_bar[s], sa, cb * TILE_K, m0);
+              tma_load_2d(&p.tmA, &full_bar[s], sa, a_c0 + cb * TILE_K, m0);
             tma_load_3d(&p.tmB, &full_bar[s], sb, cb * TILE_K, (int)p.widx[tap], n0);
           }
         }
@@ -384,7 +237,7 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
     // ===================== MMA issuer =====================
     constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BLOCK_N, 0, 0);
     uint32_t it = 0, lt = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+    for (int mt = m_first; mt < p.m_tiles; mt += m_step, ++lt) {
       const uint32_t buf = lt & 1;
       mbar_wait(&tmem_empty_bar[buf], ((lt >> 1) & 1) ^ 1);  // epilogue has drained this buffer
       tc_fence_after();
@@ -416,46 +269,69 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
     const int quarter = warp % 4;
     const int chalf = (warp - 2) / 4;
     constexpr int HALF_N = BLOCK_N / 2;
+    constexpr int NCH = HALF_N / 32;          // 32-column chunks per warp: 1, 2 or 4
     const int row = quarter * 32 + lane;
     const bool storer = (warp == 2 && lane == 0);
+    const uint32_t st_base = smem_u32(stage_out);
+    const uint32_t row_addr = st_base + row * 128;
+    const uint32_t row7 = (uint32_t)(row & 7);
+    const uint32_t lane_taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+    // BatchNorm column sums: thread (pr, rg) owns the column pair 2*pr of row group rg
+    const int et = (int)threadIdx.x - 64;
+    constexpr int PAIRS = BLOCK_N / 2;
+    constexpr int RG = 256 / PAIRS;           // row groups: 2, 4 or 8
+    constexpr int RPG = TILE_M / RG;          // rows per group: 64, 32 or 16
+    const int pr = et % PAIRS, rg = et / PAIRS;
+    const int sc = pr * 2;
+    const uint32_t col_addr = st_base + (sc / 64) * (TILE_M * 128) + (sc % 8) * 2 + rg * RPG * 128;
+    uint32_t soff[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) soff[i] = i * 128 + ((((sc % 64) / 8) ^ i) << 4);  // RPG % 8 == 0
+    float as0 = 0.f, as1 = 0.f, aq0 = 0.f, aq1 = 0.f;
+    const bool want_stats = p.stats != nullptr;
+
     uint32_t lt = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
-      const int m0 = (tile / p.n_tiles) * TILE_M;
-      const int n0 = (tile % p.n_tiles) * BLOCK_N;
+    for (int mt = m_first; mt < p.m_tiles; mt += m_step, ++lt) {
+      const int m0 = mt * TILE_M;
       const uint32_t buf = lt & 1;
       mbar_wait(&tmem_full_bar[buf], (lt >> 1) & 1);
       tc_fence_after();
       // the previous tile's TMA store must have finished READING the staging buffer
       if (storer) tma_store_wait_read0();
       asm volatile("bar.sync 1, 256;" ::: "memory");
-#pragma unroll 1
-      for (int c0 = chalf * HALF_N; c0 < (chalf + 1) * HALF_N; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + buf * BLOCK_N + (uint32_t)c0, v);
+      const uint32_t tcol = lane_taddr + buf * BLOCK_N + (uint32_t)(chalf * HALF_N);
+      uint32_t v[2][32];
+      tmem_ld_32x32b_x32(tcol, v[0]);
+#pragma unroll
+      for (int ch = 0; ch < NCH; ++ch) {
         tmem_ld_wait();
-        uint8_t* box = stage_out + (c0 / 64) * (TILE_M * 128);
+        if (ch + 1 < NCH) tmem_ld_32x32b_x32(tcol + (uint32_t)((ch + 1) * 32), v[(ch + 1) & 1]);
+        const uint32_t(&cur)[32] = v[ch & 1];
+        const int c0 = chalf * HALF_N + ch * 32;
+        const uint32_t box = row_addr + (uint32_t)(c0 / 64) * (TILE_M * 128);
+        const uint32_t chunk0 = (uint32_t)((c0 % 64) / 8);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           uint32_t packed[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
-            float f0 = __uint_as_float(v[j * 8 + e * 2 + 0]);
-            float f1 = __uint_as_float(v[j * 8 + e * 2 + 1]);
-            const int col = n0 + c0 + j * 8 + e * 2;
-            if (p.flags & CNB_CONV_BIAS) {
-              f0 += (col < p.Kout) ? p.bias[col] : 0.f;
-              f1 += (col + 1 < p.Kout) ? p.bias[col + 1] : 0.f;
-            }
-            if (p.flags & CNB_CONV_RELU) {
-              f0 = (f0 > 0.f || f0 != f0) ? f0 : 0.f;
-              f1 = (f1 > 0.f || f1 != f1) ? f1 : 0.f;
+            float f0 = __uint_as_float(cur[j * 8 + e * 2 + 0]);
+            float f1 = __uint_as_float(cur[j * 8 + e * 2 + 1]);
+            if (!PLAIN) {
+              const int col = n0 + c0 + j * 8 + e * 2;
+              if (p.flags & CNB_CONV_BIAS) {
+                f0 += (col < p.Kout) ? p.bias[col] : 0.f;
+                f1 += (col + 1 < p.Kout) ? p.bias[col + 1] : 0.f;
+              }
+              if (p.flags & CNB_CONV_RELU) {
+                f0 = (f0 > 0.f || f0 != f0) ? f0 : 0.f;
+                f1 = (f1 > 0.f || f1 != f1) ? f1 : 0.f;
+              }
             }
             __nv_bfloat162 h = __floats2bfloat162_rn(f0, f1);
             packed[e] = *reinterpret_cast<uint32_t*>(&h);
           }
-          const int chunk = (c0 % 64) / 8 + j;
-          uint4* dst = reinterpret_cast<uint4*>(box + row * 128 + ((chunk ^ (row & 7)) * 16));
-          *dst = make_uint4(packed[0], packed[1], packed[2], packed[3]);
+          sts_v4(box + (((chunk0 + j) ^ row7) << 4), packed[0], packed[1], packed[2], packed[3]);
         }
       }
       // accumulator buffer fully read: hand it back to the MMA warp
@@ -470,34 +346,52 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
         }
         tma_store_commit();
       }
-      if (p.stats != nullptr) {
-        // BatchNorm statistics of this tile from the staged (bf16-rounded, i.e. as stored) values:
-        // each thread owns a pair of adjacent columns and walks the rows of the swizzled boxes.
-        // One fp32 partial row per m-tile -> merged in fixed order by bn_partials_k (deterministic).
-        // Two partial rows per m-tile: threads 0..127 sum tile rows 0..63, threads 128..255 rows 64..127.
-        const int e = (int)threadIdx.x - 64;
-        const int rbeg = (e / 128) * (TILE_M / 2);
-        const int rows = min(rbeg + TILE_M / 2, p.M - m0);
-        float* dst = p.stats + ((size_t)(tile / p.n_tiles) * 2 + (e / 128)) * 2 * p.Kout;
-        for (int pr = e % 128; pr < BLOCK_N / 2; pr += 128) {
-          const int c = pr * 2;
-          const uint8_t* colp = stage_out + (c / 64) * (TILE_M * 128) + (c % 8) * 2;
-          const int chunk = (c % 64) / 8;
-          float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-#pragma unroll 8
-          for (int r = rbeg; r < rows; ++r) {
-            const uint32_t w2 = *reinterpret_cast<const uint32_t*>(colp + r * 128 + ((chunk ^ (r & 7)) * 16));
-            const float a = __uint_as_float(w2 << 16), b = __uint_as_float(w2 & 0xffff0000u);
-            s0 += a; q0 = fmaf(a, a, q0);
-            s1 += b; q1 = fmaf(b, b, q1);
+      if (want_stats) {
+        // BatchNorm statistics of this tile from the staged (bf16-rounded, i.e. as stored) values.
+        // Rows past the end of the tensor are zero (TMA zero-fill x weights) unless a bias was
+        // added, so only the generic variant needs the row bound.
+        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+        const int rows_left = p.M - m0 - rg * RPG;  // valid rows of this thread's group
+#pragma unroll
+        for (int r8 = 0; r8 < RPG / 8; ++r8) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            if (PLAIN || r8 * 8 + i < rows_left) {
+              const uint32_t w2 = lds_u32(col_addr + r8 * 1024 + soff[i]);
+              const float a = __uint_as_float(w2 << 16), b = __uint_as_float(w2 & 0xffff0000u);
+              s0 += a; q0 = fmaf(a, a, q0);
+              s1 += b; q1 = fmaf(b, b, q1);
+            }
           }
-          const int col = n0 + c;
-          if (col < p.Kout) { dst[col] = s0; dst[p.Kout + col] = q0; }
-          if (col + 1 < p.Kout) { dst[col + 1] = s1; dst[p.Kout + col + 1] = q1; }
         }
+        as0 += s0; as1 += s1; aq0 += q0; aq1 += q1;  // two-level sum: per tile, then per CTA
       }
     }
     if (storer) tma_store_wait0();
+    if (want_stats) {
+      // combine the row groups in fixed order and write this CTA's partial row
+      asm volatile("bar.sync 1, 256;" ::: "memory");  // staging is idle (last store completed)
+      const uint32_t red = st_base;                    // [RG][2][BLOCK_N] floats
+      sts_f32(red + ((rg * 2 + 0) * BLOCK_N + sc) * 4, as0);
+      sts_f32(red + ((rg * 2 + 0) * BLOCK_N + sc + 1) * 4, as1);
+      sts_f32(red + ((rg * 2 + 1) * BLOCK_N + sc) * 4, aq0);
+      sts_f32(red + ((rg * 2 + 1) * BLOCK_N + sc + 1) * 4, aq1);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (et < BLOCK_N) {
+        float S = 0.f, Qs = 0.f;
+#pragma unroll
+        for (int g = 0; g < RG; ++g) {
+          S += lds_f32(red + ((g * 2 + 0) * BLOCK_N + et) * 4);
+          Qs += lds_f32(red + ((g * 2 + 1) * BLOCK_N + et) * 4);
+        }
+        const int col = n0 + et;
+        if (col < p.Kout) {
+          float* dst = p.stats + (size_t)m_first * 2 * p.Kout;
+          dst[col] = S;
+          dst[p.Kout + col] = Qs;
+        }
+      }
+    }
   }
   __syncthreads();
   if (warp == 1) {
@@ -521,6 +415,7 @@ struct WgradParams {
   int taps_per_cta, tap_groups;
   int cin_tiles, cout_tiles;
   int splits, pixblk_per_split;  // pixel blocks (64 pixels) per split
+  int grp_out, grp_in;           // grouped conv: out / in channels per group (0 = dense)
   int16_t off_h[kMaxTaps], off_w[kMaxTaps];
 };
 
@@ -562,7 +457,9 @@ conv_wgrad_tc_k(const __grid_constant__ WgradParams p) {
   const int pb1 = min(pb0 + p.pixblk_per_split, total_pixblk);
   const int npb = max(pb1 - pb0, 0);
   const int cout0 = ct * TILE_M;
-  const int cin0 = cit * NT;
+  const int cin0 = cit * NT;   // input-channel coordinate of the OUTPUT tile
+  // input-channel coordinate of the x LOADS: grouped layers read the slice of their out-channel tile
+  const int xc0 = p.grp_out > 0 ? (cout0 / p.grp_out) * p.grp_in + cin0 : cin0;
 
   // TMEM columns: power of two >= taps_per_cta * NT (host guarantees <= 512)
   uint32_t tmem_cols = 32;
@@ -616,7 +513,7 @@ conv_wgrad_tc_k(const __grid_constant__ WgradParams p) {
           mbar_expect_tx(&fullB[s], (uint32_t)ntap * PIX * 128);
           uint8_t* dst = sB + s * X_BYTES;
           for (int tp = 0; tp < ntap; ++tp)
-            tma_load_im2col_4d(&p.tmX, &fullB[s], dst + tp * PIX * 128, cin0, bw, bh, bn,
+            tma_load_im2col_4d(&p.tmX, &fullB[s], dst + tp * PIX * 128, xc0, bw, bh, bn,
                                (uint16_t)p.off_w[tap0 + tp], (uint16_t)p.off_h[tap0 + tp]);
           ++itb;
           continue;
@@ -630,10 +527,10 @@ conv_wgrad_tc_k(const __grid_constant__ WgradParams p) {
 #pragma unroll
           for (int b = 0; b < NT / 64; ++b) {
             if (IM2COL)
-              tma_load_im2col_4d(&p.tmX, &fullB[s], dst + b * PIX * 128, cin0 + b * 64, bw, bh, bn,
+              tma_load_im2col_4d(&p.tmX, &fullB[s], dst + b * PIX * 128, xc0 + b * 64, bw, bh, bn,
                                  (uint16_t)p.off_w[tap0 + tp], (uint16_t)p.off_h[tap0 + tp]);
             else
-              tma_load_2d(&p.tmX, &fullB[s], dst + b * PIX * 128, cin0 + b * 64, pix0);
+              tma_load_2d(&p.tmX, &fullB[s], dst + b * PIX * 128, xc0 + b * 64, pix0);
           }
         }
       }
@@ -817,51 +714,47 @@ struct FpropLaunch {
   float* stats;                  // optional BatchNorm partials (forward only)
   int flags;
   bool tiled2d;                  // pure GEMM: A is the [M, C] matrix itself
+  int grp_out, grp_in, wC;       // grouped: out / reduction channels per group, expanded filter width
 };
 
-template <int BLOCK_N, int STAGES, bool IM2COL, int MINB>
-static int launch_fprop_inst(const FpropParams& prm, int grid, cudaStream_t st) {
-  constexpr int STAGE_BYTES = A_TILE_BYTES + BLOCK_N * TILE_K * 2;
-  constexpr size_t smem = (size_t)STAGES * STAGE_BYTES + (2 * STAGES + 1) * 8 + 16 + 1024;
-  static bool attr_done = false;
-  auto kern = conv_fprop_tc_k<BLOCK_N, STAGES, IM2COL, MINB>;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cudaFuncSetAttribute(fprop): %s",
-                cudaGetErrorString(e));
-    attr_done = true;
-  }
-  kern<<<grid, kTcThreads, smem, st>>>(prm);
-  return check_launch("conv_fprop_tc");
+// Persistent grid: a multiple of n_tiles (every CTA keeps one n-tile), at most one CTA per SM, and
+// no CTA without work.  grid / n_tiles is also the number of BatchNorm partial rows.
+static int persist_grid(int64_t m_tiles, int n_tiles) {
+  int64_t per = sm_count() / n_tiles;
+  if (per < 1) per = 1;
+  if (per > m_tiles) per = m_tiles;
+  return (int)(per * n_tiles);
 }
 
-template <int BLOCK_N, int STAGES, bool IM2COL>
+static int fprop_block_n(int Kout, bool grouped) {
+  if (grouped) return 64;
+  return Kout <= 64 ? 64 : (Kout <= 128 ? 128 : 256);
+}
+
+template <int BLOCK_N, int STAGES, bool IM2COL, bool PLAIN>
 static int launch_fprop_persist_inst(const FpropParams& prm, cudaStream_t st) {
   constexpr int STAGE_BYTES = A_TILE_BYTES + BLOCK_N * TILE_K * 2;
   constexpr size_t smem = (size_t)STAGES * STAGE_BYTES + (size_t)TILE_M * BLOCK_N * 2 +
                           (2 * STAGES + 4) * 8 + 16 + 1024;
   static_assert(smem <= 232448, "exceeds the 227 KB dynamic shared memory limit");
   static bool attr_done = false;
-  auto kern = conv_fprop_tc_persist_k<BLOCK_N, STAGES, IM2COL>;
+  auto kern = conv_fprop_tc_persist_k<BLOCK_N, STAGES, IM2COL, PLAIN>;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cudaFuncSetAttribute(fprop persistent): %s",
                 cudaGetErrorString(e));
     attr_done = true;
   }
-  const int grid = prm.num_tiles < sm_count() ? prm.num_tiles : sm_count();
+  const int grid = persist_grid(prm.m_tiles, prm.n_tiles);
   kern<<<grid, kPersistThreads, smem, st>>>(prm);
   return check_launch("conv_fprop_tc_persist");
 }
 
-// CNB_CONV_PERSIST=0 selects the one-tile-per-CTA kernel (kept for A/B measurement only).
-static bool use_persistent() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("CNB_CONV_PERSIST");
-    v = (e && e[0] == '0') ? 0 : 1;
-  }
-  return v == 1;
+template <bool IM2COL, bool PLAIN>
+static int launch_fprop_bn(const FpropParams& prm, int BLOCK_N, cudaStream_t st) {
+  if (BLOCK_N == 64) return launch_fprop_persist_inst<64, 8, IM2COL, PLAIN>(prm, st);
+  if (BLOCK_N == 128) return launch_fprop_persist_inst<128, 5, IM2COL, PLAIN>(prm, st);
+  return launch_fprop_persist_inst<256, 3, IM2COL, PLAIN>(prm, st);
 }
 
 static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
@@ -880,10 +773,12 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
     CNB_TRY(make_im2col_map(&prm.tmA, L.a, L.aN, L.aH, L.aW, L.aC, L.lower_w, L.lower_h, L.upper_w,
                             L.upper_h, L.trav_w, L.trav_h, TILE_M, "A(im2col)"));
   }
-  const int BLOCK_N = L.Kout <= 64 ? 64 : (L.Kout <= 128 ? 128 : 256);
+  const bool grouped = L.grp_out > 0;
+  const int BLOCK_N = fprop_block_n(L.Kout, grouped);
+  const int wC = grouped ? L.wC : L.aC;   // reduction width of the filter operand
   {
-    uint64_t dims[3] = {(uint64_t)L.aC, (uint64_t)L.RS, (uint64_t)L.Kout};
-    uint64_t str[2] = {(uint64_t)L.aC * 2, (uint64_t)L.aC * L.RS * 2};
+    uint64_t dims[3] = {(uint64_t)wC, (uint64_t)L.RS, (uint64_t)L.Kout};
+    uint64_t str[2] = {(uint64_t)wC * 2, (uint64_t)wC * L.RS * 2};
     uint32_t box[3] = {TILE_K, 1, (uint32_t)BLOCK_N};
     CNB_TRY(make_tiled_map(&prm.tmB, L.w, 3, dims, str, box, "B(weights)"));
   }
@@ -899,9 +794,12 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
   prm.outP = L.outP; prm.outQ = L.outQ;
   prm.lower_h = L.lower_h; prm.lower_w = L.lower_w;
   prm.trav_h = L.trav_h; prm.trav_w = L.trav_w;
-  prm.num_cblk = (L.aC + TILE_K - 1) / TILE_K;
+  prm.num_cblk = (wC + TILE_K - 1) / TILE_K;
   prm.num_taps = L.ntaps;
   prm.n_tiles = (L.Kout + BLOCK_N - 1) / BLOCK_N;
+  prm.m_tiles = (int)ceil_div(M, TILE_M);
+  prm.grp_out = L.grp_out;
+  prm.grp_in = L.grp_in;
   prm.Kout = L.Kout;
   prm.flags = L.flags & ((L.bias ? CNB_CONV_BIAS : 0) | CNB_CONV_RELU);
   for (int t = 0; t < L.ntaps; ++t) {
@@ -909,41 +807,97 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
     prm.off_w[t] = L.off_w[t];
     prm.widx[t] = L.widx[t];
   }
-  const int64_t grid64 = ceil_div(M, TILE_M) * prm.n_tiles;
-  CNB_REQUIRE(grid64 < (1ll << 31), CNB_ERR_UNSUPPORTED, "conv_tc: grid too large");
-  const int grid = (int)grid64;
-  prm.num_tiles = grid;
-  if (use_persistent()) {
-    if (L.tiled2d) {
-      if (BLOCK_N == 64) return launch_fprop_persist_inst<64, 8, false>(prm, st);
-      if (BLOCK_N == 128) return launch_fprop_persist_inst<128, 5, false>(prm, st);
-      return launch_fprop_persist_inst<256, 3, false>(prm, st);
+  const bool plain = prm.flags == 0;
+  if (L.tiled2d)
+    return plain ? launch_fprop_bn<false, true>(prm, BLOCK_N, st)
+                 : launch_fprop_bn<false, false>(prm, BLOCK_N, st);
+  return plain ? launch_fprop_bn<true, true>(prm, BLOCK_N, st)
+               : launch_fprop_bn<true, false>(prm, BLOCK_N, st);
+}
+
+// ==========================================================================================
+// grouped convolutions (ResNeXt / SENet / SKNet 3x3 with 4..32 channels per group, ShuffleNet 1x1)
+// ==========================================================================================
+// GEMM-N side = "out" channels (out_per_g per group), reduction side = "in" channels (in_per_g).
+// An n-tile [n0, n0 + tile) of out channels belongs to groups g_lo..g_hi and therefore reads the
+// input-channel slice [g_lo * in_per_g, (g_hi + 1) * in_per_g): its widest extent is the `span`.
+// The filter operand is EXPANDED to width wC = round_up(span, 64): row k holds weight (k, c) at
+// column (g(k) - g_lo) * in_per_g + c and zeros elsewhere, i.e. the dense kernels run unchanged on
+// a block-diagonal filter restricted to the slice (the A operand's channel coordinate starts at
+// g_lo * in_per_g).  The padded multiplications by zero are not counted as algorithmic FLOPs;
+// these layers are HBM-bound (AI 5..60 FLOP/B) and the tensor pipe has the slack.
+static int grouped_span(int out_total, int out_per_g, int in_per_g, int tile) {
+  int mx = 0;
+  for (int n0 = 0; n0 < out_total; n0 += tile) {
+    const int g_lo = n0 / out_per_g;
+    const int last = (n0 + tile < out_total ? n0 + tile : out_total) - 1;
+    const int g_hi = last / out_per_g;
+    const int sp = (g_hi - g_lo + 1) * in_per_g;
+    mx = sp > mx ? sp : mx;
+  }
+  return mx;
+}
+
+constexpr int kGroupTileN = 64;     // fprop / dgrad n-tile of the grouped path
+constexpr int kGroupMaxWidth = 1024; // widest expanded reduction slice
+
+// out[o][rs][cc], cc in [0, wC).  transposed == 0 (forward operand): o = k, reduction = c.
+// transposed == 1 (data-grad operand): o = c, reduction = k.  w is the plain [K][RS][Cg] filter.
+__global__ void expand_grouped_filter_k(const bf16* __restrict__ w, bf16* __restrict__ out, int K,
+                                        int RS, int Cg, int Kg, int wC, int tile, int transposed) {
+  const int C = (K / Kg) * Cg;
+  const int O = transposed ? C : K;
+  const int out_per_g = transposed ? Cg : Kg, in_per_g = transposed ? Kg : Cg;
+  const int64_t total = (int64_t)O * RS * wC;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int cc = (int)(i % wC);
+    const int64_t t = i / wC;
+    const int rs = (int)(t % RS);
+    const int o = (int)(t / RS);
+    const int g_lo = ((o / tile) * tile) / out_per_g;
+    const int g = o / out_per_g;
+    const int rl = cc - (g - g_lo) * in_per_g;   // reduction channel within the group
+    bf16 v = __float2bfloat16_rn(0.f);
+    if (rl >= 0 && rl < in_per_g) {
+      const int k = transposed ? g * Kg + rl : o;
+      const int c = transposed ? o - g * Cg : rl;
+      v = w[((int64_t)k * RS + rs) * Cg + c];
     }
-    if (BLOCK_N == 64) return launch_fprop_persist_inst<64, 8, true>(prm, st);
-    if (BLOCK_N == 128) return launch_fprop_persist_inst<128, 5, true>(prm, st);
-    return launch_fprop_persist_inst<256, 3, true>(prm, st);
+    out[i] = v;
   }
-  CNB_REQUIRE(L.stats == nullptr, CNB_ERR_UNSUPPORTED,
-              "conv_tc: BatchNorm partials need the persistent kernel (unset CNB_CONV_PERSIST=0)");
-  const bool shallow = prm.num_taps * prm.num_cblk <= 4;
-  if (L.tiled2d) {
-    if (shallow) {
-      if (BLOCK_N == 64) return launch_fprop_inst<64, 2, false, 3>(prm, grid, st);
-      if (BLOCK_N == 128) return launch_fprop_inst<128, 2, false, 3>(prm, grid, st);
-      return launch_fprop_inst<256, 2, false, 2>(prm, grid, st);
-    }
-    if (BLOCK_N == 64) return launch_fprop_inst<64, 6, false, 1>(prm, grid, st);
-    if (BLOCK_N == 128) return launch_fprop_inst<128, 5, false, 1>(prm, grid, st);
-    return launch_fprop_inst<256, 4, false, 1>(prm, grid, st);
+}
+
+// dw[k][rs][c] = sum over splits of part[split][k][rs][(g(k) - g_lo(k-tile)) * Cg + c]: picks the
+// block diagonal out of the dense [128 out-ch x NT] tiles the grouped weight-grad produced.
+__global__ void extract_grouped_wgrad_k(const float* __restrict__ part, float* __restrict__ dw,
+                                        int splits, int K, int RS, int Cg, int Kg, int NT) {
+  const int64_t total = (int64_t)K * RS * Cg;
+  const int64_t psz = (int64_t)K * RS * NT;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % Cg);
+    const int64_t t = i / Cg;
+    const int k = (int)(t / RS);
+    const int g_lo = ((k / TILE_M) * TILE_M) / Kg;
+    const int64_t src = t * NT + (int64_t)(k / Kg - g_lo) * Cg + c;
+    float sum = 0.f;
+    for (int sp = 0; sp < splits; ++sp) sum += part[(int64_t)sp * psz + src];
+    dw[i] = sum;
   }
-  if (shallow) {
-    if (BLOCK_N == 64) return launch_fprop_inst<64, 2, true, 3>(prm, grid, st);
-    if (BLOCK_N == 128) return launch_fprop_inst<128, 2, true, 3>(prm, grid, st);
-    return launch_fprop_inst<256, 2, true, 2>(prm, grid, st);
-  }
-  if (BLOCK_N == 64) return launch_fprop_inst<64, 6, true, 1>(prm, grid, st);
-  if (BLOCK_N == 128) return launch_fprop_inst<128, 5, true, 1>(prm, grid, st);
-  return launch_fprop_inst<256, 4, true, 1>(prm, grid, st);
+}
+
+// expanded reduction width (multiple of 64) for the forward (dir 0) / data-grad (dir 1) operand
+static int grouped_width(const cnb_conv_desc& d, int transposed) {
+  const int Cg = d.C / d.groups, Kg = d.K / d.groups;
+  const int span = transposed ? grouped_span(d.C, Cg, Kg, kGroupTileN)
+                              : grouped_span(d.K, Kg, Cg, kGroupTileN);
+  return (span + 63) / 64 * 64;
+}
+// widest input-channel slice of a 128-out-channel tile of the grouped weight-grad
+static int grouped_wgrad_span(const cnb_conv_desc& d) {
+  const int Cg = d.C / d.groups, Kg = d.K / d.groups;
+  return grouped_span(d.K, Kg, Cg, TILE_M);
 }
 
 static bool corners_ok(int v) { return v >= -128 && v <= 127; }
@@ -952,8 +906,12 @@ bool conv_tc_supported(const cnb_conv_desc& d, int direction, const char** why) 
   static const char* dummy;
   if (!why) why = &dummy;
   if (d.dtype != CNB_BF16) { *why = "tcgen05 path is bf16-only (fp32-IO mode uses CUDA cores)"; return false; }
-  if (d.groups != 1) { *why = "grouped convolution"; return false; }
   if (d.C % 8 != 0 || d.K % 8 != 0) { *why = "C and K must be multiples of 8 (16-byte TMA strides)"; return false; }
+  if (d.groups != 1) {
+    if (direction != CNB_WGRAD && grouped_width(d, direction == CNB_DGRAD) > kGroupMaxWidth) {
+      *why = "grouped convolution: channel slice wider than 1024"; return false;
+    }
+  }
   if (d.R * d.S > kMaxTaps) { *why = "more than 49 filter taps"; return false; }
   int P, Q;
   conv_out_dims(d, P, Q);
@@ -975,7 +933,8 @@ bool conv_tc_supported(const cnb_conv_desc& d, int direction, const char** why) 
 
 static void wgrad_geometry(const cnb_conv_desc& d, int& NT, int& taps_per_cta, int& tap_groups,
                            int& cin_tiles, int& cout_tiles, int& splits, int& pixblk_per_split) {
-  const int Cg = d.C;
+  const bool grouped = d.groups > 1;
+  const int Cg = grouped ? grouped_wgrad_span(d) : d.C;   // grouped: the slice of one out-channel tile
   NT = Cg >= 256 ? 256 : (Cg >= 128 ? 128 : 64);
   const int taps = d.R * d.S;
   int maxt = 512 / NT;
@@ -1013,10 +972,16 @@ static void wgrad_geometry(const cnb_conv_desc& d, int& NT, int& taps_per_cta, i
   splits = (int)ceil_div(total_pb, pixblk_per_split);
 }
 
+static size_t dgrad_filter_bytes(const cnb_conv_desc& d) {
+  if (d.groups > 1) return align_up((size_t)d.C * d.R * d.S * grouped_width(d, 1) * 2, 1024);
+  return align_up((size_t)d.K * d.R * d.S * d.C * 2, 1024);
+}
+
 size_t conv_tc_workspace(const cnb_conv_desc& d, int direction) {
-  if (direction == CNB_FWD) return 0;
+  if (direction == CNB_FWD)
+    return d.groups > 1 ? align_up((size_t)d.K * d.R * d.S * grouped_width(d, 0) * 2, 1024) + 1024 : 0;
   if (direction == CNB_DGRAD) {
-    size_t wt = align_up((size_t)d.K * d.R * d.S * d.C * 2, 1024);
+    size_t wt = dgrad_filter_bytes(d);
     size_t tmp = 0;
     if (d.stride_h != 1 || d.stride_w != 1) {
       // compact per-class results: each at most ceil(H/sh)*ceil(W/sw) pixels
@@ -1027,22 +992,39 @@ size_t conv_tc_workspace(const cnb_conv_desc& d, int direction) {
   }
   int NT, tpc, tg, cit, cot, splits, pps;
   wgrad_geometry(d, NT, tpc, tg, cit, cot, splits, pps);
+  if (d.groups > 1)  // dense [K][RS][NT] tiles per split; the block diagonal is extracted afterwards
+    return (size_t)splits * d.K * d.R * d.S * (cit * NT) * sizeof(float) + 1024;
   return (size_t)(splits > 1 ? splits : 0) * d.K * d.R * d.S * d.C * sizeof(float) + 1024;
 }
 
 int conv_tc_stats_rows(const cnb_conv_desc& d) {
   int P, Q;
   conv_out_dims(d, P, Q);
-  return 2 * (int)ceil_div((int64_t)d.N * P * Q, TILE_M);  // two half-tile rows per 128-pixel tile
+  const int BLOCK_N = fprop_block_n(d.K, d.groups > 1);
+  const int n_tiles = (d.K + BLOCK_N - 1) / BLOCK_N;
+  // one row per persistent CTA of an n-tile column (conv_fprop_tc_persist_k)
+  return persist_grid(ceil_div((int64_t)d.N * P * Q, TILE_M), n_tiles) / n_tiles;
 }
 
 int conv_tc_fwd(const cnb_conv_desc& d, const void* x, const void* w, const float* bias, void* y,
                 float* stats, void* ws, size_t ws_bytes, cudaStream_t st) {
-  (void)ws; (void)ws_bytes;
   FpropLaunch L;
   memset(&L, 0, sizeof(L));
   int P, Q;
   conv_out_dims(d, P, Q);
+  if (d.groups > 1) {
+    // block-diagonal expansion of the filter, rebuilt per call (a few hundred KB, one tiny kernel)
+    CNB_REQUIRE(ws && ws_bytes >= conv_tc_workspace(d, CNB_FWD), CNB_ERR_WORKSPACE,
+                "conv_tc_fwd(grouped): workspace %zu < %zu", ws_bytes, conv_tc_workspace(d, CNB_FWD));
+    const int Cg = d.C / d.groups, Kg = d.K / d.groups, wC = grouped_width(d, 0);
+    bf16* wexp = reinterpret_cast<bf16*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
+    const int64_t total = (int64_t)d.K * d.R * d.S * wC;
+    expand_grouped_filter_k<<<grid_for(total, 256), 256, 0, st>>>((const bf16*)w, wexp, d.K, d.R * d.S,
+                                                                 Cg, Kg, wC, kGroupTileN, 0);
+    CNB_TRY(check_launch("expand_grouped_filter"));
+    w = wexp;
+    L.grp_out = Kg; L.grp_in = Cg; L.wC = wC;
+  }
   L.a = x; L.aN = d.N; L.aH = d.H; L.aW = d.W; L.aC = d.C;
   L.lower_h = -d.pad_h; L.lower_w = -d.pad_w;
   L.upper_h = d.pad_h - (d.R - 1) * d.dil_h;
@@ -1075,13 +1057,23 @@ int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const v
   // transposed filter wt[C][RS][K]
   bf16* wt_ws = reinterpret_cast<bf16*>((reinterpret_cast<uintptr_t>(ws) + 1023) & ~(uintptr_t)1023);
   const bf16* wt = reinterpret_cast<const bf16*>(w_t);
-  if (!wt) {  // no pre-transposed copy from cnb_pack_filter: build it in the workspace
+  const bool grouped = d.groups > 1;
+  const int Cg = d.C / d.groups, Kg = d.K / d.groups;
+  const int wCd = grouped ? grouped_width(d, 1) : 0;
+  if (grouped) {
+    // block-diagonal expansion of the transposed filter: [C][RS][wCd] (w_t is not used)
+    const int64_t total = (int64_t)d.C * RS * wCd;
+    expand_grouped_filter_k<<<grid_for(total, 256), 256, 0, st>>>((const bf16*)w, wt_ws, d.K, RS, Cg, Kg,
+                                                                 wCd, kGroupTileN, 1);
+    CNB_TRY(check_launch("expand_grouped_filter(dgrad)"));
+    wt = wt_ws;
+  } else if (!wt) {  // no pre-transposed copy from cnb_pack_filter: build it in the workspace
     int64_t total = (int64_t)d.K * RS * d.C;
     transpose_filter_k<<<grid_for(total, 256), 256, 0, st>>>((const bf16*)w, wt_ws, d.K, RS, d.C);
     CNB_TRY(check_launch("transpose_filter"));
     wt = wt_ws;
   }
-  uint8_t* tmp_base = reinterpret_cast<uint8_t*>(wt_ws) + align_up((size_t)d.K * RS * d.C * 2, 1024);
+  uint8_t* tmp_base = reinterpret_cast<uint8_t*>(wt_ws) + dgrad_filter_bytes(d);
 
   if (d.stride_h == 1 && d.stride_w == 1) {
     FpropLaunch L;
@@ -1105,6 +1097,7 @@ int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const v
         L.widx[t] = (uint8_t)t;
       }
     L.w = wt; L.Kout = d.C; L.RS = RS;
+    if (grouped) { L.grp_out = Cg; L.grp_in = Kg; L.wC = wCd; }
     L.out = dx; L.bias = nullptr; L.flags = 0;
     L.tiled2d = (RS == 1 && d.pad_h == 0 && d.pad_w == 0);
     return launch_fprop(L, st);
@@ -1162,6 +1155,7 @@ int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const v
           L.widx[t] = (uint8_t)(rr[i] * d.S + ss[j]);
         }
       L.w = wt; L.Kout = d.C; L.RS = RS;
+      if (grouped) { L.grp_out = Cg; L.grp_in = Kg; L.wC = wCd; }
       bf16* tmp = reinterpret_cast<bf16*>(tmp_base + (size_t)cls * cls_bytes);
       L.out = tmp; L.bias = nullptr; L.flags = 0;
       L.tiled2d = false;
@@ -1201,9 +1195,11 @@ int conv_tc_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* 
   int NT;
   wgrad_geometry(d, NT, prm.taps_per_cta, prm.tap_groups, prm.cin_tiles, prm.cout_tiles, prm.splits,
                  prm.pixblk_per_split);
-  const int64_t wsz = (int64_t)d.K * RS * d.C;
+  const bool grouped = d.groups > 1;
+  const int CW = grouped ? prm.cin_tiles * NT : d.C;   // innermost extent of the kernel's output tensor
+  const int64_t wsz = (int64_t)d.K * RS * CW;
   float* part = dw;
-  if (prm.splits > 1) {
+  if (prm.splits > 1 || grouped) {
     CNB_REQUIRE(ws && ws_bytes >= (size_t)prm.splits * wsz * sizeof(float) + 1024, CNB_ERR_WORKSPACE,
                 "conv_tc_wgrad: workspace %zu < %zu", ws_bytes,
                 (size_t)prm.splits * wsz * sizeof(float) + 1024);
@@ -1229,9 +1225,9 @@ int conv_tc_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* 
   }
   prm.out = part;
   {
-    cuuint64_t gdim[4] = {(cuuint64_t)d.C, (cuuint64_t)RS, (cuuint64_t)d.K,
+    cuuint64_t gdim[4] = {(cuuint64_t)CW, (cuuint64_t)RS, (cuuint64_t)d.K,
                           (cuuint64_t)(prm.splits > 1 ? prm.splits : 1)};
-    cuuint64_t gstr[3] = {(cuuint64_t)d.C * 4, (cuuint64_t)RS * d.C * 4, (cuuint64_t)wsz * 4};
+    cuuint64_t gstr[3] = {(cuuint64_t)CW * 4, (cuuint64_t)RS * CW * 4, (cuuint64_t)wsz * 4};
     cuuint32_t box[4] = {32, 1, (cuuint32_t)TILE_M, 1};
     cuuint32_t es[4] = {1, 1, 1, 1};
     CUresult r = g_encodeTiled(&prm.tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, part, gdim, gstr, box, es,
@@ -1244,7 +1240,9 @@ int conv_tc_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* 
   prm.outP = P; prm.outQ = Q;
   prm.lower_h = -d.pad_h; prm.lower_w = -d.pad_w;
   prm.trav_h = d.stride_h; prm.trav_w = d.stride_w;
-  prm.K = d.K; prm.Cg = d.C; prm.RS = RS;
+  prm.K = d.K; prm.Cg = CW; prm.RS = RS;
+  prm.grp_out = grouped ? d.K / d.groups : 0;
+  prm.grp_in = grouped ? d.C / d.groups : 0;
   prm.num_taps = RS;
   for (int r = 0; r < d.R; ++r)
     for (int s = 0; s < d.S; ++s) {
@@ -1268,6 +1266,12 @@ int conv_tc_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* 
     else s = launch_wgrad_inst<256, 3, 5, true>(prm, grid, st);
   }
   CNB_TRY(s);
+  if (grouped) {
+    const int64_t n = (int64_t)d.K * RS * (d.C / d.groups);
+    extract_grouped_wgrad_k<<<grid_for(n, 256), 256, 0, st>>>(part, dw, prm.splits, d.K, RS,
+                                                             d.C / d.groups, d.K / d.groups, CW);
+    return check_launch("extract_grouped_wgrad");
+  }
   if (prm.splits > 1) {
     sum_splits_tc_k<<<grid_for(wsz, 256), 256, 0, st>>>(part, dw, prm.splits, wsz);
     CNB_TRY(check_launch("wgrad_sum_splits"));

