@@ -230,6 +230,47 @@ conv_simt_k(ConvP p, const T* __restrict__ src_a, const T* __restrict__ src_b,
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// 1x1 convolutions on [B, C, 1, 1] vectors (SK descriptor / attention convs, src/sknet.py:205-219):
+// a skinny GEMM out[i][j] = sum_k A[i*sAi + k*sAk] * B[k*sBk + j*sBj] with a handful of rows.  The
+// 64x64 tile kernel above would run it on one or two CTAs; here every output element gets KS = 8
+// lanes that stride the reduction (fixed-order shuffle tree -> deterministic).
+template <typename T, typename TO>
+__global__ void __launch_bounds__(256)
+vec_gemm_k(const T* __restrict__ A, int64_t sAi, int64_t sAk, const T* __restrict__ B, int64_t sBk,
+           int64_t sBj, TO* __restrict__ out, int I, int J, int Kd, const float* __restrict__ bias,
+           int flags) {
+  constexpr int KS = 8;
+  const int64_t gid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int kl = (int)(gid % KS);
+  const int64_t o = gid / KS;
+  const bool live = o < (int64_t)I * J;
+  const int i = live ? (int)(o / J) : 0, j = live ? (int)(o % J) : 0;
+  const T* a = A + i * sAi;
+  const T* b = B + j * sBj;
+  float acc0 = 0.f, acc1 = 0.f;
+  int k = kl;
+  for (; k + KS < Kd; k += 2 * KS) {
+    acc0 = fmaf(to_f(a[k * sAk]), to_f(b[k * sBk]), acc0);
+    acc1 = fmaf(to_f(a[(k + KS) * sAk]), to_f(b[(k + KS) * sBk]), acc1);
+  }
+  if (k < Kd) acc0 = fmaf(to_f(a[k * sAk]), to_f(b[k * sBk]), acc0);
+  float v = acc0 + acc1;
+#pragma unroll
+  for (int off = KS / 2; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off, KS);
+  if (live && kl == 0) {
+    if (flags & CNB_CONV_BIAS) v += bias[j];
+    if (flags & CNB_CONV_RELU) v = (v > 0.f || v != v) ? v : 0.f;
+    out[o] = from_f<TO>(v);
+  }
+}
+
+static bool is_vector_gemm(const ConvP& p) {
+  return p.G == 1 && p.R == 1 && p.S == 1 && p.H == 1 && p.W == 1 && p.P == 1 && p.Q == 1 &&
+         p.ph == 0 && p.pw == 0;
+}
+static unsigned vec_gemm_blocks(int I, int J) { return (unsigned)ceil_div((int64_t)I * J * 8, 256); }
+
 __global__ void sum_splits2_k(const float* __restrict__ part, float* __restrict__ out, int splits,
                               int64_t n) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
@@ -281,6 +322,11 @@ int conv_simt_fwd(const cnb_conv_desc& d, const void* x, const void* w, const fl
   dim3 grid((unsigned)ceil_div(Mg, BM), (unsigned)ceil_div(p.Kg, BN), p.G);
   CNB_REQUIRE(grid.y <= 65535 && grid.z <= 65535, CNB_ERR_UNSUPPORTED, "conv_simt_fwd: grid too large");
   int flags = d.flags & ((bias ? CNB_CONV_BIAS : 0) | CNB_CONV_RELU);
+  if (is_vector_gemm(p)) {  // y[n][k] = sum_c x[n][c] * w[k][c]
+    CNB_DISPATCH_T(d.dtype, (vec_gemm_k<T, T><<<vec_gemm_blocks(p.N, p.K), 256, 0, st>>>(
+                                (const T*)x, p.C, 1, (const T*)w, 1, p.C, (T*)y, p.N, p.K, p.C, bias, flags)));
+    return check_launch("conv_simt_fwd(vector)");
+  }
   CNB_DISPATCH_T(d.dtype, (conv_simt_k<T, MODE_FWD><<<grid, 256, 0, st>>>(p, (const T*)x, (const T*)w,
                                                                           y, bias, flags, 1, 0)));
   return check_launch("conv_simt_fwd");
@@ -292,6 +338,11 @@ int conv_simt_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, void*
   int64_t Mg = (int64_t)p.N * p.H * p.W;
   dim3 grid((unsigned)ceil_div(Mg, BM), (unsigned)ceil_div(p.Cg, BN), p.G);
   CNB_REQUIRE(grid.y <= 65535 && grid.z <= 65535, CNB_ERR_UNSUPPORTED, "conv_simt_dgrad: grid too large");
+  if (is_vector_gemm(p)) {  // dx[n][c] = sum_k dy[n][k] * w[k][c]
+    CNB_DISPATCH_T(d.dtype, (vec_gemm_k<T, T><<<vec_gemm_blocks(p.N, p.C), 256, 0, st>>>(
+                                (const T*)dy, p.K, 1, (const T*)w, p.C, 1, (T*)dx, p.N, p.C, p.K, nullptr, 0)));
+    return check_launch("conv_simt_dgrad(vector)");
+  }
   CNB_DISPATCH_T(d.dtype, (conv_simt_k<T, MODE_DGRAD><<<grid, 256, 0, st>>>(
                               p, (const T*)dy, (const T*)w, dx, nullptr, 0, 1, 0)));
   return check_launch("conv_simt_dgrad");
@@ -300,6 +351,11 @@ int conv_simt_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, void*
 int conv_simt_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* dw, void* ws,
                     size_t ws_bytes, cudaStream_t st) {
   ConvP p = make_convp(d);
+  if (is_vector_gemm(p)) {  // dw[k][c] = sum_n dy[n][k] * x[n][c]
+    CNB_DISPATCH_T(d.dtype, (vec_gemm_k<T, float><<<vec_gemm_blocks(p.K, p.C), 256, 0, st>>>(
+                                (const T*)dy, 1, p.K, (const T*)x, p.C, 1, dw, p.K, p.C, p.N, nullptr, 0)));
+    return check_launch("conv_simt_wgrad(vector)");
+  }
   int splits = wgrad_splits(p);
   int64_t wsz = (int64_t)p.K * p.R * p.S * p.Cg;
   int64_t Kd = (int64_t)p.N * p.P * p.Q;

@@ -4,6 +4,8 @@
 // Arithmetic intensity is ~R*S flops per 2 bytes -> HBM-bound, so the kernels are plain
 // 128-bit-vectorised NHWC gathers: one thread owns V contiguous channels of one pixel; the
 // R*S*V filter taps of a thread are read through L1 (the whole filter is <= 9*1024 elements).
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace cnb {
@@ -175,6 +177,291 @@ __global__ void dw_wgrad_k(const T* __restrict__ x, const T* __restrict__ dy,
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// 3x3 / pad 1 / dilation 1 strip kernels (every depthwise layer of MobileNet-v1 and ShuffleNet-v1).
+// A thread owns one 16-byte channel vector and walks strips of TQ adjacent outputs of one row: the
+// 9 x V filter taps stay in registers for the thread's whole lifetime (the channel vector of a
+// thread never changes: blockDim.x spans channels, rows of the thread grid span strips), and each
+// input vector is loaded once per strip and used by every (output, tap) pair it feeds — 4.5 loads
+// per output at stride 1 instead of 9 vector + 72 scalar filter loads.
+constexpr int kDwTQ = 4;
+// 4 channels per thread (8-byte bf16 / 16-byte fp32 vectors): 36 filter + 16 accumulator + 36..72
+// input registers leave room for two 256-thread CTAs per SM with ALL loads of a strip in flight
+constexpr int kDwV = 4;
+
+struct DwS {
+  int N, IH, IW, OH, OW, C;   // input / output spatial extents of THIS launch (dgrad swaps them)
+  int cv_total;               // channel vectors
+  int strips_per_row;         // ceil(OW / kDwTQ)
+  int64_t total_strips;       // N * OH * strips_per_row
+  int flags;
+};
+
+// out(oh, q) = sum_{r,s} in(oh*STRIDE - 1 + r, q*STRIDE - 1 + s) * w[r][s]   (FLIP: w[2-r][2-s],
+// which with STRIDE == 1 is exactly the data gradient of the pad-1 convolution)
+template <typename T, int STRIDE, bool FLIP>
+__global__ void __launch_bounds__(256, (STRIDE == 1 && sizeof(T) == 2) ? 2 : 1)
+dw3x3_strip_k(const T* __restrict__ in, const T* __restrict__ w, const float* __restrict__ bias,
+              T* __restrict__ out, DwS p) {
+  constexpr int V = kDwV;
+  constexpr int NCOL = kDwTQ * STRIDE + 3 - STRIDE;
+  const int cv = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cv >= p.cv_total) return;
+  const int c0 = cv * V;
+  float wr[9][V];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int j = 0; j < V; ++j) wr[t][j] = to_f(w[(int64_t)(c0 + j) * 9 + (FLIP ? 8 - t : t)]);
+  float bz[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) bz[j] = (p.flags & CNB_CONV_BIAS) ? bias[c0 + j] : 0.f;
+  const bool relu = p.flags & CNB_CONV_RELU;
+  const int64_t step = (int64_t)gridDim.y * blockDim.y;
+  for (int64_t sidx = (int64_t)blockIdx.y * blockDim.y + threadIdx.y; sidx < p.total_strips; sidx += step) {
+    const int qs = (int)(sidx % p.strips_per_row);
+    const int64_t t2 = sidx / p.strips_per_row;
+    const int oh = (int)(t2 % p.OH);
+    const int n = (int)(t2 / p.OH);
+    const int q0 = qs * kDwTQ;
+    float acc[kDwTQ][V];
+#pragma unroll
+    for (int q = 0; q < kDwTQ; ++q)
+#pragma unroll
+      for (int j = 0; j < V; ++j) acc[q][j] = bz[j];
+    const T* ib = in + (int64_t)n * p.IH * p.IW * p.C + c0;
+    const int iw0 = q0 * STRIDE - 1;
+    // issue every load of the strip (3 rows x NCOL vectors) before the first FMA
+    Pack<T, V> a[3][NCOL];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int ih = oh * STRIDE - 1 + r;
+      const bool rok = ih >= 0 && ih < p.IH;
+      const T* rowp = ib + (int64_t)ih * p.IW * p.C;
+#pragma unroll
+      for (int col = 0; col < NCOL; ++col) {
+        const int iw = iw0 + col;
+        if (rok && iw >= 0 && iw < p.IW) a[r][col] = ld_pack<T, V>(rowp + (int64_t)iw * p.C);
+        else {
+#pragma unroll
+          for (int j = 0; j < V; ++j) a[r][col].v[j] = from_f<T>(0.f);
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int q = 0; q < kDwTQ; ++q)
+#pragma unroll
+        for (int s = 0; s < 3; ++s) {
+#pragma unroll
+          for (int j = 0; j < V; ++j)
+            acc[q][j] = fmaf(to_f(a[r][q * STRIDE + s].v[j]), wr[r * 3 + s][j], acc[q][j]);
+        }
+    T* ob = out + (((int64_t)n * p.OH + oh) * p.OW + q0) * p.C + c0;
+#pragma unroll
+    for (int q = 0; q < kDwTQ; ++q) {
+      if (q0 + q < p.OW) {
+        Pack<T, V> o;
+#pragma unroll
+        for (int j = 0; j < V; ++j) {
+          float f = acc[q][j];
+          if (relu) f = (f > 0.f || f != f) ? f : 0.f;
+          o.v[j] = from_f<T>(f);
+        }
+        st_pack<T, V>(ob + (int64_t)q * p.C, o);
+      }
+    }
+  }
+}
+
+// data gradient of the stride-2 / pad-1 3x3 depthwise conv: a strip of 4 dx columns (w0 % 4 == 0)
+// of row h gathers from dy rows (h+1-r)/2, r of the parity of h+1, and dy columns w0/2 .. w0/2+2:
+//   ow0 -> (s=1: dx0, s=2: dx1)   ow1 -> (s=0: dx1, s=1: dx2, s=2: dx3)   ow2 -> (s=0: dx3)
+template <typename T>
+__global__ void __launch_bounds__(256)
+dw3x3_s2_dgrad_strip_k(const T* __restrict__ dy, const T* __restrict__ w, T* __restrict__ dx, DwS p) {
+  constexpr int V = kDwV;
+  const int cv = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cv >= p.cv_total) return;
+  const int c0 = cv * V;
+  float wr[9][V];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int j = 0; j < V; ++j) wr[t][j] = to_f(w[(int64_t)(c0 + j) * 9 + t]);
+  const int64_t step = (int64_t)gridDim.y * blockDim.y;
+  // here IH/IW are the dy extents (P, Q) and OH/OW the dx extents (H, W)
+  for (int64_t sidx = (int64_t)blockIdx.y * blockDim.y + threadIdx.y; sidx < p.total_strips; sidx += step) {
+    const int ws_ = (int)(sidx % p.strips_per_row);
+    const int64_t t2 = sidx / p.strips_per_row;
+    const int h = (int)(t2 % p.OH);
+    const int n = (int)(t2 / p.OH);
+    const int w0 = ws_ * 4;
+    float acc[4][V];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+      for (int j = 0; j < V; ++j) acc[q][j] = 0.f;
+    const T* gb = dy + (int64_t)n * p.IH * p.IW * p.C + c0;
+    const int ow0 = w0 / 2;
+    // filter row r is a compile-time constant in each call (registers, not local memory)
+    auto do_row = [&](auto rc, int oh) {
+      constexpr int r = decltype(rc)::value;
+      if (oh < 0 || oh >= p.IH) return;
+      const T* rowp = gb + (int64_t)oh * p.IW * p.C;
+      Pack<T, V> g[3];
+#pragma unroll
+      for (int o = 0; o < 3; ++o) {
+        if (ow0 + o < p.IW) g[o] = ld_pack<T, V>(rowp + (int64_t)(ow0 + o) * p.C);
+        else {
+#pragma unroll
+          for (int j = 0; j < V; ++j) g[o].v[j] = from_f<T>(0.f);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        const float g0 = to_f(g[0].v[j]), g1 = to_f(g[1].v[j]), g2 = to_f(g[2].v[j]);
+        const float k0 = wr[r * 3 + 0][j], k1 = wr[r * 3 + 1][j], k2 = wr[r * 3 + 2][j];
+        acc[0][j] = fmaf(g0, k1, acc[0][j]);
+        acc[1][j] = fmaf(g0, k2, fmaf(g1, k0, acc[1][j]));
+        acc[2][j] = fmaf(g1, k1, acc[2][j]);
+        acc[3][j] = fmaf(g1, k2, fmaf(g2, k0, acc[3][j]));
+      }
+    };
+    if (h & 1) {  // h odd: filter rows 0 and 2
+      do_row(std::integral_constant<int, 0>{}, (h + 1) >> 1);
+      do_row(std::integral_constant<int, 2>{}, (h - 1) >> 1);
+    } else {      // h even: filter row 1
+      do_row(std::integral_constant<int, 1>{}, h >> 1);
+    }
+    T* ob = dx + (((int64_t)n * p.OH + h) * p.OW + w0) * p.C + c0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (w0 + q < p.OW) {
+        Pack<T, V> o;
+#pragma unroll
+        for (int j = 0; j < V; ++j) o.v[j] = from_f<T>(acc[q][j]);
+        st_pack<T, V>(ob + (int64_t)q * p.C, o);
+      }
+    }
+  }
+}
+
+// weight gradient, same strip walk: 4 dy vectors and 3 x (4*STRIDE + 3 - STRIDE) x vectors per strip
+// feed 9 x V register accumulators; rows of the thread block are then summed through shared memory
+// three taps at a time and written as partial[split][c][9] (fixed order -> deterministic).
+template <typename T, int STRIDE>
+__global__ void __launch_bounds__(256)
+dw3x3_wgrad_strip_k(const T* __restrict__ x, const T* __restrict__ dy, float* __restrict__ part,
+                    DwS p, int64_t strips_per_split) {
+  constexpr int V = kDwV;
+  constexpr int NCOL = kDwTQ * STRIDE + 3 - STRIDE;
+  extern __shared__ float red[];  // [ry][cx * V * 3]
+  const int cv = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c0 = cv * V;
+  const bool live = cv < p.cv_total;
+  float acc[9][V];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int j = 0; j < V; ++j) acc[t][j] = 0.f;
+  // here IH/IW are the x extents and OH/OW the dy extents
+  const int64_t s0 = (int64_t)blockIdx.y * strips_per_split;
+  int64_t s1 = s0 + strips_per_split;
+  if (s1 > p.total_strips) s1 = p.total_strips;
+  if (live) {
+    for (int64_t sidx = s0 + threadIdx.y; sidx < s1; sidx += blockDim.y) {
+      const int qs = (int)(sidx % p.strips_per_row);
+      const int64_t t2 = sidx / p.strips_per_row;
+      const int oh = (int)(t2 % p.OH);
+      const int n = (int)(t2 / p.OH);
+      const int q0 = qs * kDwTQ;
+      float gf[kDwTQ][V];
+      const T* gb = dy + (((int64_t)n * p.OH + oh) * p.OW + q0) * p.C + c0;
+#pragma unroll
+      for (int q = 0; q < kDwTQ; ++q) {
+        if (q0 + q < p.OW) {
+          Pack<T, V> g = ld_pack<T, V>(gb + (int64_t)q * p.C);
+#pragma unroll
+          for (int j = 0; j < V; ++j) gf[q][j] = to_f(g.v[j]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < V; ++j) gf[q][j] = 0.f;
+        }
+      }
+      const T* ib = x + (int64_t)n * p.IH * p.IW * p.C + c0;
+      const int iw0 = q0 * STRIDE - 1;
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const int ih = oh * STRIDE - 1 + r;
+        if (ih < 0 || ih >= p.IH) continue;
+        const T* rowp = ib + (int64_t)ih * p.IW * p.C;
+        Pack<T, V> a[NCOL];
+#pragma unroll
+        for (int col = 0; col < NCOL; ++col) {
+          const int iw = iw0 + col;
+          if (iw >= 0 && iw < p.IW) a[col] = ld_pack<T, V>(rowp + (int64_t)iw * p.C);
+          else {
+#pragma unroll
+            for (int j = 0; j < V; ++j) a[col].v[j] = from_f<T>(0.f);
+          }
+        }
+#pragma unroll
+        for (int q = 0; q < kDwTQ; ++q)
+#pragma unroll
+          for (int s = 0; s < 3; ++s)
+#pragma unroll
+            for (int j = 0; j < V; ++j)
+              acc[r * 3 + s][j] = fmaf(gf[q][j], to_f(a[q * STRIDE + s].v[j]), acc[r * 3 + s][j]);
+      }
+    }
+  }
+  const int Wd = blockDim.x * V * 3;
+  const int cbase = blockIdx.x * blockDim.x * V;
+#pragma unroll
+  for (int r = 0; r < 3; ++r) {
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < 3; ++s)
+#pragma unroll
+      for (int j = 0; j < V; ++j) red[threadIdx.y * Wd + (threadIdx.x * V + j) * 3 + s] = acc[r * 3 + s][j];
+    __syncthreads();
+    for (int e = threadIdx.y * blockDim.x + threadIdx.x; e < Wd; e += blockDim.x * blockDim.y) {
+      const int c = cbase + e / 3;
+      if (c < p.C) {
+        float sum = 0.f;
+        for (int y = 0; y < (int)blockDim.y; ++y) sum += red[y * Wd + e];
+        part[((int64_t)blockIdx.y * p.C + c) * 9 + r * 3 + (e % 3)] = sum;
+      }
+    }
+  }
+}
+
+// thread-grid geometry of the strip kernels: blockDim = (cx channel vectors, 256 / cx strips)
+struct DwStripGeom { dim3 grid, block; };
+static DwStripGeom dw_strip_geom(int cv_total, int64_t strips, int waves) {
+  int cx = 1;
+  while (cx * 2 <= cv_total && cx * 2 <= 32) cx *= 2;
+  const int ry = kDwThreads / cx;
+  const int cblocks = (int)ceil_div(cv_total, cx);
+  int64_t rows = ceil_div((int64_t)sm_count() * waves, cblocks);
+  const int64_t max_rows = ceil_div(strips, ry);
+  if (rows > max_rows) rows = max_rows;
+  if (rows < 1) rows = 1;
+  if (rows > 65535) rows = 65535;
+  DwStripGeom g;
+  g.grid = dim3(cblocks, (unsigned)rows);
+  g.block = dim3(cx, ry);
+  return g;
+}
+
+static bool dw_strip_ok(const cnb_conv_desc& d, const void* a, const void* b) {
+  return d.R == 3 && d.S == 3 && d.pad_h == 1 && d.pad_w == 1 && d.dil_h == 1 && d.dil_w == 1 &&
+         d.stride_h == d.stride_w && (d.stride_h == 1 || d.stride_h == 2) && d.C % kDwV == 0 &&
+         (uintptr_t)a % 16 == 0 && (uintptr_t)b % 16 == 0;
+}
+
 __global__ void sum_splits_k(const float* __restrict__ part, float* __restrict__ out, int splits,
                              int64_t n) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
@@ -220,6 +507,20 @@ size_t dwconv_wgrad_ws(const cnb_conv_desc& d) {
 int dwconv_fwd(const cnb_conv_desc& d, const void* x, const void* w, const float* bias, void* y,
                cudaStream_t st) {
   DwP p = make_dw(d);
+  if (dw_strip_ok(d, x, y)) {
+    const int v = kDwV;
+    DwS q{p.N, p.H, p.W, p.P, p.Q, p.C, p.C / v, (int)ceil_div(p.Q, kDwTQ), 0,
+          d.flags & (((d.flags & CNB_CONV_BIAS) && bias ? CNB_CONV_BIAS : 0) | CNB_CONV_RELU)};
+    q.total_strips = (int64_t)p.N * p.P * q.strips_per_row;
+    DwStripGeom g = dw_strip_geom(q.cv_total, q.total_strips, 8);
+    if (d.stride_h == 1)
+      CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 1, false><<<g.grid, g.block, 0, st>>>(
+                                  (const T*)x, (const T*)w, bias, (T*)y, q)));
+    else
+      CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 2, false><<<g.grid, g.block, 0, st>>>(
+                                  (const T*)x, (const T*)w, bias, (T*)y, q)));
+    return check_launch("dwconv_fwd(strip)");
+  }
   int v = pick_vec(p.C, dtype_size(d.dtype), x, y);
   int64_t total = (int64_t)p.N * p.P * p.Q * (p.C / v);
   int gr = grid_for(total, kDwThreads);
@@ -237,6 +538,20 @@ int dwconv_fwd(const cnb_conv_desc& d, const void* x, const void* w, const float
 
 int dwconv_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, void* dx, cudaStream_t st) {
   DwP p = make_dw(d);
+  if (dw_strip_ok(d, dy, dx)) {
+    const int v = kDwV;
+    // input of this launch = dy (P x Q), output = dx (H x W)
+    DwS q{p.N, p.P, p.Q, p.H, p.W, p.C, p.C / v, (int)ceil_div(p.W, kDwTQ), 0, 0};
+    q.total_strips = (int64_t)p.N * p.H * q.strips_per_row;
+    DwStripGeom g = dw_strip_geom(q.cv_total, q.total_strips, 8);
+    if (d.stride_h == 1)  // H == P, W == Q: correlation with the flipped filter, pad 2 - 1 = 1
+      CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 1, true><<<g.grid, g.block, 0, st>>>(
+                                  (const T*)dy, (const T*)w, nullptr, (T*)dx, q)));
+    else
+      CNB_DISPATCH_T(d.dtype, (dw3x3_s2_dgrad_strip_k<T><<<g.grid, g.block, 0, st>>>(
+                                  (const T*)dy, (const T*)w, (T*)dx, q)));
+    return check_launch("dwconv_dgrad(strip)");
+  }
   int v = pick_vec(p.C, dtype_size(d.dtype), dy, dx);
   int64_t total = (int64_t)p.N * p.H * p.W * (p.C / v);
   CNB_DISPATCH_TV(d.dtype, v, (dw_dgrad_k<T, V><<<grid_for(total, kDwThreads), kDwThreads, 0, st>>>(
@@ -251,6 +566,31 @@ int dwconv_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* d
   CNB_REQUIRE(RS <= 25, CNB_ERR_UNSUPPORTED, "dwconv_wgrad: filter %dx%d larger than 5x5", p.R, p.S);
   CNB_REQUIRE(ws && ws_bytes >= dwconv_wgrad_ws(d), CNB_ERR_WORKSPACE,
               "dwconv_wgrad: workspace %zu < %zu", ws_bytes, dwconv_wgrad_ws(d));
+  if (dw_strip_ok(d, x, dy)) {
+    const int v = kDwV;
+    DwS q{p.N, p.H, p.W, p.P, p.Q, p.C, p.C / v, (int)ceil_div(p.Q, kDwTQ), 0, 0};
+    q.total_strips = (int64_t)p.N * p.P * q.strips_per_row;
+    DwStripGeom g = dw_strip_geom(q.cv_total, q.total_strips, 2);
+    int64_t max_splits = (int64_t)sm_count() * 4;
+    if (max_splits > 1024) max_splits = 1024;
+    int64_t splits = g.grid.y;
+    if (splits > max_splits) splits = max_splits;
+    const int64_t per = ceil_div(q.total_strips, splits);
+    splits = ceil_div(q.total_strips, per);
+    g.grid.y = (unsigned)splits;
+    const size_t smem = (size_t)g.block.y * g.block.x * v * 3 * sizeof(float);
+    float* part = (float*)ws;
+    if (d.stride_h == 1)
+      CNB_DISPATCH_T(d.dtype, (dw3x3_wgrad_strip_k<T, 1><<<g.grid, g.block, smem, st>>>(
+                                  (const T*)x, (const T*)dy, part, q, per)));
+    else
+      CNB_DISPATCH_T(d.dtype, (dw3x3_wgrad_strip_k<T, 2><<<g.grid, g.block, smem, st>>>(
+                                  (const T*)x, (const T*)dy, part, q, per)));
+    CNB_TRY(check_launch("dwconv_wgrad(strip)"));
+    int64_t n = (int64_t)p.C * 9;
+    sum_splits_k<<<grid_for(n, 256), 256, 0, st>>>(part, dw, (int)splits, n);
+    return check_launch("dwconv_wgrad_sum");
+  }
   int v = pick_vec(p.C, dtype_size(d.dtype), x, dy);
   if (v > 4) v = 4;
   if (RS > 9 && v > 2) v = 2;

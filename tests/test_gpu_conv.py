@@ -69,6 +69,13 @@ SIMT_CASES = [
     c(2, 32, 13, 13, 32, 3, pad=1, groups=32, dtype="bf16"),           # depthwise s1
     c(2, 64, 14, 14, 64, 3, pad=1, stride=2, groups=64, dtype="f32"),  # depthwise s2
     c(2, 60, 7, 7, 60, 3, pad=1, stride=2, groups=60, dtype="bf16"),   # depthwise, C % 8 != 0
+    c(2, 64, 15, 15, 64, 3, pad=1, stride=2, groups=64, dtype="bf16"), # depthwise s2, odd extent
+    c(2, 32, 7, 10, 32, 3, pad=1, groups=32, dtype="bf16", bias=True), # depthwise strips: ragged row, bias
+    c(2, 40, 9, 6, 40, 3, pad=1, stride=2, groups=40, dtype="f32"),    # depthwise s2 fp32, W < one strip pair
+    c(1, 1024, 7, 7, 1024, 3, pad=1, groups=1024, dtype="bf16"),       # MobileNet tail
+    c(3, 120, 14, 14, 120, 3, pad=1, stride=2, groups=120, dtype="bf16"),  # ShuffleNet: 15 channel vectors
+    c(16, 1024, 1, 1, 64, 1, dtype="f32"),                             # SK descriptor conv on [B,C,1,1]
+    c(16, 64, 1, 1, 1024, 1, dtype="f32", bias=True),                  # SK attention conv (vector GEMM)
 ]
 
 
