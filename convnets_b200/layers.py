@@ -14,6 +14,29 @@ from . import functional as F_
 from . import lib as _L
 
 
+# Packed operand copies of the weights are cached per layer and must be rebuilt whenever the
+# parameter changes.  The tensor version counter is NOT enough: torch's fused (multi-tensor) Adam /
+# SGD kernels update parameters without bumping it, so a global post-step hook on every optimizer
+# advances an epoch that is part of the cache key (load_state_dict / manual in-place edits still
+# move the version counter).
+_WEIGHT_EPOCH = [0]
+
+
+def _bump_weight_epoch(*_args, **_kwargs) -> None:
+    _WEIGHT_EPOCH[0] += 1
+
+
+from torch.optim.optimizer import register_optimizer_step_post_hook as _reg_post_hook  # noqa: E402
+
+_reg_post_hook(_bump_weight_epoch)
+
+
+def invalidate_packed_weights() -> None:
+    """Force every layer to re-pack its weights on the next forward (call after editing
+    parameters through a path neither an optimizer step nor the version counter sees)."""
+    _bump_weight_epoch()
+
+
 class Conv2d(nn.Conv2d):
     """nn.Conv2d whose forward / backward run in libconvnets_b200 (tcgen05 implicit GEMM for
     dense bf16 layers, CUDA cores for fp32 / grouped / depthwise)."""
@@ -40,7 +63,7 @@ class Conv2d(nn.Conv2d):
         """(operand copy of the weight in `dtype`, [C, R*S, K] copy for data-grad or None), cached
         until the parameter changes (optimizer.step() bumps its version counter)."""
         w = self.weight
-        key = (w._version, w.data_ptr(), dtype)
+        key = (_WEIGHT_EPOCH[0], w._version, w.data_ptr(), dtype)
         cache = self.__dict__.get("_cnb_pack")
         if cache is None or cache[0] != key:
             dense_tc = (dtype == torch.bfloat16 and self.groups == 1 and w.dtype == torch.float32

@@ -113,8 +113,10 @@ class MultiClassBaseModel(nn.Module):
         # multi-tensor ("fused") implementation runs it in a handful of launches instead of ~10
         # per parameter
         fused = bool(params) and all(p.is_cuda for p in params)
+        # capturable: the step counters live on the device, so the update can sit inside the CUDA
+        # graph of a whole training step (convnets_b200.graph.StepGraph)
         self.optimizer = torch.optim.Adam(params, lr=s.learning_rate, weight_decay=s.weight_decay,
-                                          fused=fused)
+                                          fused=fused, capturable=fused)
         self.lr_scheduler = torch.optim.lr_scheduler.ReduceLROnPlateau(
             self.optimizer, mode="min" if s.loss_optim else "max", factor=s.lr_factor,
             patience=s.lr_patience)
@@ -169,6 +171,18 @@ class MultiClassBaseModel(nn.Module):
         autocast + GradScaler branch (basemodel.py:253-270) is not taken."""
         self.train()
         epoch_loss, epoch_score = 0.0, 0
+        graph = getattr(self, "_cnb_step_graph", None)
+        if graph is not None:
+            # same step, replayed from one CUDA graph (convnets_b200.enable_step_graph)
+            for batch in dataloader:
+                inputs, targets = self.setting.device.move(batch)
+                loss, outputs = graph(inputs, targets)
+                epoch_loss += loss.item()
+                epoch_score += self.score(outputs, targets)
+                if self.setting.sanity_check:
+                    break
+            n = len(dataloader.dataset)
+            return epoch_loss / n, epoch_score / n
         for batch in dataloader:
             self.optimizer.zero_grad()
             loss, score = self.training_step(batch)

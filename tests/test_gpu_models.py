@@ -196,3 +196,75 @@ def test_train_model_loop_runs_and_learns():
 
     losses = [m.train_model(Loader([(x, y)]))[0] for _ in range(8)]
     assert losses[-1] < losses[0], losses
+
+
+@pytest.mark.gpu
+def test_packed_weights_follow_fused_adam():
+    """torch's fused Adam updates parameters WITHOUT bumping their version counter; the cached bf16
+    operand copies must still be rebuilt after every optimizer step (layers._WEIGHT_EPOCH)."""
+    from convnets_b200 import layers as L
+    model, _, s = _build("ResNeXt", "50", 32, torch.bfloat16)
+    model.init_optimizer()
+    model.train()
+    g = torch.Generator().manual_seed(5)
+    convs = [m for m in model.modules() if isinstance(m, L.Conv2d) and not m.cast_input]
+    assert any(m.groups > 1 for m in convs) and any(m.groups == 1 for m in convs)
+    for step in range(3):
+        x = torch.randn(4, 3, 32, 32, generator=g).cuda()
+        y = torch.randint(0, 10, (4,), generator=g).cuda()
+        model.optimizer.zero_grad()
+        loss = model.cost_function(model(x).float(), y)
+        for m in convs:  # the copy the forward just used == the current weight, rounded
+            wb = m.__dict__["_cnb_pack"][1][0]
+            assert torch.equal(wb.float(), m.weight.detach().to(torch.bfloat16).float()), (step, m)
+        loss.backward()
+        model.optimizer.step()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("family,kind", [("ResNet", "18"), ("MobileNetV1", ""), ("SKResNet", "26")])
+def test_step_graph_matches_eager_steps(family, kind):
+    """The CUDA-graph replay of the training step (convnets_b200.graph.StepGraph) must walk the
+    same trajectory as the eagerly enqueued reference loop — every kernel of the library is
+    deterministic, so losses and weights agree to rounding after six Adam steps (three eager, one
+    capture + replay, two replays) on changing batches."""
+    import convnets_b200 as cnb
+
+    def make():
+        model, _, s = _build(family, kind, 32, torch.bfloat16)
+        model.init_optimizer()
+        model.train()
+        return model
+
+    g = torch.Generator().manual_seed(3)
+    batches = [(torch.randn(8, 3, 32, 32, generator=g).cuda(), torch.randint(0, 10, (8,), generator=g).cuda())
+               for _ in range(6)]
+    eager, graphed = make(), make()
+    graphed.load_state_dict(eager.state_dict())
+    sg = cnb.StepGraph(graphed, eager_steps=3)
+    for i, (x, y) in enumerate(batches):
+        eager.optimizer.zero_grad()
+        out = eager(x)
+        l0 = eager.cost_function(out.float(), y)
+        l0.backward()
+        eager.optimizer.step()
+        l1, _ = sg(x, y)
+        assert abs(l0.item() - l1.item()) <= 1e-5 * max(1.0, abs(l0.item())), (i, l0.item(), l1.item())
+    assert sg.graph is not None and sg.launches_per_step > 0
+    worst = 0.0
+    for (k, a), (_, b) in zip(eager.named_parameters(), graphed.named_parameters()):
+        worst = max(worst, O.rel_l2(b.detach(), a.detach()))
+    assert worst <= 1e-5, worst
+    # train_model goes through the graph once it is enabled
+    cnb.enable_step_graph(graphed, eager_steps=0)
+    loss, acc = graphed.train_model(_Loader(batches[:2]))
+    assert loss == loss and 0.0 <= acc <= 1.0
+
+
+class _Loader:
+    def __init__(self, batches):
+        self.batches = batches
+        self.dataset = range(sum(int(b[1].numel()) for b in batches))
+
+    def __iter__(self):
+        return iter(self.batches)
