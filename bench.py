@@ -428,9 +428,23 @@ def run_ours(args):
         if sync is not None:
             line["config"]["allreduces_per_step"] = len(sync.buckets)
         print(json.dumps(line), flush=True)
+    sys.stdout.flush()
     if world > 1:
+        # Tear-down: destroying a NCCL communicator whose collectives were captured into a live CUDA
+        # graph can block (seen at N=2: the JSON line was out, destroy_process_group never returned).
+        # The results are printed; release the graph, meet at a barrier under a watchdog, and leave
+        # without running the communicator destructors.
+        import threading
+        wd = threading.Timer(30.0, lambda: os._exit(0))
+        wd.daemon = True
+        wd.start()
+        if sg is not None and sg.graph is not None:
+            sg.graph.reset()
+            sg.graph = None
+        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():
