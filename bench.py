@@ -384,6 +384,15 @@ def run_ours(args):
         else:
             roof = {"bound": "hbm", "achieved": f["gbs"], "peak": pk["hbm"], "unit": "GB/s",
                     "frac": f["gbs"] / pk["hbm"], "traffic": None}
+        # DRAM bytes actually moved per call of this family, from the committed ncu capture
+        tpath = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tpath) and args.model == "resnet50" and args.hw == 224 and B == 256:
+            with open(tpath) as fh:
+                tj = json.load(fh).get(name)
+            if tj:
+                roof["traffic"] = tj["dram_bytes_per_call"]
+                roof["traffic_source"] = tj["source"]
+                roof["algorithmic_bytes_per_call"] = f["bytes"] / per
         roof.update({"kernel": name, "launches_per_step": per, "avg_launch_ms": f["ms"] / per,
                      "share_of_step": f["share"], "peak_source": pk["src"] +
                      (" (sustained cuBLAS bf16)" if roof["bound"] == "tensor" else " (copy)"),

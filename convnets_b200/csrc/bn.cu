@@ -532,8 +532,10 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
   if (conv_partials) {
     // statistics were accumulated by the producing convolution's epilogue: merge its per-tile rows
     BnGeom g;
-    g.V = 1; g.cx = 64; g.ry = kBnThreads / 64;
-    g.cblocks = (int)ceil_div(C, 64);
+    // <= 512 rows (one per persistent conv CTA): 16 channels x 16 row lanes per CTA keeps the
+    // serial chain of dependent L2 loads per thread to ~5 trips and spreads C over C/16 CTAs
+    g.V = 1; g.cx = n_partials <= 512 ? 16 : 64; g.ry = kBnThreads / g.cx;
+    g.cblocks = (int)ceil_div(C, g.cx);
     int64_t splits = ceil_div((int64_t)sm_count() * 2, g.cblocks);
     int64_t max_splits = ceil_div((int64_t)n_partials, (int64_t)g.ry * 4);
     if (splits > max_splits) splits = max_splits;

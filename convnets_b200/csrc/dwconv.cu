@@ -4,6 +4,8 @@
 // Arithmetic intensity is ~R*S flops per 2 bytes -> HBM-bound, so the kernels are plain
 // 128-bit-vectorised NHWC gathers: one thread owns V contiguous channels of one pixel; the
 // R*S*V filter taps of a thread are read through L1 (the whole filter is <= 9*1024 elements).
+#include <stdlib.h>
+
 #include <type_traits>
 
 #include "common.cuh"
@@ -275,6 +277,98 @@ dw3x3_strip_k(const T* __restrict__ in, const T* __restrict__ w, const float* __
   }
 }
 
+// Stride-1 column walk (bf16): a thread owns 4 channels x 4 output columns and walks kDwRH output
+// rows DOWN the image with a 4-slot register ring of input rows — every input row is loaded once
+// per walk instead of three times (once per filter row), and the row needed two steps ahead is
+// requested before the current output row is computed.  Units = (image, row block, column strip).
+constexpr int kDwRH = 8;
+
+template <typename T, bool FLIP>
+__global__ void __launch_bounds__(128, 3)
+dw3x3_s1_walk_k(const T* __restrict__ in, const T* __restrict__ w, const float* __restrict__ bias,
+                T* __restrict__ out, DwS p, int row_blocks) {
+  constexpr int V = kDwV;
+  constexpr int NCOL = kDwTQ + 2;
+  const int cv = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cv >= p.cv_total) return;
+  const int c0 = cv * V;
+  float wr[9][V];
+#pragma unroll
+  for (int t = 0; t < 9; ++t)
+#pragma unroll
+    for (int j = 0; j < V; ++j) wr[t][j] = to_f(w[(int64_t)(c0 + j) * 9 + (FLIP ? 8 - t : t)]);
+  float bz[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) bz[j] = (p.flags & CNB_CONV_BIAS) ? bias[c0 + j] : 0.f;
+  const bool relu = p.flags & CNB_CONV_RELU;
+  const int64_t units = (int64_t)p.N * row_blocks * p.strips_per_row;
+  const int64_t step = (int64_t)gridDim.y * blockDim.y;
+  for (int64_t u = (int64_t)blockIdx.y * blockDim.y + threadIdx.y; u < units; u += step) {
+    const int qs = (int)(u % p.strips_per_row);
+    const int64_t t2 = u / p.strips_per_row;
+    const int rb = (int)(t2 % row_blocks);
+    const int n = (int)(t2 / row_blocks);
+    const int q0 = qs * kDwTQ;
+    const int oh0 = rb * kDwRH;
+    const T* ib = in + (int64_t)n * p.IH * p.IW * p.C + c0;
+    T* ob = out + ((int64_t)n * p.OH * p.OW + q0) * p.C + c0;
+    const int iw0 = q0 - 1;
+    Pack<T, V> S[4][NCOL];
+    auto ld_row = [&](Pack<T, V>(&dst)[NCOL], int ih) {
+      const bool rok = ih >= 0 && ih < p.IH;
+      const T* rowp = ib + (int64_t)ih * p.IW * p.C;
+#pragma unroll
+      for (int col = 0; col < NCOL; ++col) {
+        const int iw = iw0 + col;
+        if (rok && iw >= 0 && iw < p.IW) dst[col] = ld_pack<T, V>(rowp + (int64_t)iw * p.C);
+        else {
+#pragma unroll
+          for (int j = 0; j < V; ++j) dst[col].v[j] = from_f<T>(0.f);
+        }
+      }
+    };
+    ld_row(S[0], oh0 - 1);
+    ld_row(S[1], oh0);
+    ld_row(S[2], oh0 + 1);
+#pragma unroll 1
+    for (int kk = 0; kk < kDwRH; kk += 4)
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {  // ring slots are compile-time constants inside this loop
+      ld_row(S[(k + 3) & 3], oh0 + kk + k + 2);  // needed by output row kk + k + 1
+      const int oh = oh0 + kk + k;
+      if (oh < p.OH) {
+        float acc[kDwTQ][V];
+#pragma unroll
+        for (int q = 0; q < kDwTQ; ++q)
+#pragma unroll
+          for (int j = 0; j < V; ++j) acc[q][j] = bz[j];
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int q = 0; q < kDwTQ; ++q)
+#pragma unroll
+            for (int sx = 0; sx < 3; ++sx)
+#pragma unroll
+              for (int j = 0; j < V; ++j)
+                acc[q][j] = fmaf(to_f(S[(k + r) & 3][q + sx].v[j]), wr[r * 3 + sx][j], acc[q][j]);
+#pragma unroll
+        for (int q = 0; q < kDwTQ; ++q) {
+          if (q0 + q < p.OW) {
+            Pack<T, V> o;
+#pragma unroll
+            for (int j = 0; j < V; ++j) {
+              float f = acc[q][j];
+              if (relu) f = (f > 0.f || f != f) ? f : 0.f;
+              o.v[j] = from_f<T>(f);
+            }
+            st_pack<T, V>(ob + ((int64_t)oh * p.OW + q) * p.C, o);
+          }
+        }
+      }
+    }
+  }
+}
+
 // data gradient of the stride-2 / pad-1 3x3 depthwise conv: a strip of 4 dx columns (w0 % 4 == 0)
 // of row h gathers from dy rows (h+1-r)/2, r of the parity of h+1, and dy columns w0/2 .. w0/2+2:
 //   ow0 -> (s=1: dx0, s=2: dx1)   ow1 -> (s=0: dx1, s=1: dx2, s=2: dx3)   ow2 -> (s=0: dx3)
@@ -440,10 +534,10 @@ dw3x3_wgrad_strip_k(const T* __restrict__ x, const T* __restrict__ dy, float* __
 
 // thread-grid geometry of the strip kernels: blockDim = (cx channel vectors, 256 / cx strips)
 struct DwStripGeom { dim3 grid, block; };
-static DwStripGeom dw_strip_geom(int cv_total, int64_t strips, int waves) {
+static DwStripGeom dw_strip_geom(int cv_total, int64_t strips, int waves, int threads = kDwThreads) {
   int cx = 1;
   while (cx * 2 <= cv_total && cx * 2 <= 32) cx *= 2;
-  const int ry = kDwThreads / cx;
+  const int ry = threads / cx;
   const int cblocks = (int)ceil_div(cv_total, cx);
   int64_t rows = ceil_div((int64_t)sm_count() * waves, cblocks);
   const int64_t max_rows = ceil_div(strips, ry);
@@ -454,6 +548,16 @@ static DwStripGeom dw_strip_geom(int cv_total, int64_t strips, int waves) {
   g.grid = dim3(cblocks, (unsigned)rows);
   g.block = dim3(cx, ry);
   return g;
+}
+
+// CNB_DW_WALK=0 keeps the per-strip kernel for stride-1 layers (A/B measurement)
+static bool dw_walk_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("CNB_DW_WALK");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
 }
 
 static bool dw_strip_ok(const cnb_conv_desc& d, const void* a, const void* b) {
@@ -513,6 +617,13 @@ int dwconv_fwd(const cnb_conv_desc& d, const void* x, const void* w, const float
           d.flags & (((d.flags & CNB_CONV_BIAS) && bias ? CNB_CONV_BIAS : 0) | CNB_CONV_RELU)};
     q.total_strips = (int64_t)p.N * p.P * q.strips_per_row;
     DwStripGeom g = dw_strip_geom(q.cv_total, q.total_strips, 8);
+    if (d.stride_h == 1 && d.dtype == CNB_BF16 && dw_walk_enabled()) {
+      const int rbs = (int)ceil_div(p.P, kDwRH);
+      DwStripGeom gw = dw_strip_geom(q.cv_total, (int64_t)p.N * rbs * q.strips_per_row, 12, 128);
+      dw3x3_s1_walk_k<bf16, false><<<gw.grid, gw.block, 0, st>>>((const bf16*)x, (const bf16*)w, bias,
+                                                                 (bf16*)y, q, rbs);
+      return check_launch("dwconv_fwd(walk)");
+    }
     if (d.stride_h == 1)
       CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 1, false><<<g.grid, g.block, 0, st>>>(
                                   (const T*)x, (const T*)w, bias, (T*)y, q)));
@@ -544,6 +655,13 @@ int dwconv_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, void* dx
     DwS q{p.N, p.P, p.Q, p.H, p.W, p.C, p.C / v, (int)ceil_div(p.W, kDwTQ), 0, 0};
     q.total_strips = (int64_t)p.N * p.H * q.strips_per_row;
     DwStripGeom g = dw_strip_geom(q.cv_total, q.total_strips, 8);
+    if (d.stride_h == 1 && d.dtype == CNB_BF16 && dw_walk_enabled()) {
+      const int rbs = (int)ceil_div(p.H, kDwRH);
+      DwStripGeom gw = dw_strip_geom(q.cv_total, (int64_t)p.N * rbs * q.strips_per_row, 12, 128);
+      dw3x3_s1_walk_k<bf16, true><<<gw.grid, gw.block, 0, st>>>((const bf16*)dy, (const bf16*)w, nullptr,
+                                                                (bf16*)dx, q, rbs);
+      return check_launch("dwconv_dgrad(walk)");
+    }
     if (d.stride_h == 1)  // H == P, W == Q: correlation with the flipped filter, pad 2 - 1 = 1
       CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 1, true><<<g.grid, g.block, 0, st>>>(
                                   (const T*)dy, (const T*)w, nullptr, (T*)dx, q)));

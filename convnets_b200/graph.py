@@ -17,6 +17,8 @@ every replay sees the weights the previous replay's Adam step produced.
 """
 from __future__ import annotations
 
+import gc
+
 import torch
 
 from . import functional as F_
@@ -71,8 +73,18 @@ class StepGraph:
         n0 = _L.launch_count()
         if self.stream is None:
             self.stream = torch.cuda.Stream(device=dev)
-        with torch.cuda.graph(g, stream=self.stream):
-            self.loss, self.logits = self._step(self.x, self.y)
+        # No garbage collection while the stream is capturing: a collected cycle that owns CUDA
+        # resources (an older model, graph or event) would issue cudaFree / cudaGraphExecDestroy
+        # in the middle of the capture and invalidate it (seen once in the full GPU test run).
+        gc.collect()
+        gc_was_enabled = gc.isenabled()
+        gc.disable()
+        try:
+            with torch.cuda.graph(g, stream=self.stream):
+                self.loss, self.logits = self._step(self.x, self.y)
+        finally:
+            if gc_was_enabled:
+                gc.enable()
         self.launches_per_step = _L.launch_count() - n0
         F_._workspaces.clear()      # eager code must not reuse the graph's scratch buffers
         self.graph = g
