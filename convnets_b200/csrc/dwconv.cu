@@ -201,12 +201,12 @@ struct DwS {
 
 // out(oh, q) = sum_{r,s} in(oh*STRIDE - 1 + r, q*STRIDE - 1 + s) * w[r][s]   (FLIP: w[2-r][2-s],
 // which with STRIDE == 1 is exactly the data gradient of the pad-1 convolution)
-template <typename T, int STRIDE, bool FLIP>
-__global__ void __launch_bounds__(256, (STRIDE == 1 && sizeof(T) == 2) ? 2 : 1)
+template <typename T, int STRIDE, bool FLIP, int TQ = kDwTQ>
+__global__ void __launch_bounds__(256, sizeof(T) == 2 ? 2 : 1)
 dw3x3_strip_k(const T* __restrict__ in, const T* __restrict__ w, const float* __restrict__ bias,
               T* __restrict__ out, DwS p) {
   constexpr int V = kDwV;
-  constexpr int NCOL = kDwTQ * STRIDE + 3 - STRIDE;
+  constexpr int NCOL = TQ * STRIDE + 3 - STRIDE;
   const int cv = blockIdx.x * blockDim.x + threadIdx.x;
   if (cv >= p.cv_total) return;
   const int c0 = cv * V;
@@ -225,10 +225,10 @@ dw3x3_strip_k(const T* __restrict__ in, const T* __restrict__ w, const float* __
     const int64_t t2 = sidx / p.strips_per_row;
     const int oh = (int)(t2 % p.OH);
     const int n = (int)(t2 / p.OH);
-    const int q0 = qs * kDwTQ;
-    float acc[kDwTQ][V];
+    const int q0 = qs * TQ;
+    float acc[TQ][V];
 #pragma unroll
-    for (int q = 0; q < kDwTQ; ++q)
+    for (int q = 0; q < TQ; ++q)
 #pragma unroll
       for (int j = 0; j < V; ++j) acc[q][j] = bz[j];
     const T* ib = in + (int64_t)n * p.IH * p.IW * p.C + c0;
@@ -253,7 +253,7 @@ dw3x3_strip_k(const T* __restrict__ in, const T* __restrict__ w, const float* __
 #pragma unroll
     for (int r = 0; r < 3; ++r)
 #pragma unroll
-      for (int q = 0; q < kDwTQ; ++q)
+      for (int q = 0; q < TQ; ++q)
 #pragma unroll
         for (int s = 0; s < 3; ++s) {
 #pragma unroll
@@ -262,7 +262,7 @@ dw3x3_strip_k(const T* __restrict__ in, const T* __restrict__ w, const float* __
         }
     T* ob = out + (((int64_t)n * p.OH + oh) * p.OW + q0) * p.C + c0;
 #pragma unroll
-    for (int q = 0; q < kDwTQ; ++q) {
+    for (int q = 0; q < TQ; ++q) {
       if (q0 + q < p.OW) {
         Pack<T, V> o;
 #pragma unroll
@@ -627,9 +627,14 @@ int dwconv_fwd(const cnb_conv_desc& d, const void* x, const void* w, const float
     if (d.stride_h == 1)
       CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 1, false><<<g.grid, g.block, 0, st>>>(
                                   (const T*)x, (const T*)w, bias, (T*)y, q)));
-    else
-      CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 2, false><<<g.grid, g.block, 0, st>>>(
+    else {
+      // stride 2: strips of 2 outputs (3 x 5 input vectors) keep two CTAs per SM resident
+      q.strips_per_row = (int)ceil_div(p.Q, 2);
+      q.total_strips = (int64_t)p.N * p.P * q.strips_per_row;
+      g = dw_strip_geom(q.cv_total, q.total_strips, 8);
+      CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 2, false, 2><<<g.grid, g.block, 0, st>>>(
                                   (const T*)x, (const T*)w, bias, (T*)y, q)));
+    }
     return check_launch("dwconv_fwd(strip)");
   }
   int v = pick_vec(p.C, dtype_size(d.dtype), x, y);
