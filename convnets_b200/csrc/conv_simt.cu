@@ -271,6 +271,210 @@ static bool is_vector_gemm(const ConvP& p) {
 }
 static unsigned vec_gemm_blocks(int I, int J) { return (unsigned)ceil_div((int64_t)I * J * 8, 256); }
 
+// ------------------------------------------------------------------------------------------
+// Pointwise (1x1, stride 1) convolutions with narrow groups that the TMA path cannot address
+// (C or K not a multiple of 8: ShuffleNet-g3 stage 2 has 60-channel tensors = 120-byte rows).
+// They are skinny GEMMs — hundreds of thousands of pixels against <= 96 x 96 channels per group —
+// and HBM-bound, but the generic 64x64 tile above fills 20 of its 64 columns and loads scalars.
+//   pw_gemm_k  : out[m][n0 + j] = sum_k A[m][a0 + k] * B[k][j]   (forward and data-grad)
+//                CTA = (128 pixels, one group); the group's whole filter and the A tile (stored
+//                k-major) sit in shared memory as fp32; a thread owns 4 pixels x 4 channels and
+//                reads two 16-byte vectors per 16 FMAs.
+//   pw_wgrad_k : dW[k][c] = sum_m dy[m][k] * x[m][c] per group, split over pixel ranges; 64-pixel
+//                chunks of dy and x are staged in shared memory, a thread owns a 4 x 4 tile of dW
+//                (several thread lanes share a tile when the group is small and are summed in a
+//                fixed order at the end) -> fp32 partials -> sum_splits2_k.
+constexpr int PW_BM = 128, PW_MAXD = 96, PW_RC = 64;
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+pw_gemm_k(const T* __restrict__ A, int lda, const T* __restrict__ W, int64_t sWk, int64_t sWj,
+          int64_t sWg, T* __restrict__ out, int ldo, int64_t M, int Kd, int Ng,
+          const float* __restrict__ bias, int flags) {
+  extern __shared__ __align__(16) float pw_smem[];
+  const int Np = (Ng + 3) & ~3;
+  constexpr int LDA = PW_BM + 4;
+  float* Bs = pw_smem;                 // [Kd][Np]
+  float* As = pw_smem + Kd * Np;       // [Kd][LDA]  (k-major: 4 pixels of one k are one float4)
+  const int t = threadIdx.x;
+  const int g = blockIdx.y;
+  const int64_t m0 = (int64_t)blockIdx.x * PW_BM;
+  const int a0 = g * Kd, n0 = g * Ng;
+  const T* Wg = W + g * sWg;
+  for (int i = t; i < Kd * Np; i += 256) {
+    const int k = i / Np, j = i - k * Np;
+    Bs[i] = j < Ng ? to_f(Wg[k * sWk + j * sWj]) : 0.f;
+  }
+  for (int i = t; i < PW_BM * Kd; i += 256) {
+    const int m = i / Kd, k = i - m * Kd;
+    const int64_t row = m0 + m;
+    As[k * LDA + m] = row < M ? to_f(A[row * lda + a0 + k]) : 0.f;
+  }
+  __syncthreads();
+  const int rgp = t & 31;
+  for (int cg = t >> 5; cg < Np / 4; cg += 8) {
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    const float* ap = As + rgp * 4;
+    const float* bp = Bs + cg * 4;
+#pragma unroll 4
+    for (int k = 0; k < Kd; ++k) {
+      const float4 a = *reinterpret_cast<const float4*>(ap + k * LDA);
+      const float4 b = *reinterpret_cast<const float4*>(bp + k * Np);
+      const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int64_t row = m0 + rgp * 4 + i;
+      if (row >= M) continue;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int col = cg * 4 + j;
+        if (col >= Ng) continue;
+        float v = acc[i][j];
+        if (flags & CNB_CONV_BIAS) v += bias[n0 + col];
+        if (flags & CNB_CONV_RELU) v = (v > 0.f || v != v) ? v : 0.f;
+        out[row * ldo + n0 + col] = from_f<T>(v);
+      }
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+pw_wgrad_k(const T* __restrict__ dy, int ldy, const T* __restrict__ x, int ldx,
+           float* __restrict__ part, int64_t M, int Kg, int Cg, int K, int64_t rows_per_split) {
+  extern __shared__ __align__(16) float pw_smem[];
+  const int Kp = (Kg + 3) & ~3, Cp = (Cg + 3) & ~3;
+  float* dys = pw_smem;                  // [PW_RC][Kp]
+  float* xs = pw_smem + PW_RC * Kp;      // [PW_RC][Cp]
+  const int t = threadIdx.x;
+  const int g = blockIdx.y;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_split;
+  int64_t r1 = r0 + rows_per_split;
+  if (r1 > M) r1 = M;
+  const int ctiles = Cp / 4;
+  const int tiles = (Kp / 4) * ctiles;
+  // few tiles: several row lanes per tile; many tiles: up to 3 tiles per thread, one lane
+  const int lanes = tiles < 256 ? 256 / tiles : 1;
+  const int lane = tiles < 256 ? t / tiles : 0;
+  const int tile0 = tiles < 256 ? t % tiles : t;
+  const bool live = lane < lanes;
+  float acc[3][4][4];
+#pragma unroll
+  for (int s = 0; s < 3; ++s)
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[s][i][j] = 0.f;
+  for (int i = t; i < PW_RC * (Kp + Cp); i += 256) pw_smem[i] = 0.f;  // padding columns stay zero
+  for (int64_t mb = r0; mb < r1; mb += PW_RC) {
+    __syncthreads();
+    for (int i = t; i < PW_RC * Kg; i += 256) {
+      const int m = i / Kg, k = i - m * Kg;
+      dys[m * Kp + k] = mb + m < r1 ? to_f(dy[(mb + m) * ldy + g * Kg + k]) : 0.f;
+    }
+    for (int i = t; i < PW_RC * Cg; i += 256) {
+      const int m = i / Cg, c = i - m * Cg;
+      xs[m * Cp + c] = mb + m < r1 ? to_f(x[(mb + m) * ldx + g * Cg + c]) : 0.f;
+    }
+    __syncthreads();
+    if (live) {
+#pragma unroll
+      for (int s = 0; s < 3; ++s) {
+        const int tile = tile0 + s * 256;
+        if (tile < tiles && (s == 0 || tiles >= 256)) {
+          const int kt = tile / ctiles, ct = tile - kt * ctiles;
+          for (int m = lane; m < PW_RC; m += lanes) {
+            const float4 a = *reinterpret_cast<const float4*>(dys + m * Kp + kt * 4);
+            const float4 b = *reinterpret_cast<const float4*>(xs + m * Cp + ct * 4);
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+              for (int j = 0; j < 4; ++j) acc[s][i][j] = fmaf(av[i], bv[j], acc[s][i][j]);
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();
+  float* outp = part + ((int64_t)blockIdx.x * K + (int64_t)g * Kg) * Cg;
+  if (tiles >= 256) {
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+      const int tile = tile0 + s * 256;
+      if (tile < tiles) {
+        const int kt = tile / ctiles, ct = tile - kt * ctiles;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (kt * 4 + i < Kg && ct * 4 + j < Cg) outp[(kt * 4 + i) * Cg + ct * 4 + j] = acc[s][i][j];
+      }
+    }
+    return;
+  }
+  // sum the row lanes of each tile in lane order through shared memory ([lanes][tiles][16] floats)
+  float* red = pw_smem;
+  if (live) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) red[(lane * tiles + tile0) * 16 + i * 4 + j] = acc[0][i][j];
+  }
+  __syncthreads();
+  for (int e = t; e < tiles * 16; e += 256) {
+    const int tile = e / 16, ij = e - tile * 16;
+    float sum = 0.f;
+    for (int l = 0; l < lanes; ++l) sum += red[(l * tiles + tile) * 16 + ij];
+    const int kt = tile / ctiles, ct = tile - kt * ctiles;
+    const int k = kt * 4 + ij / 4, c = ct * 4 + (ij & 3);
+    if (k < Kg && c < Cg) outp[k * Cg + c] = sum;
+  }
+}
+
+static bool is_pointwise_narrow(const ConvP& p) {
+  return p.R == 1 && p.S == 1 && p.sh == 1 && p.sw == 1 && p.ph == 0 && p.pw == 0 &&
+         p.Cg <= PW_MAXD && p.Kg <= PW_MAXD;
+}
+static size_t pw_gemm_smem(int Kd, int Ng) {
+  return ((size_t)Kd * ((Ng + 3) & ~3) + (size_t)Kd * (PW_BM + 4)) * sizeof(float);
+}
+static size_t pw_wgrad_smem(int Kg, int Cg) {
+  const size_t kp = (Kg + 3) & ~3, cp = (Cg + 3) & ~3;
+  size_t stage = PW_RC * (kp + cp) * sizeof(float);
+  size_t red = 256 * 16 * sizeof(float);
+  return stage > red ? stage : red;
+}
+static int pw_wgrad_splits(const ConvP& p) {
+  const int64_t M = (int64_t)p.N * p.P * p.Q;
+  int64_t want = ceil_div((int64_t)sm_count() * 4, p.G);
+  const int64_t maxs = ceil_div(M, 4 * PW_RC);
+  if (want > maxs) want = maxs;
+  if (want < 1) want = 1;
+  return (int)want;
+}
+// opt in to 100 KB of dynamic shared memory, once per kernel instantiation (T = its element type)
+template <typename T, int WHICH, typename K>
+static int pw_set_smem(K kern, size_t bytes, const char* what) {
+  static bool done = false;
+  CNB_REQUIRE(bytes <= 100 * 1024, CNB_ERR_UNSUPPORTED, "%s: shared memory %zu > 100 KB", what, bytes);
+  if (!done) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e));
+    done = true;
+  }
+  return CNB_OK;
+}
+
 __global__ void sum_splits2_k(const float* __restrict__ part, float* __restrict__ out, int splits,
                               int64_t n) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
@@ -312,6 +516,7 @@ static int wgrad_splits(const ConvP& p) {
 size_t conv_simt_wgrad_ws(const cnb_conv_desc& d) {
   ConvP p = make_convp(d);
   int splits = wgrad_splits(p);
+  if (is_pointwise_narrow(p) && !is_vector_gemm(p)) splits = pw_wgrad_splits(p);
   return (size_t)splits * p.K * p.R * p.S * p.Cg * sizeof(float) + 256;
 }
 
@@ -322,6 +527,17 @@ int conv_simt_fwd(const cnb_conv_desc& d, const void* x, const void* w, const fl
   dim3 grid((unsigned)ceil_div(Mg, BM), (unsigned)ceil_div(p.Kg, BN), p.G);
   CNB_REQUIRE(grid.y <= 65535 && grid.z <= 65535, CNB_ERR_UNSUPPORTED, "conv_simt_fwd: grid too large");
   int flags = d.flags & ((bias ? CNB_CONV_BIAS : 0) | CNB_CONV_RELU);
+  if (!is_vector_gemm(p) && is_pointwise_narrow(p)) {
+    // y[m][g*Kg + j] = sum_c x[m][g*Cg + c] * w[g*Kg + j][c]:  B[k=c][j] = w[(g*Kg + j)*Cg + c]
+    const size_t smem = pw_gemm_smem(p.Cg, p.Kg);
+    dim3 pgrid((unsigned)ceil_div(Mg, PW_BM), p.G);
+    CNB_DISPATCH_T(d.dtype, {
+      CNB_TRY((pw_set_smem<T, 0>(pw_gemm_k<T>, smem, "conv_simt_fwd(pointwise)")));
+      pw_gemm_k<T><<<pgrid, 256, smem, st>>>((const T*)x, p.C, (const T*)w, 1, p.Cg, (int64_t)p.Kg * p.Cg,
+                                             (T*)y, p.K, Mg, p.Cg, p.Kg, bias, flags);
+    });
+    return check_launch("conv_simt_fwd(pointwise)");
+  }
   if (is_vector_gemm(p)) {  // y[n][k] = sum_c x[n][c] * w[k][c]
     CNB_DISPATCH_T(d.dtype, (vec_gemm_k<T, T><<<vec_gemm_blocks(p.N, p.K), 256, 0, st>>>(
                                 (const T*)x, p.C, 1, (const T*)w, 1, p.C, (T*)y, p.N, p.K, p.C, bias, flags)));
@@ -338,6 +554,17 @@ int conv_simt_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, void*
   int64_t Mg = (int64_t)p.N * p.H * p.W;
   dim3 grid((unsigned)ceil_div(Mg, BM), (unsigned)ceil_div(p.Cg, BN), p.G);
   CNB_REQUIRE(grid.y <= 65535 && grid.z <= 65535, CNB_ERR_UNSUPPORTED, "conv_simt_dgrad: grid too large");
+  if (!is_vector_gemm(p) && is_pointwise_narrow(p)) {
+    // dx[m][g*Cg + c] = sum_k dy[m][g*Kg + k] * w[g*Kg + k][c]:  B[k][j=c] = w[(g*Kg + k)*Cg + c]
+    const size_t smem = pw_gemm_smem(p.Kg, p.Cg);
+    dim3 pgrid((unsigned)ceil_div(Mg, PW_BM), p.G);
+    CNB_DISPATCH_T(d.dtype, {
+      CNB_TRY((pw_set_smem<T, 0>(pw_gemm_k<T>, smem, "conv_simt_dgrad(pointwise)")));
+      pw_gemm_k<T><<<pgrid, 256, smem, st>>>((const T*)dy, p.K, (const T*)w, p.Cg, 1, (int64_t)p.Kg * p.Cg,
+                                             (T*)dx, p.C, Mg, p.Kg, p.Cg, nullptr, 0);
+    });
+    return check_launch("conv_simt_dgrad(pointwise)");
+  }
   if (is_vector_gemm(p)) {  // dx[n][c] = sum_k dy[n][k] * w[k][c]
     CNB_DISPATCH_T(d.dtype, (vec_gemm_k<T, T><<<vec_gemm_blocks(p.N, p.C), 256, 0, st>>>(
                                 (const T*)dy, p.K, 1, (const T*)w, p.C, 1, (T*)dx, p.N, p.C, p.K, nullptr, 0)));
@@ -355,6 +582,26 @@ int conv_simt_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float
     CNB_DISPATCH_T(d.dtype, (vec_gemm_k<T, float><<<vec_gemm_blocks(p.K, p.C), 256, 0, st>>>(
                                 (const T*)dy, 1, p.K, (const T*)x, p.C, 1, dw, p.K, p.C, p.N, nullptr, 0)));
     return check_launch("conv_simt_wgrad(vector)");
+  }
+  if (is_pointwise_narrow(p)) {
+    const int64_t M = (int64_t)p.N * p.P * p.Q;
+    const int64_t wsz1 = (int64_t)p.K * p.Cg;
+    int psplits = pw_wgrad_splits(p);
+    const int64_t rows = ceil_div(M, psplits);
+    psplits = (int)ceil_div(M, rows);
+    CNB_REQUIRE(ws && ws_bytes >= (size_t)psplits * wsz1 * sizeof(float), CNB_ERR_WORKSPACE,
+                "conv_simt_wgrad(pointwise): workspace %zu < %zu", ws_bytes,
+                (size_t)psplits * wsz1 * sizeof(float));
+    const size_t smem = pw_wgrad_smem(p.Kg, p.Cg);
+    dim3 pgrid((unsigned)psplits, p.G);
+    CNB_DISPATCH_T(d.dtype, {
+      CNB_TRY((pw_set_smem<T, 1>(pw_wgrad_k<T>, smem, "conv_simt_wgrad(pointwise)")));
+      pw_wgrad_k<T><<<pgrid, 256, smem, st>>>((const T*)dy, p.K, (const T*)x, p.C, (float*)ws, M, p.Kg, p.Cg,
+                                              p.K, rows);
+    });
+    CNB_TRY(check_launch("conv_simt_wgrad(pointwise)"));
+    sum_splits2_k<<<grid_for(wsz1, 256), 256, 0, st>>>((const float*)ws, dw, psplits, wsz1);
+    return check_launch("conv_simt_wgrad_sum");
   }
   int splits = wgrad_splits(p);
   int64_t wsz = (int64_t)p.K * p.R * p.S * p.Cg;

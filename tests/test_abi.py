@@ -93,3 +93,22 @@ def test_product_never_imports_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
+
+
+def test_packed_weight_cache_key_moves_with_every_optimizer_step():
+    """torch's fused Adam does not bump `Parameter._version`; the epoch that convnets_b200.layers
+    adds to the pack-cache key must advance on every optimizer step of ANY optimizer."""
+    from convnets_b200 import layers as L
+    p = torch.nn.Parameter(torch.randn(4, 4))
+    for kw in ({}, {"fused": True}, {"foreach": True}):
+        opt = torch.optim.Adam([p], lr=1e-3, **kw)
+        for _ in range(2):
+            before = (L._WEIGHT_EPOCH[0], p._version)
+            opt.zero_grad()
+            (p * p).sum().backward()
+            opt.step()
+            assert (L._WEIGHT_EPOCH[0], p._version) != before
+            assert L._WEIGHT_EPOCH[0] == before[0] + 1
+    e = L._WEIGHT_EPOCH[0]
+    L.invalidate_packed_weights()
+    assert L._WEIGHT_EPOCH[0] == e + 1

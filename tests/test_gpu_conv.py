@@ -74,6 +74,10 @@ SIMT_CASES = [
     c(2, 40, 9, 6, 40, 3, pad=1, stride=2, groups=40, dtype="f32"),    # depthwise s2 fp32, W < one strip pair
     c(1, 1024, 7, 7, 1024, 3, pad=1, groups=1024, dtype="bf16"),       # MobileNet tail
     c(3, 120, 14, 14, 120, 3, pad=1, stride=2, groups=120, dtype="bf16"),  # ShuffleNet: 15 channel vectors
+    c(4, 24, 9, 9, 60, 1, dtype="bf16"),                               # ShuffleNet first compress (narrow pointwise)
+    c(3, 60, 11, 11, 216, 1, groups=3, dtype="bf16"),                  # ShuffleNet first expand: Cg 20, Kg 72
+    c(5, 240, 13, 13, 60, 1, groups=3, dtype="bf16", bias=True),       # narrow pointwise, ragged 128-pixel tile
+    c(2, 96, 6, 6, 96, 1, dtype="f32"),                                # pointwise path at its 96 x 96 limit
     c(16, 1024, 1, 1, 64, 1, dtype="f32"),                             # SK descriptor conv on [B,C,1,1]
     c(16, 64, 1, 1, 1024, 1, dtype="f32", bias=True),                  # SK attention conv (vector GEMM)
 ]
