@@ -41,7 +41,7 @@ static BnGeom bn_geom(int64_t M, int C, int V, int waves, int max_cx = 32) {
   g.ry = kBnThreads / g.cx;
   g.cblocks = (int)ceil_div(cvs, g.cx);
   int64_t target = (int64_t)sm_count() * waves;
-  int64_t splits = ceil_div(target, g.cblocks);
+  int64_t splits = target / g.cblocks;  // floor: never more CTAs than `waves` whole waves
   int64_t max_splits = ceil_div(M, (int64_t)g.ry * kBnUnroll);  // >= one unrolled trip per thread
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
@@ -285,8 +285,8 @@ __global__ void bn_eval_coeff_k(const float* __restrict__ gamma, const float* __
 
 // y = [relu](x*scale + shift [+ res]); 2-D thread map (channel vector fixed per thread, so the
 // coefficients live in registers), kBnUnroll independent 16-byte loads in flight per thread.
-template <typename T, int V, bool RELU, bool ADD>
-__global__ void __launch_bounds__(kBnThreads)
+template <typename T, int V, bool RELU, bool ADD, int U, int MINB>
+__global__ void __launch_bounds__(kBnThreads, MINB)
 bn_apply_k(const T* __restrict__ x, const T* __restrict__ res, const float* __restrict__ scale,
            const float* __restrict__ shift, const float* __restrict__ mean, T* __restrict__ y,
            uint8_t* __restrict__ mask, int64_t M, int C, int64_t rows_per_split) {
@@ -305,39 +305,55 @@ bn_apply_k(const T* __restrict__ x, const T* __restrict__ res, const float* __re
     sh[j] = shift[c0 + j];
     mu[j] = mean[c0 + j];
   }
-  const int64_t step = (int64_t)blockDim.y * kBnUnroll;
-  for (int64_t r = r0 + threadIdx.y; r < r1; r += step) {
-    Pack<T, V> a[kBnUnroll], rs[kBnUnroll];
+  const bool bits_out = RELU && V == 8 && mask != nullptr;
+  const int ry = blockDim.y;
+  const int64_t stride = (int64_t)ry * C, mstride = stride >> 3;
+  int64_t r = r0 + threadIdx.y;
+  const int64_t e0 = r * C + c0;
+  const T* xp = x + e0;
+  const T* rp = ADD ? res + e0 : nullptr;
+  T* yp = y + e0;
+  uint8_t* mp = bits_out ? mask + (e0 >> 3) : nullptr;
+  auto emit = [&](const Pack<T, V>& a, const Pack<T, V>& rs, T* o_ptr, uint8_t* m_ptr) {
+    Pack<T, V> o;
+    uint32_t bits = 0;
 #pragma unroll
-    for (int u = 0; u < kBnUnroll; ++u) {
-      int64_t rr = r + (int64_t)u * blockDim.y;
-      if (rr < r1) {
-        a[u] = ld_pack<T, V>(x + rr * C + c0);
-        if (ADD) rs[u] = ld_pack<T, V>(res + rr * C + c0);
+    for (int j = 0; j < V; ++j) {
+      float v = fmaf(to_f(a.v[j]) - mu[j], sc[j], sh[j]);
+      if (ADD) {
+        // the reference materialises bn(x) in the storage dtype before `output += identity`
+        v = to_f(from_f<T>(v)) + to_f(rs.v[j]);
       }
+      if (RELU) v = (v > 0.f || v != v) ? v : 0.f;
+      o.v[j] = from_f<T>(v);
+      if (RELU && V == 8) bits |= (to_f(o.v[j]) > 0.f ? 1u : 0u) << j;
+    }
+    st_pack<T, V>(o_ptr, o);
+    // 1 bit per element (y > 0): backward reads this instead of y (1/16 of the bytes)
+    if (bits_out) *m_ptr = (uint8_t)bits;
+  };
+  for (; r + (int64_t)(U - 1) * ry < r1; r += (int64_t)U * ry) {
+    Pack<T, V> a[U], rs[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      a[u] = ld_pack<T, V>(xp + u * stride);
+      if (ADD) rs[u] = ld_pack<T, V>(rp + u * stride);
     }
 #pragma unroll
-    for (int u = 0; u < kBnUnroll; ++u) {
-      int64_t rr = r + (int64_t)u * blockDim.y;
-      if (rr < r1) {
-        Pack<T, V> o;
-        uint32_t bits = 0;
-#pragma unroll
-        for (int j = 0; j < V; ++j) {
-          float v = fmaf(to_f(a[u].v[j]) - mu[j], sc[j], sh[j]);
-          if (ADD) {
-            // the reference materialises bn(x) in the storage dtype before `output += identity`
-            v = to_f(from_f<T>(v)) + to_f(rs[u].v[j]);
-          }
-          if (RELU) v = (v > 0.f || v != v) ? v : 0.f;
-          o.v[j] = from_f<T>(v);
-          if (RELU && V == 8) bits |= (to_f(o.v[j]) > 0.f ? 1u : 0u) << j;
-        }
-        st_pack<T, V>(y + rr * C + c0, o);
-        // 1 bit per element (y > 0): backward reads this instead of y (1/16 of the bytes)
-        if (RELU && V == 8 && mask) mask[(rr * C + c0) >> 3] = (uint8_t)bits;
-      }
-    }
+    for (int u = 0; u < U; ++u) emit(a[u], rs[u], yp + u * stride, bits_out ? mp + u * mstride : nullptr);
+    xp += U * stride;
+    yp += U * stride;
+    if (ADD) rp += U * stride;
+    if (bits_out) mp += U * mstride;
+  }
+  for (; r < r1; r += ry) {
+    Pack<T, V> a = ld_pack<T, V>(xp), rs;
+    if (ADD) rs = ld_pack<T, V>(rp);
+    emit(a, rs, yp, mp);
+    xp += stride;
+    yp += stride;
+    if (ADD) rp += stride;
+    if (bits_out) mp += mstride;
   }
 }
 
@@ -345,8 +361,12 @@ bn_apply_k(const T* __restrict__ x, const T* __restrict__ res, const float* __re
 // s = sum dy', q = sum dy' * (x - mean)   (dy' = dy masked by y > 0 when ReLU is fused), then
 // dbeta = s ; dgamma = rstd * q ; dx = c1 * (dy' - c2 - (x - mean) * c3) with
 // c1 = gamma*rstd, c2 = s/M, c3 = rstd^2 * q / M
-template <typename T, int V, bool RELU>
-__global__ void __launch_bounds__(kBnThreads)
+// U rows of every operand are in flight per thread; MINB resident CTAs per SM bound the registers.
+// The row loop walks pointers (one 64-bit add per operand and trip) and runs unguarded while U
+// whole rows remain; a one-row tail loop finishes the split.
+// RELU: 0 = none, 1 = mask from the forward output y > 0, 2 = 1-bit mask written by the forward pass
+template <typename T, int V, int RELU, int U, int MINB>
+__global__ void __launch_bounds__(kBnThreads, MINB)
 bn_bwd_reduce_k(const T* __restrict__ x, const T* __restrict__ y, const uint8_t* __restrict__ mask,
                 const T* __restrict__ dy, const float* __restrict__ mean, float* __restrict__ part,
                 int64_t M, int C,
@@ -365,38 +385,63 @@ bn_bwd_reduce_k(const T* __restrict__ x, const T* __restrict__ y, const uint8_t*
   if (c0 < C) {
 #pragma unroll
     for (int j = 0; j < V; ++j) mu[j] = mean[c0 + j];
-    constexpr int U = 2;
-    const int64_t step = (int64_t)blockDim.y * U;
-    for (int64_t r = r0 + threadIdx.y; r < r1; r += step) {
+    constexpr bool bits = RELU == 2 && V == 8;
+    const int ry = blockDim.y;
+    const int64_t stride = (int64_t)ry * C;
+    int64_t r = r0 + threadIdx.y;
+    const int64_t e0 = r * C + c0;
+    const T* xp = x + e0;
+    const T* gp = dy + e0;
+    const T* yp = (RELU && !bits) ? y + e0 : nullptr;
+    const uint8_t* mp = bits ? mask + (e0 >> 3) : nullptr;
+    const int64_t mstride = stride >> 3;
+    auto accum = [&](const Pack<T, V>& a, const Pack<T, V>& g, uint32_t mb, const Pack<T, V>& o) {
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        float gf = to_f(g.v[j]);
+        if (RELU) {
+          const bool pos = bits ? ((mb >> j) & 1u) : (to_f(o.v[j]) > 0.f);
+          if (!pos) gf = 0.f;
+        }
+        s[j] += gf;
+        q[j] = fmaf(gf, to_f(a.v[j]) - mu[j], q[j]);
+      }
+    };
+    for (; r + (int64_t)(U - 1) * ry < r1; r += (int64_t)U * ry) {
       Pack<T, V> a[U], g[U], o[U];
       uint32_t mb[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
-        int64_t rr = r + (int64_t)u * blockDim.y;
-        if (rr < r1) {
-          a[u] = ld_pack<T, V>(x + rr * C + c0);
-          g[u] = ld_pack<T, V>(dy + rr * C + c0);
-          if (RELU) {
-            if (V == 8 && mask) mb[u] = mask[(rr * C + c0) >> 3];
-            else o[u] = ld_pack<T, V>(y + rr * C + c0);
-          }
+        a[u] = ld_pack<T, V>(xp + u * stride);
+        g[u] = ld_pack<T, V>(gp + u * stride);
+        mb[u] = 0;
+        if (RELU) {
+          if (bits) mb[u] = mp[u * mstride];
+          else o[u] = ld_pack<T, V>(yp + u * stride);
         }
       }
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        int64_t rr = r + (int64_t)u * blockDim.y;
-        if (rr < r1) {
-#pragma unroll
-          for (int j = 0; j < V; ++j) {
-            float gf = to_f(g[u].v[j]);
-            if (RELU) {
-              const bool pos = (V == 8 && mask) ? ((mb[u] >> j) & 1u) : (to_f(o[u].v[j]) > 0.f);
-              if (!pos) gf = 0.f;
-            }
-            s[j] += gf;
-            q[j] = fmaf(gf, to_f(a[u].v[j]) - mu[j], q[j]);
-          }
-        }
+      for (int u = 0; u < U; ++u) accum(a[u], g[u], mb[u], o[u]);
+      xp += U * stride;
+      gp += U * stride;
+      if (RELU) {
+        if (bits) mp += U * mstride;
+        else yp += U * stride;
+      }
+    }
+    for (; r < r1; r += ry) {
+      Pack<T, V> a = ld_pack<T, V>(xp), g = ld_pack<T, V>(gp), o;
+      uint32_t mb = 0;
+      if (RELU) {
+        if (bits) mb = *mp;
+        else o = ld_pack<T, V>(yp);
+      }
+      accum(a, g, mb, o);
+      xp += stride;
+      gp += stride;
+      if (RELU) {
+        if (bits) mp += mstride;
+        else yp += stride;
       }
     }
   }
@@ -412,8 +457,8 @@ bn_bwd_reduce_k(const T* __restrict__ x, const T* __restrict__ y, const uint8_t*
   f.c3[c] = (float)(Q * (double)rs * (double)rs / (double)M);
 }
 
-template <typename T, int V, bool RELU, bool DRES>
-__global__ void __launch_bounds__(kBnThreads)
+template <typename T, int V, int RELU, bool DRES, int U, int MINB>
+__global__ void __launch_bounds__(kBnThreads, MINB)
 bn_bwd_dx_k(const T* __restrict__ x, const T* __restrict__ y, const uint8_t* __restrict__ mask,
             const T* __restrict__ dy, const float* __restrict__ mean, const float* __restrict__ c1,
             const float* __restrict__ c2, const float* __restrict__ c3, T* __restrict__ dx,
@@ -434,46 +479,104 @@ bn_bwd_dx_k(const T* __restrict__ x, const T* __restrict__ y, const uint8_t* __r
     k3[j] = c3[c0 + j];
     mu[j] = mean[c0 + j];
   }
-  constexpr int U = 2;
-  const int64_t step = (int64_t)blockDim.y * U;
-  for (int64_t r = r0 + threadIdx.y; r < r1; r += step) {
+  constexpr bool bits = RELU == 2 && V == 8;
+  const int ry = blockDim.y;
+  const int64_t stride = (int64_t)ry * C;
+  int64_t r = r0 + threadIdx.y;
+  const int64_t e0 = r * C + c0;
+  const T* xp = x + e0;
+  const T* gp = dy + e0;
+  const T* yp = (RELU && !bits) ? y + e0 : nullptr;
+  const uint8_t* mp = bits ? mask + (e0 >> 3) : nullptr;
+  T* op = dx + e0;
+  T* dp = DRES ? dres + e0 : nullptr;
+  const int64_t mstride = stride >> 3;
+  auto emit = [&](const Pack<T, V>& a, const Pack<T, V>& g, uint32_t mb, const Pack<T, V>& m, T* o_ptr,
+                  T* d_ptr) {
+    Pack<T, V> o, dr;
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      float gf = to_f(g.v[j]);
+      if (RELU) {
+        const bool pos = bits ? ((mb >> j) & 1u) : (to_f(m.v[j]) > 0.f);
+        if (!pos) gf = 0.f;
+      }
+      if (DRES) dr.v[j] = from_f<T>(gf);
+      o.v[j] = from_f<T>(k1[j] * (gf - k2[j] - (to_f(a.v[j]) - mu[j]) * k3[j]));
+    }
+    st_pack<T, V>(o_ptr, o);
+    if (DRES) st_pack<T, V>(d_ptr, dr);
+  };
+  for (; r + (int64_t)(U - 1) * ry < r1; r += (int64_t)U * ry) {
     Pack<T, V> a[U], g[U], m[U];
     uint32_t mb[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
-      int64_t rr = r + (int64_t)u * blockDim.y;
-      if (rr < r1) {
-        a[u] = ld_pack<T, V>(x + rr * C + c0);
-        g[u] = ld_pack<T, V>(dy + rr * C + c0);
-        if (RELU) {
-          if (V == 8 && mask) mb[u] = mask[(rr * C + c0) >> 3];
-          else m[u] = ld_pack<T, V>(y + rr * C + c0);
-        }
+      a[u] = ld_pack<T, V>(xp + u * stride);
+      g[u] = ld_pack<T, V>(gp + u * stride);
+      mb[u] = 0;
+      if (RELU) {
+        if (bits) mb[u] = mp[u * mstride];
+        else m[u] = ld_pack<T, V>(yp + u * stride);
       }
     }
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      int64_t rr = r + (int64_t)u * blockDim.y;
-      if (rr < r1) {
-        Pack<T, V> o, dr;
-#pragma unroll
-        for (int j = 0; j < V; ++j) {
-          float gf = to_f(g[u].v[j]);
-          if (RELU) {
-            const bool pos = (V == 8 && mask) ? ((mb[u] >> j) & 1u) : (to_f(m[u].v[j]) > 0.f);
-            if (!pos) gf = 0.f;
-          }
-          if (DRES) dr.v[j] = from_f<T>(gf);
-          o.v[j] = from_f<T>(k1[j] * (gf - k2[j] - (to_f(a[u].v[j]) - mu[j]) * k3[j]));
-        }
-        st_pack<T, V>(dx + rr * C + c0, o);
-        if (DRES) st_pack<T, V>(dres + rr * C + c0, dr);
-      }
+    for (int u = 0; u < U; ++u) emit(a[u], g[u], mb[u], m[u], op + u * stride, DRES ? dp + u * stride : nullptr);
+    xp += U * stride;
+    gp += U * stride;
+    op += U * stride;
+    if (DRES) dp += U * stride;
+    if (RELU) {
+      if (bits) mp += U * mstride;
+      else yp += U * stride;
+    }
+  }
+  for (; r < r1; r += ry) {
+    Pack<T, V> a = ld_pack<T, V>(xp), g = ld_pack<T, V>(gp), m;
+    uint32_t mb = 0;
+    if (RELU) {
+      if (bits) mb = *mp;
+      else m = ld_pack<T, V>(yp);
+    }
+    emit(a, g, mb, m, op, dp);
+    xp += stride;
+    gp += stride;
+    op += stride;
+    if (DRES) dp += stride;
+    if (RELU) {
+      if (bits) mp += mstride;
+      else yp += stride;
     }
   }
 }
 
 constexpr int kReduceWaves = 4, kStreamWaves = 8, kReduceCx = 8;
+
+// Loop shape of the bf16 backward kernels: (rows in flight per thread, resident CTAs per SM).
+// 0: (2, 2)  1: (2, 3)  2: (4, 2)  3: (3, 2)  4: (4, 3).  CNB_BN_BWD_VARIANT overrides the default.
+// Loop shape of the bf16 apply kernel: 0: (4, 2)  1: (2, 3)  2: (4, 3)  3: (2, 4).
+static int bn_fwd_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("CNB_BN_FWD_VARIANT");
+    v = e ? atoi(e) : 2;   // measured on ResNet-50 (profiles/r01v): 3.73 / 3.59 / 3.40 / 3.48 ms per step
+    if (v < 0 || v > 3) v = 0;
+  }
+  return v;
+}
+static int apply_waves(bool hot, int variant) {
+  if (hot && (variant == 1 || variant == 2)) return 6;   // 3 resident CTAs per SM
+  return kStreamWaves;                                    // 2 or 4 resident CTAs per SM
+}
+static int bn_bwd_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("CNB_BN_BWD_VARIANT");
+    v = e ? atoi(e) : 1;   // measured on ResNet-50 (profiles/r01u): 7.07 / 6.10 / 6.49 / - / 6.15 ms per step
+    if (v < 0 || v > 4) v = 0;
+  }
+  return v;
+}
 static size_t bn_ws_bytes(int C) {
   // partials: splits <= min(2048, kReduceWaves*SMs) rows of 2*C floats, then 5*C coefficients
   int64_t splits = (int64_t)sm_count() * kReduceWaves;
@@ -569,17 +672,33 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
   float* shift = scale + C;
   const float* mean_ptr = save_mean;
   uint8_t* mask = (uint8_t*)relu_mask;
-  BnGeom ga = bn_geom(M, C, v, kStreamWaves);
+  const bool ahot = d->dtype == CNB_BF16 && v == 8;
+  const int avariant = bn_fwd_variant();
+  BnGeom ga = bn_geom(M, C, v, apply_waves(ahot, avariant));
   dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
   const int64_t arows = ga.rows_per_split;
-#define APPLY(R, A)                                                                              \
-  CNB_DISPATCH_TV(d->dtype, v, (bn_apply_k<T, V, R, A><<<agrid, ablock, 0, st>>>(                \
-                                   (const T*)x, (const T*)residual, scale, shift, mean_ptr,     \
-                                   (T*)y, mask, d->M, C, arows)))
-  if (relu && add) APPLY(true, true);
-  else if (relu) APPLY(true, false);
-  else if (add) APPLY(false, true);
-  else APPLY(false, false);
+#define APPLY_ARGS (const T*)x, (const T*)residual, scale, shift, mean_ptr, (T*)y, mask, d->M, C, arows
+#define APPLY(R, A) \
+  CNB_DISPATCH_TV(d->dtype, v, (bn_apply_k<T, V, R, A, 4, 2><<<agrid, ablock, 0, st>>>(APPLY_ARGS)))
+#define APPLY_HOT(UU, MB)                                                                          \
+  do {                                                                                             \
+    using T = bf16;                                                                                \
+    if (relu && add) bn_apply_k<T, 8, true, true, UU, MB><<<agrid, ablock, 0, st>>>(APPLY_ARGS);   \
+    else if (relu) bn_apply_k<T, 8, true, false, UU, MB><<<agrid, ablock, 0, st>>>(APPLY_ARGS);    \
+    else if (add) bn_apply_k<T, 8, false, true, UU, MB><<<agrid, ablock, 0, st>>>(APPLY_ARGS);     \
+    else bn_apply_k<T, 8, false, false, UU, MB><<<agrid, ablock, 0, st>>>(APPLY_ARGS);             \
+  } while (0)
+#define APPLY_ANY()                                   \
+  do {                                                \
+    if (ahot && avariant == 1) APPLY_HOT(2, 3);       \
+    else if (ahot && avariant == 2) APPLY_HOT(4, 3);  \
+    else if (ahot && avariant == 3) APPLY_HOT(2, 4);  \
+    else if (relu && add) APPLY(true, true);          \
+    else if (relu) APPLY(true, false);                \
+    else if (add) APPLY(false, true);                 \
+    else APPLY(false, false);                         \
+  } while (0)
+  APPLY_ANY();
   return check_launch("bn_apply");
 }
 
@@ -603,16 +722,18 @@ int cnb_bn_fwd_eval(const cnb_bn_desc* d, const void* x, const void* residual, c
                                                               running_var, scale, shift, C, d->eps);
   CNB_TRY(check_launch("bn_eval_coeff"));
   int v = pick_vec(C, dtype_size(d->dtype), x, y, add ? residual : nullptr);
-  BnGeom ga = bn_geom(d->M, C, v, kStreamWaves);
+  const bool ahot = d->dtype == CNB_BF16 && v == 8;
+  const int avariant = bn_fwd_variant();
+  BnGeom ga = bn_geom(d->M, C, v, apply_waves(ahot, avariant));
   dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
   const int64_t arows = ga.rows_per_split;
   uint8_t* mask = nullptr;
   const float* mean_ptr = running_mean;
-  if (relu && add) APPLY(true, true);
-  else if (relu) APPLY(true, false);
-  else if (add) APPLY(false, true);
-  else APPLY(false, false);
+  APPLY_ANY();
+#undef APPLY_ANY
+#undef APPLY_HOT
 #undef APPLY
+#undef APPLY_ARGS
   return check_launch("bn_apply(eval)");
 }
 
@@ -638,7 +759,13 @@ int cnb_bn_bwd(const cnb_bn_desc* d, const void* x, const void* y, const void* r
   if (d_residual)
     while (v > 1 && (uintptr_t)d_residual % (v * dtype_size(d->dtype)) != 0) v >>= 1;
   CNB_REQUIRE(!mask || v == 8, CNB_ERR_INVALID, "cnb_bn_bwd: relu_mask needs 16-byte aligned tensors");
-  BnGeom g = bn_geom(M, C, v, kReduceWaves, kReduceCx);
+  const bool hot = d->dtype == CNB_BF16 && v == 8;   // the feature-map configuration of every zoo model
+  const int variant = bn_bwd_variant();
+  const int mode = relu ? (mask ? 2 : 1) : 0;
+  // grids are whole multiples of the CTAs that are resident at once: 2 per SM with the (.., 2)
+  // loop shapes, 3 per SM with the (.., 3) ones (80 registers)
+  const bool three = hot && (variant == 1 || variant == 4);
+  BnGeom g = bn_geom(M, C, v, three ? 3 : kReduceWaves, kReduceCx);
   float* part = (float*)workspace;
   float* c1 = part + (size_t)2 * C * g.splits;
   float* c2 = c1 + C;
@@ -650,28 +777,59 @@ int cnb_bn_bwd(const cnb_bn_desc* d, const void* x, const void* y, const void* r
     size_t smem = (size_t)g.ry * 2 * g.cx * v * sizeof(float);
     if (smem < 4096) smem = 4096;  // the merge step re-uses it for 256 x 2 doubles
     BnBwdFin fin{gamma, save_rstd, dgamma, dbeta, c1, c2, c3};
-    if (relu)
-      CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_reduce_k<T, V, true><<<grid, block, smem, st>>>(
-                                       (const T*)x, (const T*)y, mask, (const T*)dy, save_mean, part, M, C,
-                                       g.rows_per_split, g.splits, counter, fin)));
+#define RED_ARGS (const T*)x, (const T*)y, mask, (const T*)dy, save_mean, part, M, C, g.rows_per_split, \
+                 g.splits, counter, fin
+#define RED_HOT(UU, MB)                                                                      \
+  do {                                                                                       \
+    using T = bf16;                                                                          \
+    if (mode == 2) bn_bwd_reduce_k<T, 8, 2, UU, MB><<<grid, block, smem, st>>>(RED_ARGS);    \
+    else if (mode == 1) bn_bwd_reduce_k<T, 8, 1, UU, MB><<<grid, block, smem, st>>>(RED_ARGS); \
+    else bn_bwd_reduce_k<T, 8, 0, UU, MB><<<grid, block, smem, st>>>(RED_ARGS);              \
+  } while (0)
+    if (hot && variant == 1) RED_HOT(2, 3);
+    else if (hot && variant == 2) RED_HOT(4, 2);
+    else if (hot && variant == 3) RED_HOT(3, 2);
+    else if (hot && variant == 4) RED_HOT(4, 3);
+    else if (mode == 2)
+      CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_reduce_k<T, V, 2, 2, 2><<<grid, block, smem, st>>>(RED_ARGS)));
+    else if (mode == 1)
+      CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_reduce_k<T, V, 1, 2, 2><<<grid, block, smem, st>>>(RED_ARGS)));
     else
-      CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_reduce_k<T, V, false><<<grid, block, smem, st>>>(
-                                       (const T*)x, (const T*)y, mask, (const T*)dy, save_mean, part, M, C,
-                                       g.rows_per_split, g.splits, counter, fin)));
+      CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_reduce_k<T, V, 0, 2, 2><<<grid, block, smem, st>>>(RED_ARGS)));
+#undef RED_HOT
+#undef RED_ARGS
     CNB_TRY(check_launch("bn_bwd_reduce"));
   }
-  BnGeom ga = bn_geom(M, C, v, kStreamWaves);
+  BnGeom ga = bn_geom(M, C, v, three ? 6 : kStreamWaves);
   dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
   const int64_t arows = ga.rows_per_split;
-#define DX(R, D)                                                                                  \
-  CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_dx_k<T, V, R, D><<<agrid, ablock, 0, st>>>(                \
-                                   (const T*)x, (const T*)y, mask, (const T*)dy, save_mean, c1,   \
-                                   c2, c3, (T*)dx, (T*)d_residual, M, C, arows)))
-  if (relu && d_residual) DX(true, true);
-  else if (relu) DX(true, false);
-  else if (d_residual) DX(false, true);
-  else DX(false, false);
+#define DX_ARGS (const T*)x, (const T*)y, mask, (const T*)dy, save_mean, c1, c2, c3, (T*)dx, \
+                (T*)d_residual, M, C, arows
+#define DX(R, D) \
+  CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_dx_k<T, V, R, D, 2, 2><<<agrid, ablock, 0, st>>>(DX_ARGS)))
+#define DX_HOT(UU, MB)                                                                            \
+  do {                                                                                            \
+    using T = bf16;                                                                               \
+    if (mode == 2 && d_residual) bn_bwd_dx_k<T, 8, 2, true, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS); \
+    else if (mode == 2) bn_bwd_dx_k<T, 8, 2, false, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS);   \
+    else if (mode == 1 && d_residual) bn_bwd_dx_k<T, 8, 1, true, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS); \
+    else if (mode == 1) bn_bwd_dx_k<T, 8, 1, false, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS);   \
+    else if (d_residual) bn_bwd_dx_k<T, 8, 0, true, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS);   \
+    else bn_bwd_dx_k<T, 8, 0, false, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS);                  \
+  } while (0)
+  if (hot && variant == 1) DX_HOT(2, 3);
+  else if (hot && variant == 2) DX_HOT(4, 2);
+  else if (hot && variant == 3) DX_HOT(3, 2);
+  else if (hot && variant == 4) DX_HOT(4, 3);
+  else if (mode == 2 && d_residual) DX(2, true);
+  else if (mode == 2) DX(2, false);
+  else if (mode == 1 && d_residual) DX(1, true);
+  else if (mode == 1) DX(1, false);
+  else if (d_residual) DX(0, true);
+  else DX(0, false);
+#undef DX_HOT
 #undef DX
+#undef DX_ARGS
   return check_launch("bn_bwd_dx");
 }
 

@@ -305,12 +305,32 @@ pw_gemm_k(const T* __restrict__ A, int lda, const T* __restrict__ W, int64_t sWk
     const int k = i / Np, j = i - k * Np;
     Bs[i] = j < Ng ? to_f(Wg[k * sWk + j * sWj]) : 0.f;
   }
-  for (int i = t; i < PW_BM * Kd; i += 256) {
-    const int m = i / Kd, k = i - m * Kd;
+  // 4-element vectors along the reduction when rows, group offsets and pointers allow it: a thread
+  // keeps ONE pixel (conflict-free k-major stores) and strides the vectors — no divisions
+  const bool avec = (Kd % 4 == 0) && (lda % 4 == 0) && ((uintptr_t)A % (4 * sizeof(T)) == 0);
+  if (avec) {
+    const int m = t & (PW_BM - 1);
     const int64_t row = m0 + m;
-    As[k * LDA + m] = row < M ? to_f(A[row * lda + a0 + k]) : 0.f;
+    const T* arow = A + row * lda + a0;
+    for (int v = t / PW_BM; v < Kd / 4; v += 256 / PW_BM) {
+      float f[4] = {0.f, 0.f, 0.f, 0.f};
+      if (row < M) {
+        const Pack<T, 4> q = ld_pack<T, 4>(arow + v * 4);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) f[j] = to_f(q.v[j]);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) As[(v * 4 + j) * LDA + m] = f[j];
+    }
+  } else {
+    for (int i = t; i < PW_BM * Kd; i += 256) {
+      const int m = i / Kd, k = i - m * Kd;
+      const int64_t row = m0 + m;
+      As[k * LDA + m] = row < M ? to_f(A[row * lda + a0 + k]) : 0.f;
+    }
   }
   __syncthreads();
+  const bool ovec = (Ng % 4 == 0) && (ldo % 4 == 0) && ((uintptr_t)out % (4 * sizeof(T)) == 0);
   const int rgp = t & 31;
   for (int cg = t >> 5; cg < Np / 4; cg += 8) {
     float acc[4][4];
@@ -334,15 +354,17 @@ pw_gemm_k(const T* __restrict__ A, int lda, const T* __restrict__ W, int64_t sWk
     for (int i = 0; i < 4; ++i) {
       const int64_t row = m0 + rgp * 4 + i;
       if (row >= M) continue;
+      Pack<T, 4> o;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         const int col = cg * 4 + j;
-        if (col >= Ng) continue;
         float v = acc[i][j];
-        if (flags & CNB_CONV_BIAS) v += bias[n0 + col];
+        if ((flags & CNB_CONV_BIAS) && col < Ng) v += bias[n0 + col];
         if (flags & CNB_CONV_RELU) v = (v > 0.f || v != v) ? v : 0.f;
-        out[row * ldo + n0 + col] = from_f<T>(v);
+        o.v[j] = from_f<T>(v);
+        if (!ovec && col < Ng) out[row * ldo + n0 + col] = o.v[j];
       }
+      if (ovec) st_pack<T, 4>(out + row * ldo + n0 + cg * 4, o);  // Ng % 4 == 0: the tile is inside
     }
   }
 }
@@ -375,15 +397,40 @@ pw_wgrad_k(const T* __restrict__ dy, int ldy, const T* __restrict__ x, int ldx,
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[s][i][j] = 0.f;
   for (int i = t; i < PW_RC * (Kp + Cp); i += 256) pw_smem[i] = 0.f;  // padding columns stay zero
+  const bool vec = (Kg % 4 == 0) && (Cg % 4 == 0) && (ldy % 4 == 0) && (ldx % 4 == 0) &&
+                   ((uintptr_t)dy % (4 * sizeof(T)) == 0) && ((uintptr_t)x % (4 * sizeof(T)) == 0);
   for (int64_t mb = r0; mb < r1; mb += PW_RC) {
     __syncthreads();
-    for (int i = t; i < PW_RC * Kg; i += 256) {
-      const int m = i / Kg, k = i - m * Kg;
-      dys[m * Kp + k] = mb + m < r1 ? to_f(dy[(mb + m) * ldy + g * Kg + k]) : 0.f;
-    }
-    for (int i = t; i < PW_RC * Cg; i += 256) {
-      const int m = i / Cg, c = i - m * Cg;
-      xs[m * Cp + c] = mb + m < r1 ? to_f(x[(mb + m) * ldx + g * Cg + c]) : 0.f;
+    if (vec) {
+      const int m = t & (PW_RC - 1);
+      const bool rok = mb + m < r1;
+      const T* dyr = dy + (mb + m) * ldy + g * Kg;
+      const T* xr = x + (mb + m) * ldx + g * Cg;
+      for (int v = t / PW_RC; v < Kg / 4; v += 256 / PW_RC) {
+        float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (rok) {
+          const Pack<T, 4> q = ld_pack<T, 4>(dyr + v * 4);
+          f = make_float4(to_f(q.v[0]), to_f(q.v[1]), to_f(q.v[2]), to_f(q.v[3]));
+        }
+        *reinterpret_cast<float4*>(dys + m * Kp + v * 4) = f;
+      }
+      for (int v = t / PW_RC; v < Cg / 4; v += 256 / PW_RC) {
+        float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (rok) {
+          const Pack<T, 4> q = ld_pack<T, 4>(xr + v * 4);
+          f = make_float4(to_f(q.v[0]), to_f(q.v[1]), to_f(q.v[2]), to_f(q.v[3]));
+        }
+        *reinterpret_cast<float4*>(xs + m * Cp + v * 4) = f;
+      }
+    } else {
+      for (int i = t; i < PW_RC * Kg; i += 256) {
+        const int m = i / Kg, k = i - m * Kg;
+        dys[m * Kp + k] = mb + m < r1 ? to_f(dy[(mb + m) * ldy + g * Kg + k]) : 0.f;
+      }
+      for (int i = t; i < PW_RC * Cg; i += 256) {
+        const int m = i / Cg, c = i - m * Cg;
+        xs[m * Cp + c] = mb + m < r1 ? to_f(x[(mb + m) * ldx + g * Cg + c]) : 0.f;
+      }
     }
     __syncthreads();
     if (live) {

@@ -202,6 +202,78 @@ im2col_nchw_rows_k(const float* __restrict__ src, T* __restrict__ dst, Im2colP p
   }
 }
 
+// Output-staged variant (the one the RGB stems use).  The patch is kept pixel-major, [R][Wp][C], so
+// the columns of one filter row are one contiguous run starting at j*stride*C.  Phase A: a warp
+// takes one 16-byte column block `cv` (its V patch offsets live in registers) and its lanes take
+// consecutive output pixels j — patch reads are sw*C elements apart across lanes (odd word stride
+// for RGB, conflict-free) and the assembled vectors go to a smem copy of the output row block.
+// Phase B streams that block to global memory with fully coalesced 16-byte stores.
+template <typename T, int V>
+__global__ void __launch_bounds__(256)
+im2col_nchw_staged_k(const float* __restrict__ src, T* __restrict__ dst, Im2colP p, int row_stride) {
+  extern __shared__ __align__(16) uint8_t sm_raw[];
+  const int Wp = p.W + 2 * p.pw;
+  const int patch_elems = p.R * Wp * p.C;
+  int* coltab = reinterpret_cast<int*>(sm_raw);                                          // [Kd]
+  T* patch = reinterpret_cast<T*>(sm_raw + (size_t)((p.Kd * 4 + 15) / 16) * 16);        // [R][Wp][C]
+  T* outs = patch + (size_t)((patch_elems + V - 1) / V) * V;                             // [Q][row_stride]
+  const int ii = blockIdx.x % p.P;
+  const int n = blockIdx.x / p.P;
+  const int RSC = p.R * p.S * p.C;
+  for (int col = threadIdx.x; col < p.Kd; col += blockDim.x) {
+    int off = -1;
+    if (col < RSC) {
+      const int c = col % p.C, rs = col / p.C;
+      const int s_ = rs % p.S, r = rs / p.S;
+      off = (r * Wp + s_ * p.dw) * p.C + c;
+    }
+    coltab[col] = off;
+  }
+  const int h0 = ii * p.sh - p.ph;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  // one warp per (channel, filter row): global reads run along w (coalesced), one division per
+  // row instead of three per element; the smem store interleaves the channels
+  for (int cr = warp; cr < p.C * p.R; cr += nwarps) {
+    const int c = cr / p.R, r = cr - c * p.R;
+    const int h = h0 + r * p.dh;
+    const bool row_ok = h >= 0 && h < p.H;
+    const float* srow = src + (((int64_t)n * p.C + c) * p.H + (row_ok ? h : 0)) * p.W;
+    T* prow = patch + (size_t)r * Wp * p.C + c;
+    for (int wp = lane; wp < Wp; wp += 32) {
+      const int w = wp - p.pw;
+      float v = 0.f;
+      if (row_ok && w >= 0 && w < p.W) v = __ldg(srow + w);
+      prow[wp * p.C] = from_f<T>(v);
+    }
+  }
+  __syncthreads();
+  const int kv = p.Kd / V;
+  const T zero = from_f<T>(0.f);
+  const int jstep = p.sw * p.C;
+  for (int cv = warp; cv < kv; cv += nwarps) {
+    int off[V];
+#pragma unroll
+    for (int e = 0; e < V; ++e) off[e] = coltab[cv * V + e];
+    for (int j = lane; j < p.Q; j += 32) {
+      const int base = j * jstep;
+      Pack<T, V> o;
+#pragma unroll
+      for (int e = 0; e < V; ++e) o.v[e] = off[e] >= 0 ? patch[off[e] + base] : zero;
+      st_pack<T, V>(outs + (size_t)j * row_stride + cv * V, o);
+    }
+  }
+  __syncthreads();
+  T* out = dst + ((int64_t)n * p.P + ii) * p.Q * p.Kd;
+  int j = threadIdx.x / kv, cv = threadIdx.x - j * kv;
+  const int dj = blockDim.x / kv, dcv = blockDim.x - dj * kv;
+  for (int i = threadIdx.x; i < p.Q * kv; i += blockDim.x) {
+    st_pack<T, V>(out + (int64_t)i * V, ld_pack<T, V>(outs + (size_t)j * row_stride + cv * V));
+    j += dj;
+    cv += dcv;
+    if (cv >= kv) { cv -= kv; ++j; }
+  }
+}
+
 // ------------------------------------------------------------------ channel shuffle / slab copy
 // y[m, j*g + i] = x[m, i*(C/g) + j]; one thread per output element pair is fine: rows are short
 // and both sides stay within one row (L1/L2 absorb the permutation), traffic = 2 * numel.
@@ -216,6 +288,83 @@ __global__ void shuffle_k(const T* __restrict__ x, T* __restrict__ y, int64_t M,
     int j = co / g, gi = co - j * g;
     y[i] = x[m * C + (int64_t)gi * cpg + j];
   }
+}
+
+// Vector form for the two shapes the zoo produces: a small factor G (the group count in the forward
+// shuffle, the channels per group in its inverse) and a large factor L, L % V == 0.  A thread moves
+// a [G x V] block: G vector loads, a register permutation with compile-time indices, G vector
+// stores — no per-element division, every access V*sizeof(T) wide.
+//   INV == false: groups = G, C/groups = L:  y[j*G + i] = x[i*L + j]
+//   INV == true : groups = L, C/groups = G:  y[j*L + i] = x[i*G + j]
+template <typename T, int V, int G, bool INV>
+__global__ void shuffle_vec_k(const T* __restrict__ x, T* __restrict__ y, int64_t M, int L) {
+  const int nb = L / V;
+  const int C = G * L;
+  const int64_t total = M * nb;
+  for (int64_t it = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; it < total;
+       it += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t m = it / nb;
+    const int b = (int)(it - m * nb);
+    const T* xr = x + m * C;
+    T* yr = y + m * C;
+    Pack<T, V> in[G], out[G];
+    if (!INV) {
+#pragma unroll
+      for (int i = 0; i < G; ++i) in[i] = ld_pack<T, V>(xr + (int64_t)i * L + b * V);
+#pragma unroll
+      for (int jj = 0; jj < V; ++jj)
+#pragma unroll
+        for (int i = 0; i < G; ++i) out[(jj * G + i) / V].v[(jj * G + i) % V] = in[i].v[jj];
+#pragma unroll
+      for (int k = 0; k < G; ++k) st_pack<T, V>(yr + (int64_t)b * V * G + k * V, out[k]);
+    } else {
+#pragma unroll
+      for (int k = 0; k < G; ++k) in[k] = ld_pack<T, V>(xr + (int64_t)b * V * G + k * V);
+#pragma unroll
+      for (int ii = 0; ii < V; ++ii)
+#pragma unroll
+        for (int j = 0; j < G; ++j) out[j].v[ii] = in[(ii * G + j) / V].v[(ii * G + j) % V];
+#pragma unroll
+      for (int j = 0; j < G; ++j) st_pack<T, V>(yr + (int64_t)j * L + b * V, out[j]);
+    }
+  }
+}
+
+template <typename T, int V, bool INV>
+static bool launch_shuffle_vec(const void* x, void* y, int64_t M, int G, int L, cudaStream_t st) {
+  const int grid = grid_for(M * (L / V), kThreads);
+#define SHV(GG)                                                                                   \
+  case GG:                                                                                        \
+    shuffle_vec_k<T, V, GG, INV><<<grid, kThreads, 0, st>>>((const T*)x, (T*)y, M, L);            \
+    return true
+  switch (G) {
+    SHV(1);
+    SHV(2);
+    SHV(3);
+    SHV(4);
+    SHV(8);
+    default: return false;
+  }
+#undef SHV
+}
+
+// true when a vector kernel took the shuffle
+static bool shuffle_vec(const void* x, void* y, int64_t M, int C, int groups, int dtype,
+                        cudaStream_t st) {
+  const int cpg = C / groups;
+  const bool fwd_shape = groups <= 8;            // small group count, wide groups
+  const bool inv_shape = !fwd_shape && cpg <= 8; // the inverse permutation (backward pass)
+  if (!fwd_shape && !inv_shape) return false;
+  const int G = fwd_shape ? groups : cpg, L = fwd_shape ? cpg : groups;
+  const int v = pick_vec(L, dtype_size(dtype), x, y);
+  if (v < 2) return false;
+  bool done = false;
+  CNB_DISPATCH_TV(dtype, v, {
+    if constexpr (V >= 2)
+      done = fwd_shape ? launch_shuffle_vec<T, V, false>(x, y, M, G, L, st)
+                       : launch_shuffle_vec<T, V, true>(x, y, M, G, L, st);
+  });
+  return done;
 }
 
 template <typename T, int V>
@@ -598,6 +747,39 @@ int cnb_im2col_nchw(const cnb_conv_desc* d, const float* src, void* dst, int32_t
             d->dil_h, d->dil_w, K_dst};
   const int64_t total = (int64_t)d->N * P * Q * (K_dst / v);
   {
+    // output-staged kernel when patch + one output row block fit 96 KB of shared memory
+    const size_t esz = dtype_size(d->dtype);
+    const int kv = K_dst / v;
+    const int row_stride = K_dst + (kv % 2 == 0 ? v : 0);  // odd 16-byte stride: conflict-free phase A
+    const size_t patch_elems = (size_t)d->R * (d->W + 2 * d->pad_w) * d->C;
+    const size_t smem = (size_t)((K_dst * 4 + 15) / 16) * 16 + ((patch_elems + v - 1) / v) * v * esz +
+                        (size_t)Q * row_stride * esz;
+    if (smem <= 96 * 1024 && kv <= 256 && (int64_t)d->N * P < (1ll << 31)) {
+      const unsigned grid = (unsigned)((int64_t)d->N * P);
+      static bool attr_bf16 = false, attr_f32 = false;  // benign race: same value from every thread
+      if (d->dtype == CNB_BF16) {
+        if (!attr_bf16) {
+          cudaError_t e = cudaFuncSetAttribute(im2col_nchw_staged_k<bf16, 8>,
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+          CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cnb_im2col_nchw: cudaFuncSetAttribute: %s",
+                      cudaGetErrorString(e));
+          attr_bf16 = true;
+        }
+        im2col_nchw_staged_k<bf16, 8><<<grid, 256, smem, (cudaStream_t)stream>>>(src, (bf16*)dst, p, row_stride);
+      } else {
+        if (!attr_f32) {
+          cudaError_t e = cudaFuncSetAttribute(im2col_nchw_staged_k<float, 4>,
+                                               cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+          CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cnb_im2col_nchw: cudaFuncSetAttribute: %s",
+                      cudaGetErrorString(e));
+          attr_f32 = true;
+        }
+        im2col_nchw_staged_k<float, 4><<<grid, 256, smem, (cudaStream_t)stream>>>(src, (float*)dst, p, row_stride);
+      }
+      return check_launch("im2col_nchw_staged");
+    }
+  }
+  {
     // row-staged kernel when its smem patch fits the default 48 KB
     const size_t smem = (size_t)((K_dst * 4 + 15) / 16) * 16 +
                         (size_t)d->C * d->R * (d->W + 2 * d->pad_w) * dtype_size(d->dtype);
@@ -626,6 +808,7 @@ int cnb_channel_shuffle(const void* x, void* y, int64_t M, int32_t C, int32_t gr
   CNB_REQUIRE(C % groups == 0, CNB_ERR_INVALID, "cnb_channel_shuffle: C=%d not divisible by groups=%d",
               C, groups);
   if (M == 0) return CNB_OK;
+  if (shuffle_vec(x, y, M, C, groups, dtype, (cudaStream_t)stream)) return check_launch("channel_shuffle(vec)");
   CNB_DISPATCH_T(dtype, (shuffle_k<T><<<grid_for(M * C, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
                             (const T*)x, (T*)y, M, C, groups)));
   return check_launch("channel_shuffle");

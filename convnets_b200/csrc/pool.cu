@@ -190,6 +190,74 @@ __global__ void maxpool_bwd_k(const T* __restrict__ dy, const int32_t* __restric
   }
 }
 
+// k3 s2 p1 (the stem pool of every ResNet-family model) with 1-byte argmax codes: a thread owns a
+// 2x2 input quad (rows 2a, 2a+1; columns 2b, 2b+1).  Only the windows (a..a+1) x (b..b+1) reach
+// it, and each of them can hit the quad at fixed window positions only (window a: rows r = 1, 2;
+// window a+1: row r = 0; same for columns), so 4 code + 4 gradient vectors produce 4 outputs with
+// 9 compile-time (window, position) compares per channel instead of 4 x 4.
+template <typename T, int V>
+__global__ void maxpool_bwd_k3s2p1_k(const T* __restrict__ dy, const uint8_t* __restrict__ code,
+                                     T* __restrict__ dx, PoolP p) {
+  const int Cv = p.C / V;
+  const int HQ = (p.H + 1) / 2, WQ = (p.W + 1) / 2;
+  const int a = blockIdx.x % HQ;
+  const int n = blockIdx.x / HQ;
+  for (int item = threadIdx.x; item < WQ * Cv; item += blockDim.x) {
+    const int b = item / Cv;
+    const int cv = item - b * Cv;
+    Pack<uint8_t, V> cc[2][2];
+    Pack<T, V> g[2][2];
+    bool ok[2][2];
+#pragma unroll
+    for (int wa = 0; wa < 2; ++wa)
+#pragma unroll
+      for (int wb = 0; wb < 2; ++wb) {
+        ok[wa][wb] = a + wa < p.P && b + wb < p.Q;
+        if (ok[wa][wb]) {
+          const int64_t o = (((int64_t)n * p.P + a + wa) * p.Q + b + wb) * p.C + cv * V;
+          cc[wa][wb] = ld_pack<uint8_t, V>(code + o);
+          g[wa][wb] = ld_pack<T, V>(dy + o);
+        }
+      }
+    float acc[2][2][V];
+#pragma unroll
+    for (int dr = 0; dr < 2; ++dr)
+#pragma unroll
+      for (int dc = 0; dc < 2; ++dc)
+#pragma unroll
+        for (int j = 0; j < V; ++j) acc[dr][dc][j] = 0.f;
+    // quad row dr sits at window row r = dr + 1 of window a and (dr == 1 only) r = 0 of window a+1
+#pragma unroll
+    for (int wa = 0; wa < 2; ++wa)
+#pragma unroll
+      for (int wb = 0; wb < 2; ++wb) {
+        if (!ok[wa][wb]) continue;
+#pragma unroll
+        for (int dr = wa; dr < 2; ++dr)
+#pragma unroll
+          for (int dc = wb; dc < 2; ++dc) {
+            const int r = wa ? 0 : dr + 1, s_ = wb ? 0 : dc + 1;
+            const int want = r * 3 + s_;
+#pragma unroll
+            for (int j = 0; j < V; ++j)
+              if ((int)cc[wa][wb].v[j] == want) acc[dr][dc][j] += to_f(g[wa][wb].v[j]);
+          }
+      }
+#pragma unroll
+    for (int dr = 0; dr < 2; ++dr)
+#pragma unroll
+      for (int dc = 0; dc < 2; ++dc) {
+        const int h = 2 * a + dr, w = 2 * b + dc;
+        if (h < p.H && w < p.W) {
+          Pack<T, V> out;
+#pragma unroll
+          for (int j = 0; j < V; ++j) out.v[j] = from_f<T>(acc[dr][dc][j]);
+          st_pack<T, V>(dx + ((((int64_t)n * p.H + h) * p.W + w) * Cv + cv) * V, out);
+        }
+      }
+  }
+}
+
 // count_include_pad=True: divisor is always kh*kw; padded positions contribute zero.
 template <typename T, int V>
 __global__ void avgpool_fwd_k(const T* __restrict__ x, T* __restrict__ y, PoolP p,
@@ -322,6 +390,16 @@ int cnb_maxpool_bwd(const cnb_pool_desc* d, const void* dy, const int32_t* idx, 
   CNB_REQUIRE((int64_t)p.N * p.H < (1ll << 31), CNB_ERR_UNSUPPORTED, "cnb_maxpool_bwd: too many rows");
   const int grid = p.N * p.H;
   cudaStream_t st = (cudaStream_t)stream;
+  if (code && p.kh == 3 && p.kw == 3 && p.sh == 2 && p.sw == 2 && p.ph == 1 && p.pw == 1) {
+    const int items = ((p.W + 1) / 2) * (p.C / v);
+    const int passes = (items + kPoolThreads - 1) / kPoolThreads;
+    int threads = ((items + passes - 1) / passes + 31) / 32 * 32;
+    threads = threads < 32 ? 32 : (threads > kPoolThreads ? kPoolThreads : threads);
+    const int qgrid = p.N * ((p.H + 1) / 2);
+    CNB_DISPATCH_TV(d->dtype, v, (maxpool_bwd_k3s2p1_k<T, V><<<qgrid, threads, 0, st>>>(
+                                     (const T*)dy, code, (T*)dx, p)));
+    return check_launch("maxpool_bwd(k3s2p1)");
+  }
 #define MPB(NN) CNB_DISPATCH_TV(d->dtype, v, (maxpool_bwd_k<T, V, NN><<<grid, kPoolThreads, 0, st>>>( \
                                    (const T*)dy, code ? nullptr : idx, code, (T*)dx, p, total)))
   if (nw == 1) MPB(1);

@@ -36,7 +36,7 @@ def rnd(*shape, dtype=torch.float32, scale=1.0, shift=0.0):
 # ------------------------------------------------------------------ BatchNorm
 @pytest.mark.parametrize("dtype", DT)
 @pytest.mark.parametrize("shape", [(4, 64, 14, 14), (3, 60, 7, 5), (2, 10, 9, 9), (8, 32, 1, 1),
-                                   (2, 256, 28, 28), (1, 2048, 7, 7)])
+                                   (2, 256, 28, 28), (1, 2048, 7, 7), (8, 64, 56, 56), (4, 128, 37, 41)])
 @pytest.mark.parametrize("relu,res", [(False, False), (True, False), (True, True), (False, True)])
 def test_batch_norm_train(dtype, shape, relu, res):
     torch.manual_seed(1)
@@ -176,7 +176,8 @@ def test_relu_add_relu(dtype):
 
 # ------------------------------------------------------------------ data movement
 @pytest.mark.parametrize("dtype", DT)
-@pytest.mark.parametrize("c,g", [(60, 3), (240, 3), (24, 1), (272, 4), (384, 8)])
+@pytest.mark.parametrize("c,g", [(60, 3), (240, 3), (24, 1), (272, 4), (384, 8), (30, 3), (21, 3),
+                                 (960, 3), (136, 2)])
 def test_channel_shuffle_bit_exact(dtype, c, g):
     torch.manual_seed(8)
     x = rnd(2, c, 7, 7, dtype=dtype)
@@ -305,6 +306,45 @@ def test_conv2d_input_im2col(case):
     assert O.rel_l2(wd.grad, dw_ref) <= 1e-2
     if b is not None:
         assert O.rel_l2(bd.grad, db_ref) <= 1e-2
+
+
+@pytest.mark.parametrize("dtype", DT)
+@pytest.mark.parametrize("c,h,w,r,stride,pad,dil", [
+    (3, 33, 37, 7, 2, 3, 1),     # ResNet-family stem (output-staged kernel, odd column-block count)
+    (3, 29, 29, 7, 2, 0, 1),     # SqueezeNet 1.0 stem, no padding
+    (3, 18, 20, 3, 1, 1, 1),     # VGG / MobileNet first layer (even column-block count: padded rows)
+    (1, 12, 12, 5, 1, 2, 1),     # single-channel input
+    (5, 11, 13, 3, 2, 2, 2),     # dilated taps
+])
+def test_im2col_nchw_bit_exact(dtype, c, h, w, r, stride, pad, dil):
+    """cnb_im2col_nchw through the C ABI: column (r*S + s)*C + c of row (n, p, q) holds the rounded
+    input pixel (or zero in the padding / alignment columns) — bit-exact against torch unfold."""
+    import ctypes as C
+    from convnets_b200 import lib
+    L = lib.load()
+    torch.manual_seed(13)
+    n = 3
+    x = torch.randn(n, c, h, w)
+    code = lib.CNB_BF16 if dtype == torch.bfloat16 else lib.CNB_F32
+    v = 8 if dtype == torch.bfloat16 else 4
+    rsc = r * r * c
+    kd = (rsc + v - 1) // v * v
+    d = lib.ConvDesc(n, h, w, c, 8, r, r, stride, stride, pad, pad, dil, dil, 1, code, 0, lib.CNB_ALGO_AUTO)
+    P, Q = C.c_int32(), C.c_int32()
+    assert L.cnb_conv2d_out_dims(C.byref(d), C.byref(P), C.byref(Q)) == 0
+    P, Q = P.value, Q.value
+    xd = x.cuda()
+    col = torch.full((n * P * Q, kd), float("nan"), dtype=dtype, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    rc = L.cnb_im2col_nchw(C.byref(d), C.c_void_p(xd.data_ptr()), C.c_void_p(col.data_ptr()), kd,
+                           C.c_void_p(st))
+    assert rc == 0, lib.last_error()
+    torch.cuda.synchronize()
+    u = torch.nn.functional.unfold(x, r, dilation=dil, padding=pad, stride=stride)   # [n, c*r*r, P*Q]
+    u = u.view(n, c, r * r, P * Q).permute(0, 3, 2, 1).reshape(n * P * Q, rsc).to(dtype)
+    ref = torch.zeros(n * P * Q, kd, dtype=dtype)
+    ref[:, :rsc] = u
+    assert torch.equal(col.cpu(), ref)
 
 
 # ------------------------------------------------------------------ conv-epilogue statistics
