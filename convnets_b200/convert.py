@@ -162,6 +162,13 @@ def convert(model: nn.Module, dtype: torch.dtype = torch.bfloat16, fuse: bool = 
                 w.data = w.data.contiguous(memory_format=_CL)
     if first_conv is not None:
         first_conv.cast_input = True
+    if dtype == torch.bfloat16:
+        dense = [m for m in model.modules() if isinstance(m, L.Conv2d) and m.groups == 1
+                 and m.weight.shape[0] % 8 == 0 and m.weight.shape[1] % 8 == 0]
+        if dense:
+            group = L.PackGroup(dense)
+            for m in dense:
+                m.__dict__["_cnb_group"] = group
     if fuse:
         for m in model.modules():
             if isinstance(m, nn.Sequential):

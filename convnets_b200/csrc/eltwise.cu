@@ -630,6 +630,53 @@ __global__ void pack_filter_k(const float* __restrict__ w, bf16* __restrict__ wb
   }
 }
 
+// Every filter of a model in ONE launch (cnb_pack_filters): block -> item by binary search over the
+// items' first_block, then one [32 out-ch x 32 in-ch] tile of one tap: coalesced fp32 reads, the
+// bf16 copy in place, the channel-exchanged copy through a padded shared-memory transpose (64-byte
+// runs along K instead of 2-byte scattered stores).
+__global__ void __launch_bounds__(256)
+pack_filters_batched_k(const cnb_pack_item* __restrict__ items, int n_items) {
+  __shared__ bf16 tile[32][34];
+  int lo = 0, hi = n_items - 1;
+  const int b = blockIdx.x;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (items[mid].first_block <= b) lo = mid;
+    else hi = mid - 1;
+  }
+  const cnb_pack_item it = items[lo];
+  const int lb = b - it.first_block;
+  const int ctiles = (it.C + 31) / 32, ktiles = (it.K + 31) / 32;
+  const int ct = lb % ctiles;
+  const int t2 = lb / ctiles;
+  const int kt = t2 % ktiles;
+  const int rs = t2 / ktiles;
+  if (rs >= it.RS) return;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int k0 = kt * 32, c0 = ct * 32;
+  const float* w = it.w;
+  bf16* wb = (bf16*)it.w_bf16;
+  bf16* wt = (bf16*)it.wt_bf16;
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    const int k = k0 + ty + 8 * p, c = c0 + tx;
+    bf16 v = __float2bfloat16_rn(0.f);
+    if (k < it.K && c < it.C) {
+      const int64_t i = ((int64_t)k * it.RS + rs) * it.C + c;
+      v = __float2bfloat16_rn(w[i]);
+      wb[i] = v;
+    }
+    tile[ty + 8 * p][tx] = v;
+  }
+  if (!wt) return;
+  __syncthreads();
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    const int c = c0 + ty + 8 * p, k = k0 + tx;
+    if (c < it.C && k < it.K) wt[((int64_t)c * it.RS + rs) * it.K + k] = tile[tx][ty + 8 * p];
+  }
+}
+
 }  // namespace cnb
 
 using namespace cnb;
@@ -693,6 +740,20 @@ int cnb_pack_filter(const float* w, void* w_bf16, void* wt_bf16, int32_t K, int3
   pack_filter_k<<<grid_for(n, kThreads), kThreads, 0, (cudaStream_t)stream>>>(
       w, (bf16*)w_bf16, (bf16*)wt_bf16, K, RS, C);
   return check_launch("pack_filter");
+}
+
+int64_t cnb_pack_filter_blocks(int32_t K, int32_t RS, int32_t C) {
+  if (K <= 0 || RS <= 0 || C <= 0) return 0;
+  return (int64_t)RS * ((K + 31) / 32) * ((C + 31) / 32);
+}
+
+int cnb_pack_filters(const cnb_pack_item* items_device, int32_t n_items, int32_t total_blocks,
+                     void* stream) {
+  CNB_REQUIRE(items_device && n_items > 0 && total_blocks > 0, CNB_ERR_INVALID,
+              "cnb_pack_filters: bad args (items=%p n=%d blocks=%d)", (const void*)items_device, n_items,
+              total_blocks);
+  pack_filters_batched_k<<<(unsigned)total_blocks, 256, 0, (cudaStream_t)stream>>>(items_device, n_items);
+  return check_launch("pack_filters");
 }
 
 int cnb_cast(const void* src, int sdt, void* dst, int ddt, int64_t n, void* stream) {

@@ -7,6 +7,8 @@ and state_dict keys are all unchanged; only `forward` differs — it calls the C
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.nn as nn
 
@@ -35,6 +37,58 @@ def invalidate_packed_weights() -> None:
     """Force every layer to re-pack its weights on the next forward (call after editing
     parameters through a path neither an optimizer step nor the version counter sees)."""
     _bump_weight_epoch()
+
+
+# One launch re-packs every tensor-core filter of a model (cnb_pack_filters) instead of one KB-sized
+# launch per layer.  Off by default until it has been through the GPU parity suite
+# (tools/check_batched_pack.py); CNB_BATCHED_PACK=1 turns it on.
+_BATCHED_PACK = os.environ.get("CNB_BATCHED_PACK", "0") == "1"
+
+
+class PackGroup:
+    """The dense tensor-core Conv2d layers of one converted model and their persistent bf16 operand
+    buffers.  `refresh()` rebuilds every copy with one kernel; the device table of pointers is
+    built on first use and again only if a parameter was re-allocated (model.to(), load)."""
+
+    def __init__(self, layers):
+        self.layers = list(layers)
+        self.ptrs = None
+        self.table = None
+        self.bufs = None
+        self.n_blocks = 0
+
+    def _build(self):
+        import ctypes as C
+        lib = _L.load()
+        items = (_L.PackItem * len(self.layers))()
+        self.bufs = []
+        first = 0
+        for i, m in enumerate(self.layers):
+            w = m.weight.data
+            if not w.is_contiguous(memory_format=torch.channels_last):
+                raise RuntimeError("PackGroup: master weights must be KRSC (convert() stores them so)")
+            k, c, r, s_ = w.shape
+            wb = torch.empty_like(w, dtype=torch.bfloat16)
+            wt = None if m.cast_input else torch.empty((c, r * s_, k), dtype=torch.bfloat16,
+                                                       device=w.device)
+            self.bufs.append((wb, wt))
+            items[i] = _L.PackItem(w.data_ptr(), wb.data_ptr(), None if wt is None else wt.data_ptr(),
+                                   k, r * s_, c, first)
+            first += int(lib.cnb_pack_filter_blocks(k, r * s_, c))
+        self.n_blocks = first
+        raw = torch.frombuffer(bytearray(bytes(items)), dtype=torch.uint8)
+        self.table = raw.to(self.layers[0].weight.device)
+        self.ptrs = tuple(m.weight.data_ptr() for m in self.layers)
+
+    def refresh(self):
+        if self.ptrs != tuple(m.weight.data_ptr() for m in self.layers):
+            self._build()
+        lib = _L.load()
+        _L.check(lib.cnb_pack_filters(self.table.data_ptr(), len(self.layers), self.n_blocks,
+                                      torch.cuda.current_stream().cuda_stream), "cnb_pack_filters")
+        for m, pair in zip(self.layers, self.bufs):
+            w = m.weight
+            m.__dict__["_cnb_pack"] = ((_WEIGHT_EPOCH[0], w._version, w.data_ptr(), torch.bfloat16), pair)
 
 
 class Conv2d(nn.Conv2d):
@@ -68,6 +122,10 @@ class Conv2d(nn.Conv2d):
         if cache is None or cache[0] != key:
             dense_tc = (dtype == torch.bfloat16 and self.groups == 1 and w.dtype == torch.float32
                         and w.shape[0] % 8 == 0 and w.shape[1] % 8 == 0)
+            group = self.__dict__.get("_cnb_group") if _BATCHED_PACK else None
+            if dense_tc and group is not None and w.is_cuda:
+                group.refresh()   # re-packs every member, this layer included
+                return self.__dict__["_cnb_pack"][1]
             if dense_tc:
                 pair = F_.pack_filter(w, transposed=not self.cast_input)
             else:

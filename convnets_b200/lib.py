@@ -34,6 +34,12 @@ class BnDesc(C.Structure):
                 ("eps", C.c_float), ("momentum", C.c_float)]
 
 
+class PackItem(C.Structure):
+    """cnb_pack_item (include/convnets_b200.h): one filter of a batched cnb_pack_filters call."""
+    _fields_ = [("w", C.c_void_p), ("w_bf16", C.c_void_p), ("wt_bf16", C.c_void_p),
+                ("K", C.c_int32), ("RS", C.c_int32), ("C", C.c_int32), ("first_block", C.c_int32)]
+
+
 _P = C.c_void_p
 _I = C.c_int
 _I32 = C.c_int32
@@ -53,6 +59,8 @@ SIGNATURES = {
     "cnb_conv2d_fwd": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_conv2d_dgrad": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_pack_filter": (_I, [_P, _P, _P, _I32, _I32, _I32, _P]),
+    "cnb_pack_filter_blocks": (_I64, [_I32, _I32, _I32]),
+    "cnb_pack_filters": (_I, [_P, _I32, _I32, _P]),
     "cnb_conv2d_wgrad": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_bn_workspace_bytes": (_SZ, [C.POINTER(BnDesc)]),
     "cnb_bn_fwd_train": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _P,

@@ -200,6 +200,20 @@ int cnb_im2col_nchw(const cnb_conv_desc* d, const float* src, void* dst, int32_t
  * [C][R*S][K] (data-grad).  One pass per optimiser step. */
 int cnb_pack_filter(const float* w, void* w_bf16, void* wt_bf16, int32_t K, int32_t RS, int32_t C,
                     void* stream);
+/* The same for every dense filter of a model in one launch (the per-layer launches are KB-sized
+ * work).  `items_device` is a device array, sorted by first_block: item i owns the blocks
+ * [first_block_i, first_block_i + cnb_pack_filter_blocks(K_i, RS_i, C_i)); total_blocks is their
+ * sum.  wt_bf16 may be NULL per item.  The table is built once per model by the caller. */
+typedef struct cnb_pack_item {
+  const float* w;
+  void* w_bf16;
+  void* wt_bf16;
+  int32_t K, RS, C;
+  int32_t first_block;
+} cnb_pack_item;
+int64_t cnb_pack_filter_blocks(int32_t K, int32_t RS, int32_t C);
+int cnb_pack_filters(const cnb_pack_item* items_device, int32_t n_items, int32_t total_blocks,
+                     void* stream);
 /* element-wise precision conversion (fp32 master weights -> bf16 operand copy, etc.) */
 int cnb_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n, void* stream);
 

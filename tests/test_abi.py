@@ -112,3 +112,35 @@ def test_packed_weight_cache_key_moves_with_every_optimizer_step():
     e = L._WEIGHT_EPOCH[0]
     L.invalidate_packed_weights()
     assert L._WEIGHT_EPOCH[0] == e + 1
+
+
+def test_batched_pack_table_layout(lib):
+    """cnb_pack_filters takes a device array of cnb_pack_item: the ctypes mirror must have the C
+    layout, the block ranges must tile [0, total) in order, and convert() must enrol exactly the
+    dense layers the tensor-core path takes (the table itself needs no GPU to build)."""
+    import convnets_b200 as cnb
+    from convnets_b200 import layers as L
+    assert C.sizeof(lib.PackItem) == 40            # 3 pointers + 4 int32, no padding
+    h = lib.load()
+    assert h.cnb_pack_filter_blocks(64, 9, 64) == 9 * 2 * 2
+    assert h.cnb_pack_filter_blocks(40, 1, 24) == 1 * 2 * 1
+    assert h.cnb_pack_filter_blocks(0, 1, 8) == 0
+    net = torch.nn.Sequential(torch.nn.Conv2d(3, 16, 3, padding=1), torch.nn.Conv2d(16, 40, 1),
+                              torch.nn.Conv2d(40, 40, 3, padding=1, groups=5),
+                              torch.nn.Conv2d(40, 72, 3, padding=1, bias=False))
+    cnb.convert(net)
+    group = net[1].__dict__["_cnb_group"]
+    assert [m is net[1] or m is net[3] for m in group.layers] == [True, True]
+    assert "_cnb_group" not in net[0].__dict__ and "_cnb_group" not in net[2].__dict__
+    group._build()
+    items = (lib.PackItem * 2).from_buffer_copy(bytes(group.table.numpy().tobytes()))
+    first = 0
+    for it, m, (wb, wt) in zip(items, group.layers, group.bufs):
+        k, c, r, s = m.weight.shape
+        assert (it.K, it.RS, it.C, it.first_block) == (k, r * s, c, first)
+        assert it.w == m.weight.data_ptr() and it.w_bf16 == wb.data_ptr() and it.wt_bf16 == wt.data_ptr()
+        assert wb.shape == m.weight.shape and wb.is_contiguous(memory_format=torch.channels_last)
+        assert wt.shape == (c, r * s, k)
+        first += h.cnb_pack_filter_blocks(k, r * s, c)
+    assert group.n_blocks == first
+    assert L._BATCHED_PACK is False                # stays opt-in until validated on the GPU
