@@ -122,6 +122,24 @@ int cnb_conv2d_dgrad(const cnb_conv_desc* d, const void* dy, const void* w, cons
   return conv_simt_dgrad(*d, dy, w, dx, st);
 }
 
+int cnb_conv2d_dgrad_add(const cnb_conv_desc* d, const void* dy, const void* w, const void* w_t,
+                         const void* addend, void* dx, void* workspace, size_t workspace_bytes,
+                         void* stream) {
+  CNB_TRY(validate_conv(d, "cnb_conv2d_dgrad_add"));
+  CNB_REQUIRE(dy && w && dx && addend, CNB_ERR_INVALID, "cnb_conv2d_dgrad_add: null tensor pointer");
+  CNB_REQUIRE(!is_depthwise(*d) && d->stride_h == 1 && d->stride_w == 1, CNB_ERR_UNSUPPORTED,
+              "cnb_conv2d_dgrad_add: stride-1 tensor-core data-grad only (stride %dx%d, groups %d)",
+              d->stride_h, d->stride_w, d->groups);
+  const char* why = "";
+  CNB_REQUIRE(d->algo != CNB_ALGO_SIMT && conv_tc_supported(*d, CNB_DGRAD, &why), CNB_ERR_UNSUPPORTED,
+              "cnb_conv2d_dgrad_add: no tensor-core path: %s", why);
+  CNB_REQUIRE(((uintptr_t)dy | (uintptr_t)w | (uintptr_t)dx | (uintptr_t)addend) % 16 == 0,
+              CNB_ERR_INVALID, "cnb_conv2d_dgrad_add: tensor pointers must be 16-byte aligned");
+  CNB_REQUIRE(!w_t || (uintptr_t)w_t % 16 == 0, CNB_ERR_INVALID,
+              "cnb_conv2d_dgrad_add: w_t must be 16-byte aligned");
+  return conv_tc_dgrad(*d, dy, w, w_t, dx, workspace, workspace_bytes, (cudaStream_t)stream, addend);
+}
+
 int cnb_conv2d_wgrad(const cnb_conv_desc* d, const void* x, const void* dy, float* dw, float* dbias,
                      void* workspace, size_t workspace_bytes, void* stream) {
   CNB_TRY(validate_conv(d, "cnb_conv2d_wgrad"));

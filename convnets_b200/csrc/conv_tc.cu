@@ -117,11 +117,15 @@ static int make_im2col_map(CUtensorMap* m, const void* base, int N, int H, int W
 // ==========================================================================================
 // forward / data-grad kernel
 // ==========================================================================================
+// internal epilogue flag (next to CNB_CONV_BIAS / CNB_CONV_RELU): out = acc + addend
+constexpr int kConvAccum = 1 << 8;
+
 struct FpropParams {
   CUtensorMap tmA;  // activations: im2col {C,W,H,N} (box 64ch x 128 pixels) or tiled {C, M}
   CUtensorMap tmB;  // weights {Cg, RS, Kout}, box {64, 1, BLOCK_N}
   CUtensorMap tmD;  // output {Kout, M}, box {64, 128}
   const float* bias;
+  const bf16* addend;  // optional [M][Kout]: added to the accumulator before the bf16 rounding (kConvAccum)
   float* stats;     // optional [persistent CTAs / n_tiles][2][Kout] column sums / sums of squares of the stored output
   int M;            // output pixels in this launch
   int outP, outQ;   // output grid per image (pixel index -> (n, i, j))
@@ -310,6 +314,21 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
         const int c0 = chalf * HALF_N + ch * 32;
         const uint32_t box = row_addr + (uint32_t)(c0 / 64) * (TILE_M * 128);
         const uint32_t chunk0 = (uint32_t)((c0 % 64) / 8);
+        // skip-gradient accumulation: this lane's 32 columns of the addend row, 4 x 16 bytes, all
+        // requested before the first use (rows past M / columns past Kout are never stored)
+        uint4 add4[4];
+        if (!PLAIN) {
+          if (p.flags & kConvAccum) {
+            const int64_t grow = (int64_t)m0 + row;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const int col = n0 + c0 + j * 8;
+              add4[j] = (grow < p.M && col < p.Kout)
+                            ? __ldg(reinterpret_cast<const uint4*>(p.addend + grow * p.Kout + col))
+                            : make_uint4(0u, 0u, 0u, 0u);
+            }
+          }
+        }
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           uint32_t packed[4];
@@ -318,6 +337,11 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
             float f0 = __uint_as_float(cur[j * 8 + e * 2 + 0]);
             float f1 = __uint_as_float(cur[j * 8 + e * 2 + 1]);
             if (!PLAIN) {
+              if (p.flags & kConvAccum) {
+                const uint32_t a2 = e == 0 ? add4[j].x : (e == 1 ? add4[j].y : (e == 2 ? add4[j].z : add4[j].w));
+                f0 += __uint_as_float(a2 << 16);
+                f1 += __uint_as_float(a2 & 0xffff0000u);
+              }
               const int col = n0 + c0 + j * 8 + e * 2;
               if (p.flags & CNB_CONV_BIAS) {
                 f0 += (col < p.Kout) ? p.bias[col] : 0.f;
@@ -711,6 +735,7 @@ struct FpropLaunch {
   int Kout, RS;
   void* out;                     // [aN*outP*outQ, Kout] bf16
   const float* bias;
+  const void* addend;            // optional [M][Kout] bf16 summed into the output (data-grad + skip gradient)
   float* stats;                  // optional BatchNorm partials (forward only)
   int flags;
   bool tiled2d;                  // pure GEMM: A is the [M, C] matrix itself
@@ -802,6 +827,8 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
   prm.grp_in = L.grp_in;
   prm.Kout = L.Kout;
   prm.flags = L.flags & ((L.bias ? CNB_CONV_BIAS : 0) | CNB_CONV_RELU);
+  prm.addend = reinterpret_cast<const bf16*>(L.addend);
+  if (L.addend) prm.flags |= kConvAccum;
   for (int t = 0; t < L.ntaps; ++t) {
     prm.off_h[t] = L.off_h[t];
     prm.off_w[t] = L.off_w[t];
@@ -1048,7 +1075,9 @@ int conv_tc_fwd(const cnb_conv_desc& d, const void* x, const void* w, const floa
 }
 
 int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const void* w_t, void* dx,
-                  void* ws, size_t ws_bytes, cudaStream_t st) {
+                  void* ws, size_t ws_bytes, cudaStream_t st, const void* addend) {
+  CNB_REQUIRE(!addend || (d.stride_h == 1 && d.stride_w == 1), CNB_ERR_UNSUPPORTED,
+              "conv_tc_dgrad: the accumulating epilogue exists for stride-1 data-grad only");
   CNB_REQUIRE(ws && ws_bytes >= conv_tc_workspace(d, CNB_DGRAD), CNB_ERR_WORKSPACE,
               "conv_tc_dgrad: workspace %zu < %zu", ws_bytes, conv_tc_workspace(d, CNB_DGRAD));
   int P, Q;
@@ -1099,6 +1128,7 @@ int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const v
     L.w = wt; L.Kout = d.C; L.RS = RS;
     if (grouped) { L.grp_out = Cg; L.grp_in = Kg; L.wC = wCd; }
     L.out = dx; L.bias = nullptr; L.flags = 0;
+    L.addend = addend;
     L.tiled2d = (RS == 1 && d.pad_h == 0 && d.pad_w == 0);
     return launch_fprop(L, st);
   }

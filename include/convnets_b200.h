@@ -116,6 +116,13 @@ int cnb_conv2d_fwd(const cnb_conv_desc* d, const void* x, const void* w, const f
  * transposes w into the workspace on every call. */
 int cnb_conv2d_dgrad(const cnb_conv_desc* d, const void* dy, const void* w, const void* w_t, void* dx,
                      void* workspace, size_t workspace_bytes, void* stream);
+/* dx = conv_transpose(dy, w) + addend[N,H,W,C]: the sum autograd forms where a residual block's
+ * input feeds both the first conv and the identity shortcut (reference src/resnet.py:139-156,
+ * 176-196), folded into the data-grad epilogue.  Stride-1 convolutions on the tensor-core path only
+ * (anything else is CNB_ERR_UNSUPPORTED); dx may alias addend. */
+int cnb_conv2d_dgrad_add(const cnb_conv_desc* d, const void* dy, const void* w, const void* w_t,
+                         const void* addend, void* dx, void* workspace, size_t workspace_bytes,
+                         void* stream);
 /* dw[K,R,S,C/g] (fp32) = x (*) dy ; dbias[K] (fp32, may be NULL) = sum over N,P,Q of dy */
 int cnb_conv2d_wgrad(const cnb_conv_desc* d, const void* x, const void* dy, float* dw, float* dbias,
                      void* workspace, size_t workspace_bytes, void* stream);
