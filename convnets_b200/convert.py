@@ -18,6 +18,7 @@ and on the mirrors in convnets_b200.zoo.
 """
 from __future__ import annotations
 
+import os
 import types
 
 import torch
@@ -51,6 +52,42 @@ def _tail(last: nn.Module):
 _BODY_NAMES = ("res_block", "res_bottleneck", "se_bottleneck", "sk_bottleneck")
 
 
+# Identity-shortcut blocks: fold the skip gradient into the first conv's data-grad epilogue
+# (functional._Conv2dSkipFn) instead of letting autograd add the two gradients of the block input.
+# Opt-in (CNB_FUSED_SKIP_GRAD=1) until tools/check_dgrad_add.py and the train-step parity tests have
+# run with it on a GPU.
+_FUSED_SKIP = os.environ.get("CNB_FUSED_SKIP_GRAD", "0") == "1"
+
+
+def _can_fold_skip(blocks, x) -> bool:
+    first = blocks[0]
+    if not (isinstance(first, nn.Sequential) and len(blocks) > 1 and torch.is_grad_enabled()
+            and x.requires_grad and x.dtype == torch.bfloat16):
+        return False
+    conv = next(iter(first.children()), None)
+    return (isinstance(conv, L.Conv2d) and not conv.cast_input and conv.stride in (1, (1, 1))
+            and conv.padding_mode == "zeros" and not isinstance(conv.padding, str))
+
+
+def _residual_forward_folded(self, blocks, x):
+    first = list(blocks[0].children())
+    out, identity = first[0].forward_with_skip(x)
+    for m in first[1:]:
+        out = m(out)
+    last = blocks[-1]
+    if isinstance(last, nn.Sequential) and isinstance(next(iter(last.children()), None), nn.Conv2d):
+        for blk in blocks[1:-1]:
+            out = blk(out)
+        conv, bn = _tail(last)
+        out = conv(out)
+        if bn is not None:
+            return bn(out, residual=identity, relu=True)
+        return F_.add_relu(out, identity)
+    for blk in blocks[1:]:
+        out = blk(out)
+    return F_.add_relu(out, identity)
+
+
 def _residual_forward(self, x):
     """body(x) += shortcut(x); relu.  When the body ends in a conv block, the residual add and the
     ReLU run inside that block's BatchNorm kernel; when it ends in an SE unit they are one
@@ -58,6 +95,8 @@ def _residual_forward(self, x):
     src/sknet.py:160-171)."""
     body = next(getattr(self, n) for n in _BODY_NAMES if hasattr(self, n))
     blocks = list(body.children())
+    if _FUSED_SKIP and self.dim_synch is None and _can_fold_skip(blocks, x):
+        return _residual_forward_folded(self, blocks, x)
     identity = x if self.dim_synch is None else self.dim_synch(x)
     last = blocks[-1]
     if isinstance(last, nn.Sequential) and isinstance(next(iter(last.children()), None), nn.Conv2d):

@@ -219,6 +219,72 @@ def conv2d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, wpac
     return y
 
 
+class _Conv2dSkipFn(torch.autograd.Function):
+    """conv2d that also hands its input on as a second output (the identity shortcut of a residual
+    block, reference src/resnet.py:139-156,176-196).  Autograd then calls ONE backward with both
+    gradients, and the data-grad epilogue adds the skip gradient (cnb_conv2d_dgrad_add) instead of
+    a separate element-wise add over the block input.  Used only when CNB_FUSED_SKIP_GRAD=1
+    (convert._residual_forward); everything but the data-grad is _Conv2dFn."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, wpack, stride, padding, dilation, groups, algo, want_stats,
+                wpack_t=None):
+        y, part = _Conv2dFn.forward(ctx, x, weight, bias, wpack, stride, padding, dilation, groups,
+                                    algo, want_stats, wpack_t)
+        return y, part, x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, dy, _dpart=None, dskip=None):
+        if dskip is None or not ctx.needs_input_grad[0]:
+            return _Conv2dFn.backward(ctx, dy, _dpart)
+        lib = _L.load()
+        x, wpack, wpack_t = ctx.saved_tensors
+        d = ctx.desc
+        dy = _nhwc(dy)
+        if dy.dtype != x.dtype:
+            dy = dy.to(x.dtype)
+        dskip = _nhwc(dskip)
+        if dskip.dtype != x.dtype:
+            dskip = dskip.to(x.dtype)
+        dx = torch.empty_like(x, memory_format=_CL)
+        nws = lib.cnb_conv2d_workspace_bytes(C.byref(d), _L.CNB_DGRAD)
+        ws = _workspace(nws, x.device)
+        fused = (d.stride_h == 1 and d.stride_w == 1 and d.algo != _L.CNB_ALGO_SIMT
+                 and lib.cnb_conv2d_uses_tc(C.byref(d), _L.CNB_DGRAD) == 1)
+        if fused:
+            _L.check(lib.cnb_conv2d_dgrad_add(C.byref(d), _p(dy), _p(wpack), _p(wpack_t), _p(dskip),
+                                              _p(dx), _p(ws), ws.numel(), _stream()),
+                     "cnb_conv2d_dgrad_add")
+        else:
+            _L.check(lib.cnb_conv2d_dgrad(C.byref(d), _p(dy), _p(wpack), _p(wpack_t), _p(dx), _p(ws),
+                                          ws.numel(), _stream()), "cnb_conv2d_dgrad")
+            dx.add_(dskip)
+        dw = db = None
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            dw = torch.empty(tuple(wpack.shape), dtype=torch.float32, device=x.device,
+                             memory_format=_CL)
+            if ctx.has_bias:
+                db = torch.empty(ctx.wshape[0], dtype=torch.float32, device=x.device)
+            nws = lib.cnb_conv2d_workspace_bytes(C.byref(d), _L.CNB_WGRAD)
+            ws = _workspace(nws, x.device)
+            _L.check(lib.cnb_conv2d_wgrad(C.byref(d), _p(x), _p(dy), _p(dw), _p(db), _p(ws),
+                                          ws.numel(), _stream()), "cnb_conv2d_wgrad")
+            if tuple(dw.shape) != ctx.wshape:
+                dw = dw[:, :ctx.wshape[1]].contiguous(memory_format=_CL)
+        return dx, dw, db, None, None, None, None, None, None, None, None
+
+
+def conv2d_with_skip(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, wpack=None,
+                     algo=_L.CNB_ALGO_AUTO, bn_stats=False, wpack_t=None):
+    """conv2d(x, ...) plus an alias of x for the identity shortcut: returns (y, partials-or-None,
+    x_skip).  See _Conv2dSkipFn."""
+    if wpack is None:
+        wpack = pack_weight(weight, x.dtype)
+    y, part, xs = _Conv2dSkipFn.apply(x, weight, bias, wpack, _pair(stride), _pair(padding),
+                                      _pair(dilation), int(groups), int(algo), bool(bn_stats), wpack_t)
+    return y, (part if (bn_stats and part.shape[0] > 0) else None), xs
+
+
 class _InputConvFn(torch.autograd.Function):
     """First layer of a network on the tensor-core path: explicit im2col of the fp32 NCHW batch
     (cnb_im2col_nchw) followed by a [N*P*Q, Kd] x [Kd, K] GEMM through cnb_conv2d_fwd with a 1x1

@@ -134,6 +134,16 @@ class Conv2d(nn.Conv2d):
             self.__dict__["_cnb_pack"] = cache
         return cache[1]
 
+    def forward_with_skip(self, x: torch.Tensor):
+        """(conv(x), alias of x for the identity shortcut): the residual blocks' first conv when
+        the skip gradient is folded into its data-grad (functional._Conv2dSkipFn)."""
+        stats = self.emit_bn_stats and self.training
+        wpack, wpack_t = self._packed(x.dtype)
+        y, part, xs = F_.conv2d_with_skip(x, self.weight, self.bias, self.stride, self.padding,
+                                          self.dilation, self.groups, wpack=wpack, algo=self.algo,
+                                          bn_stats=stats, wpack_t=wpack_t)
+        return self._tag((y, part)), xs
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if self.padding_mode != "zeros" or isinstance(self.padding, str):
             raise NotImplementedError("convnets_b200.Conv2d supports integer zero padding only")
