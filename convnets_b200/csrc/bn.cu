@@ -235,6 +235,57 @@ bn_stats_k(const T* __restrict__ x, float* __restrict__ part, int64_t M, int C,
   bn_finish_fwd(c, S, Q, (double)to_f(x[c]), M, f);
 }
 
+// Pointer-walk form of bn_stats_k (same sums, same merge; see the backward kernels for the loop
+// shape): U rows in flight per thread, MINB resident CTAs per SM.  Opt-in through
+// CNB_BN_STATS_VARIANT until it has been swept on the GPU (tools/gpu_bn_variants.sh <tag> STATS ...).
+template <typename T, int V, int U, int MINB>
+__global__ void __launch_bounds__(kBnThreads, MINB)
+bn_stats_walk_k(const T* __restrict__ x, float* __restrict__ part, int64_t M, int C,
+                int64_t rows_per_split, int splits, int* __restrict__ counter, BnFwdFin f) {
+  extern __shared__ __align__(16) float red[];
+  const int cv = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c0 = cv * V;
+  const int64_t r0 = blockIdx.y * rows_per_split;
+  int64_t r1 = r0 + rows_per_split;
+  if (r1 > M) r1 = M;
+  float s[V], q[V], piv[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) s[j] = q[j] = piv[j] = 0.f;
+  if (c0 < C) {
+    const Pack<T, V> p0 = ld_pack<T, V>(x + c0);
+#pragma unroll
+    for (int j = 0; j < V; ++j) piv[j] = to_f(p0.v[j]);
+    const int ry = blockDim.y;
+    const int64_t stride = (int64_t)ry * C;
+    int64_t r = r0 + threadIdx.y;
+    const T* xp = x + r * C + c0;
+    auto accum = [&](const Pack<T, V>& a) {
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        const float dlt = to_f(a.v[j]) - piv[j];
+        s[j] += dlt;
+        q[j] = fmaf(dlt, dlt, q[j]);
+      }
+    };
+    for (; r + (int64_t)(U - 1) * ry < r1; r += (int64_t)U * ry) {
+      Pack<T, V> a[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) a[u] = ld_pack<T, V>(xp + u * stride);
+#pragma unroll
+      for (int u = 0; u < U; ++u) accum(a[u]);
+      xp += U * stride;
+    }
+    for (; r < r1; r += ry) {
+      accum(ld_pack<T, V>(xp));
+      xp += stride;
+    }
+  }
+  int c;
+  double S, Q;
+  if (!bn_block_merge<V>(s, q, red, part, C, splits, counter, c, S, Q)) return;
+  bn_finish_fwd(c, S, Q, (double)to_f(x[c]), M, f);
+}
+
 // Statistics from per-tile partials written by the convolution epilogue (conv_tc.cu):
 // tiles[n][2][C] fp32 = column sums / sums of squares of 128-row tiles of the stored activations.
 // Same two-level, fixed-order merge as bn_stats_k (rows here are tiles, no pivot).
@@ -564,6 +615,16 @@ static int bn_fwd_variant() {
   }
   return v;
 }
+// bf16 statistics kernel: 0 = bn_stats_k (validated), 1 = walk (4 rows, 4 CTAs/SM), 2 = walk (8, 3)
+static int bn_stats_variant() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("CNB_BN_STATS_VARIANT");
+    v = e ? atoi(e) : 0;
+    if (v < 0 || v > 2) v = 0;
+  }
+  return v;
+}
 static int apply_waves(bool hot, int variant) {
   if (hot && (variant == 1 || variant == 2)) return 6;   // 3 resident CTAs per SM
   return kStreamWaves;                                    // 2 or 4 resident CTAs per SM
@@ -656,7 +717,8 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
                                              g.splits, counter, fin);
     CNB_TRY(check_launch("bn_partials"));
   } else {
-    BnGeom g = bn_geom(M, C, v, kReduceWaves, kReduceCx);
+    const int svariant = (d->dtype == CNB_BF16 && v == 8) ? bn_stats_variant() : 0;
+    BnGeom g = bn_geom(M, C, v, svariant == 2 ? 3 : kReduceWaves, kReduceCx);
     scale = part + (size_t)2 * C * g.splits;
     fin.scale = scale; fin.shift = scale + C;
     int* counter = bn_counters(g.cblocks);
@@ -664,9 +726,16 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
     dim3 grid(g.cblocks, g.splits), block(g.cx, g.ry);
     size_t smem = (size_t)g.ry * 2 * g.cx * v * sizeof(float);
     if (smem < 4096) smem = 4096;  // the merge step re-uses it for 256 x 2 doubles
-    CNB_DISPATCH_TV(d->dtype, v, (bn_stats_k<T, V><<<grid, block, smem, st>>>(
-                                     (const T*)x, part, M, C, g.rows_per_split, g.splits, counter,
-                                     fin)));
+    if (svariant == 1)
+      bn_stats_walk_k<bf16, 8, 4, 4><<<grid, block, smem, st>>>((const bf16*)x, part, M, C, g.rows_per_split,
+                                                                g.splits, counter, fin);
+    else if (svariant == 2)
+      bn_stats_walk_k<bf16, 8, 8, 3><<<grid, block, smem, st>>>((const bf16*)x, part, M, C, g.rows_per_split,
+                                                                g.splits, counter, fin);
+    else
+      CNB_DISPATCH_TV(d->dtype, v, (bn_stats_k<T, V><<<grid, block, smem, st>>>(
+                                       (const T*)x, part, M, C, g.rows_per_split, g.splits, counter,
+                                       fin)));
     CNB_TRY(check_launch("bn_stats"));
   }
   float* shift = scale + C;

@@ -27,3 +27,5 @@ try:
     d=json.loads(sys.stdin.read()); print('  %.0f img/s  %.2f ms/step'%(d['value'], d['ms_per_step']))
 except Exception as e: print('  no json', e)"
 done
+# 5. statistics-kernel loop shapes on the model that uses them most (BatchNorm after depthwise convs)
+MODEL=mobilenet bash tools/gpu_bn_variants.sh ${TAG}s STATS 0 1 2
