@@ -274,6 +274,52 @@ im2col_nchw_staged_k(const float* __restrict__ src, T* __restrict__ dst, Im2colP
   }
 }
 
+// Row im2col for the RGB stems (cnb_rowim2col_nchw): only the S horizontal taps are unrolled into
+// channels, dst[n][h][q][s*C + c] = src[n][c][h][q*sw - pw + s*dw] (zero outside / in the alignment
+// columns).  The R x S stem then runs on the im2col-mode TMA path as an R x 1 convolution over
+// S*C (21 -> 24) channels with vertical stride sh: a [N, H, Q, 24] tensor (316 MB at B = 256)
+// replaces the [N*P*Q, 152] matrix (976 MB).  One CTA per input row (n, h).
+template <typename T, int V>
+__global__ void __launch_bounds__(256)
+rowim2col_nchw_k(const float* __restrict__ src, T* __restrict__ dst, Im2colP p) {
+  extern __shared__ __align__(16) uint8_t sm_raw[];
+  const int Wp = p.W + 2 * p.pw;
+  int* coltab = reinterpret_cast<int*>(sm_raw);                                   // [Kd]
+  T* patch = reinterpret_cast<T*>(sm_raw + (size_t)((p.Kd * 4 + 15) / 16) * 16);  // [Wp][C]
+  const int h = blockIdx.x % p.H;
+  const int n = blockIdx.x / p.H;
+  const int SC = p.S * p.C;
+  for (int col = threadIdx.x; col < p.Kd; col += blockDim.x)
+    coltab[col] = col < SC ? (col / p.C) * p.dw * p.C + (col % p.C) : -1;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  for (int c = warp; c < p.C; c += nwarps) {
+    const float* srow = src + (((int64_t)n * p.C + c) * p.H + h) * p.W;
+    for (int wp = lane; wp < Wp; wp += 32) {
+      const int w = wp - p.pw;
+      patch[wp * p.C + c] = from_f<T>((w >= 0 && w < p.W) ? __ldg(srow + w) : 0.f);
+    }
+  }
+  __syncthreads();
+  const int kv = p.Kd / V;
+  T* out = dst + ((int64_t)n * p.H + h) * p.Q * p.Kd;
+  const T zero = from_f<T>(0.f);
+  int q = threadIdx.x / kv, cv = threadIdx.x - q * kv;
+  const int dq = blockDim.x / kv, dcv = blockDim.x - dq * kv;
+  for (int i = threadIdx.x; i < p.Q * kv; i += blockDim.x) {
+    const int base = q * p.sw * p.C;
+    Pack<T, V> o;
+#pragma unroll
+    for (int e = 0; e < V; ++e) {
+      const int off = coltab[cv * V + e];
+      o.v[e] = off >= 0 ? patch[off + base] : zero;
+    }
+    st_pack<T, V>(out + (int64_t)i * V, o);
+    q += dq;
+    cv += dcv;
+    if (cv >= kv) { cv -= kv; ++q; }
+  }
+}
+
 // ------------------------------------------------------------------ channel shuffle / slab copy
 // y[m, j*g + i] = x[m, i*(C/g) + j]; one thread per output element pair is fine: rows are short
 // and both sides stay within one row (L1/L2 absorb the permutation), traffic = 2 * numel.
@@ -860,6 +906,33 @@ int cnb_im2col_nchw(const cnb_conv_desc* d, const float* src, void* dst, int32_t
     im2col_nchw_k<float, 4><<<grid_for(total, kThreads, 16), kThreads, 0, (cudaStream_t)stream>>>(
         src, (float*)dst, p, total);
   return check_launch("im2col_nchw");
+}
+
+int cnb_rowim2col_nchw(const cnb_conv_desc* d, const float* src, void* dst, int32_t C_dst,
+                       void* stream) {
+  CNB_REQUIRE(d && src && dst, CNB_ERR_INVALID, "cnb_rowim2col_nchw: null pointer");
+  CNB_REQUIRE(d->N > 0 && d->H > 0 && d->W > 0 && d->C > 0 && d->S > 0 && d->stride_w > 0 &&
+                  d->dil_w > 0 && d->pad_w >= 0 && valid_dtype(d->dtype),
+              CNB_ERR_INVALID, "cnb_rowim2col_nchw: bad descriptor");
+  const int Q = (d->W + 2 * d->pad_w - d->dil_w * (d->S - 1) - 1) / d->stride_w + 1;
+  CNB_REQUIRE(Q > 0, CNB_ERR_INVALID, "cnb_rowim2col_nchw: empty output");
+  const int v = (int)(16 / dtype_size(d->dtype));
+  CNB_REQUIRE(C_dst >= d->S * d->C && C_dst % v == 0 && (uintptr_t)dst % 16 == 0, CNB_ERR_INVALID,
+              "cnb_rowim2col_nchw: C_dst=%d must be >= S*C=%d, a multiple of %d, dst 16B-aligned", C_dst,
+              d->S * d->C, v);
+  CNB_REQUIRE(C_dst / v <= 256 && (int64_t)d->N * d->H < (1ll << 31), CNB_ERR_UNSUPPORTED,
+              "cnb_rowim2col_nchw: C_dst=%d too wide (network-input stems only)", C_dst);
+  Im2colP p{d->N, d->C, d->H, d->W, 1, d->S, d->H, Q, 1, d->stride_w, 0, d->pad_w, 1, d->dil_w, C_dst};
+  const size_t smem = (size_t)((C_dst * 4 + 15) / 16) * 16 +
+                      (size_t)(d->W + 2 * d->pad_w) * d->C * dtype_size(d->dtype);
+  CNB_REQUIRE(smem <= 48 * 1024, CNB_ERR_UNSUPPORTED, "cnb_rowim2col_nchw: row of %d x %d too large", d->W,
+              d->C);
+  const unsigned grid = (unsigned)((int64_t)d->N * d->H);
+  if (d->dtype == CNB_BF16)
+    rowim2col_nchw_k<bf16, 8><<<grid, 256, smem, (cudaStream_t)stream>>>(src, (bf16*)dst, p);
+  else
+    rowim2col_nchw_k<float, 4><<<grid, 256, smem, (cudaStream_t)stream>>>(src, (float*)dst, p);
+  return check_launch("rowim2col_nchw");
 }
 
 int cnb_channel_shuffle(const void* x, void* y, int64_t M, int32_t C, int32_t groups, int dtype,

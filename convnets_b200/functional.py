@@ -360,6 +360,42 @@ def conv2d_input(x, weight, bias=None, stride=1, padding=0, dilation=1, dtype=to
     return y
 
 
+def rowim2col(x, kernel_w, stride_w, pad_w, dil_w, dtype):
+    """fp32 NCHW batch -> [N, S*C rounded up, H, Q] in `dtype`, channels_last: the S horizontal taps of
+    the stem filter unrolled into channels (cnb_rowim2col_nchw).  No gradient: x is the input batch."""
+    _cuda(x)
+    lib = _L.load()
+    if x.dtype != torch.float32 or not x.is_contiguous():
+        x = x.float().contiguous()
+    n, c, h, w = x.shape
+    v = 8 if dtype == torch.bfloat16 else 4
+    cd = (kernel_w * c + v - 1) // v * v
+    q = (w + 2 * pad_w - dil_w * (kernel_w - 1) - 1) // stride_w + 1
+    code = _L.CNB_BF16 if dtype == torch.bfloat16 else _L.CNB_F32
+    d = _L.ConvDesc(n, h, w, c, 8, 1, kernel_w, 1, stride_w, 0, pad_w, 1, dil_w, 1, code, 0,
+                    _L.CNB_ALGO_AUTO)
+    out = _empty_nhwc(n, cd, h, q, dtype, x.device)
+    _L.check(lib.cnb_rowim2col_nchw(C.byref(d), _p(x), _p(out), cd, _stream()), "cnb_rowim2col_nchw")
+    return out
+
+
+def conv2d_input_rows(x, weight, bias=None, stride=1, padding=0, dilation=1, dtype=torch.bfloat16,
+                      bn_stats=False):
+    """The network's first convolution as an R x 1 convolution over the row-im2col of the batch
+    (see rowim2col): same result as conv2d_input, a third of the bytes.  The filter is rearranged by
+    differentiable torch ops ([K, C, R, S] -> [K, S*C (+pad), R, 1]), so the weight gradient flows
+    back through them.  Opt-in (layers: CNB_STEM_ROWS=1) until validated on the GPU."""
+    stride, padding, dilation = _pair(stride), _pair(padding), _pair(dilation)
+    k, c, r, s_ = weight.shape
+    x2 = rowim2col(x, s_, stride[1], padding[1], dilation[1], dtype)
+    cd = x2.shape[1]
+    w2 = weight.permute(0, 2, 3, 1).reshape(k, r, s_ * c)
+    w2 = torch.nn.functional.pad(w2, (0, cd - s_ * c)).permute(0, 2, 1).unsqueeze(-1)
+    w2 = w2.contiguous(memory_format=_CL)                      # [K, Cd, R, 1], KRSC storage
+    return conv2d(x2, w2, bias, (stride[0], 1), (padding[0], 0), (dilation[0], 1), 1,
+                  wpack=pack_weight(w2, dtype), bn_stats=bn_stats)
+
+
 def conv2d_uses_tc(x_shape, w_shape, stride, padding, dilation, groups, dtype, direction) -> bool:
     """Which path a conv would take: True = tcgen05 implicit GEMM, False = CUDA cores."""
     code = _L.CNB_BF16 if dtype == torch.bfloat16 else _L.CNB_F32

@@ -43,6 +43,9 @@ def invalidate_packed_weights() -> None:
 # launch per layer.  Off by default until it has been through the GPU parity suite
 # (tools/check_batched_pack.py); CNB_BATCHED_PACK=1 turns it on.
 _BATCHED_PACK = os.environ.get("CNB_BATCHED_PACK", "0") == "1"
+# RGB stems through the row im2col (functional.conv2d_input_rows) instead of the full im2col matrix;
+# opt-in until validated on the GPU (tools/gpu_next_round.sh).
+_STEM_ROWS = os.environ.get("CNB_STEM_ROWS", "0") == "1"
 
 
 class PackGroup:
@@ -153,8 +156,9 @@ class Conv2d(nn.Conv2d):
             # cannot feed the tensor-core path (RGB: 16-byte TMA rows need C % 8 == 0) goes through
             # an explicit im2col + GEMM instead of the CUDA-core kernel.
             if self.compute_dtype == torch.bfloat16 and self.groups == 1 and x.shape[1] % 8:
-                return self._tag(F_.conv2d_input(x, self.weight, self.bias, self.stride, self.padding,
-                                                 self.dilation, self.compute_dtype, bn_stats=stats))
+                entry = F_.conv2d_input_rows if _STEM_ROWS else F_.conv2d_input
+                return self._tag(entry(x, self.weight, self.bias, self.stride, self.padding,
+                                       self.dilation, self.compute_dtype, bn_stats=stats))
             x = F_.to_nhwc(x, self.compute_dtype)
         wpack, wpack_t = self._packed(x.dtype)
         return self._tag(F_.conv2d(x, self.weight, self.bias, self.stride, self.padding,

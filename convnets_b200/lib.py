@@ -59,6 +59,7 @@ SIGNATURES = {
     "cnb_conv2d_fwd": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_conv2d_dgrad": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_conv2d_dgrad_add": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _SZ, _P]),
+    "cnb_rowim2col_nchw": (_I, [C.POINTER(ConvDesc), _P, _P, _I32, _P]),
     "cnb_pack_filter": (_I, [_P, _P, _P, _I32, _I32, _I32, _P]),
     "cnb_pack_filter_blocks": (_I64, [_I32, _I32, _I32]),
     "cnb_pack_filters": (_I, [_P, _I32, _I32, _P]),

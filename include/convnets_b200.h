@@ -202,6 +202,12 @@ int cnb_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t 
  * descriptor over C = K_dst "channels" (no data-grad: the network input needs none). */
 int cnb_im2col_nchw(const cnb_conv_desc* d, const float* src, void* dst, int32_t K_dst,
                     void* stream);
+/* Row im2col of the fp32 NCHW batch: dst[N][H][Q][C_dst], dst[n][h][q][s*C + c] =
+ * src[n][c][h][q*stride_w - pad_w + s*dil_w] (zeros outside and in columns >= S*C).  The R x S stem
+ * is then the R x 1 convolution with vertical stride stride_h over C_dst channels — a third of the
+ * bytes of the full im2col matrix.  Only the W-side fields of d are used. */
+int cnb_rowim2col_nchw(const cnb_conv_desc* d, const float* src, void* dst, int32_t C_dst,
+                       void* stream);
 /* fp32 master filter w[K][R*S][C] (the KRSC storage of a dense nn.Conv2d weight) -> bf16 operand
  * copies: w_bf16 in the same layout (forward / weight-grad) and, when wt_bf16 is not NULL,
  * [C][R*S][K] (data-grad).  One pass per optimiser step. */

@@ -2,8 +2,8 @@
 # First GPU visit of the next round: validate what was written after the previous round's GPU
 # minutes ran out, then measure it.  usage: bash tools/gpu_next_round.sh <tag>
 #   1. full-size property tests (tests/test_gpu_properties.py)
-#   2. cnb_conv2d_dgrad_add kernel check, batched filter pack check
-#   3. train-step parity + step-graph tests with CNB_FUSED_SKIP_GRAD=1 CNB_BATCHED_PACK=1
+#   2. cnb_conv2d_dgrad_add kernel check, batched filter pack check, row-im2col stem check
+#   3. train-step parity + step-graph tests with CNB_FUSED_SKIP_GRAD=1 CNB_BATCHED_PACK=1 CNB_STEM_ROWS=1
 #   4. ResNet-50 bench: default, each flag, both flags
 set -u
 TAG=${1:-n}
@@ -14,10 +14,12 @@ timeout 200 python tools/check_dgrad_add.py > gpurun_out/check_dgrad_add_$TAG.lo
 echo "dgrad_add rc=$?"; tail -8 gpurun_out/check_dgrad_add_$TAG.log
 CNB_BATCHED_PACK=1 timeout 200 python tools/check_batched_pack.py > gpurun_out/check_pack_$TAG.log 2>&1
 echo "batched pack rc=$?"; tail -6 gpurun_out/check_pack_$TAG.log
-CNB_FUSED_SKIP_GRAD=1 CNB_BATCHED_PACK=1 timeout 600 python -m pytest tests/test_gpu_models.py -q \
+timeout 200 python tools/check_stem_rows.py > gpurun_out/check_stem_$TAG.log 2>&1
+echo "stem rows rc=$?"; tail -8 gpurun_out/check_stem_$TAG.log
+CNB_FUSED_SKIP_GRAD=1 CNB_BATCHED_PACK=1 CNB_STEM_ROWS=1 timeout 600 python -m pytest tests/test_gpu_models.py -q \
   > gpurun_out/pytest_models_flags_$TAG.log 2>&1
 echo "models with flags rc=$?"; tail -3 gpurun_out/pytest_models_flags_$TAG.log
-for cfg in "" "CNB_FUSED_SKIP_GRAD=1" "CNB_BATCHED_PACK=1" "CNB_FUSED_SKIP_GRAD=1 CNB_BATCHED_PACK=1"; do
+for cfg in "" "CNB_FUSED_SKIP_GRAD=1" "CNB_BATCHED_PACK=1" "CNB_STEM_ROWS=1" "CNB_FUSED_SKIP_GRAD=1 CNB_BATCHED_PACK=1 CNB_STEM_ROWS=1"; do
   name=$(echo "$cfg" | tr ' =' '__'); name=${name:-default}
   env $cfg timeout 300 python bench.py --steps 10 --warmup 4 --no-cpu-baseline --no-e2e \
     > gpurun_out/bench_${TAG}_$name.log 2> gpurun_out/bench_${TAG}_$name.err
