@@ -154,9 +154,11 @@ struct FpropParams {
 //   grouped convolutions (p.grp_out > 0): the n-tile selects the input-channel slice it reads
 //           (a_c0) and the filter operand is the block-diagonal expansion built by
 //           expand_grouped_filter_k, see "grouped convolutions" below.
-template <int BLOCK_N, int STAGES, bool IM2COL, bool PLAIN>
+template <int BLOCK_N, int STAGES, bool IM2COL, int EPI>
 __global__ void __launch_bounds__(kPersistThreads, 1)
 conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
+  // EPI: 0 = bias / ReLU by flags, 1 = plain store, 2 = plain + addend (data-grad + skip gradient)
+  constexpr bool PLAIN = EPI != 0;   // rows past the end of the tensor stay zero (no bias added)
   constexpr int B_TILE_BYTES = BLOCK_N * TILE_K * 2;
   constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
   constexpr int OUT_BYTES = TILE_M * BLOCK_N * 2;
@@ -317,16 +319,14 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
         // skip-gradient accumulation: this lane's 32 columns of the addend row, 4 x 16 bytes, all
         // requested before the first use (rows past M / columns past Kout are never stored)
         uint4 add4[4];
-        if (!PLAIN) {
-          if (p.flags & kConvAccum) {
-            const int64_t grow = (int64_t)m0 + row;
+        if (EPI == 2) {
+          const int64_t grow = (int64_t)m0 + row;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-              const int col = n0 + c0 + j * 8;
-              add4[j] = (grow < p.M && col < p.Kout)
-                            ? __ldg(reinterpret_cast<const uint4*>(p.addend + grow * p.Kout + col))
-                            : make_uint4(0u, 0u, 0u, 0u);
-            }
+          for (int j = 0; j < 4; ++j) {
+            const int col = n0 + c0 + j * 8;
+            add4[j] = (grow < p.M && col < p.Kout)
+                          ? __ldg(reinterpret_cast<const uint4*>(p.addend + grow * p.Kout + col))
+                          : make_uint4(0u, 0u, 0u, 0u);
           }
         }
 #pragma unroll
@@ -336,12 +336,12 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
           for (int e = 0; e < 4; ++e) {
             float f0 = __uint_as_float(cur[j * 8 + e * 2 + 0]);
             float f1 = __uint_as_float(cur[j * 8 + e * 2 + 1]);
+            if (EPI == 2) {
+              const uint32_t a2 = e == 0 ? add4[j].x : (e == 1 ? add4[j].y : (e == 2 ? add4[j].z : add4[j].w));
+              f0 += __uint_as_float(a2 << 16);
+              f1 += __uint_as_float(a2 & 0xffff0000u);
+            }
             if (!PLAIN) {
-              if (p.flags & kConvAccum) {
-                const uint32_t a2 = e == 0 ? add4[j].x : (e == 1 ? add4[j].y : (e == 2 ? add4[j].z : add4[j].w));
-                f0 += __uint_as_float(a2 << 16);
-                f1 += __uint_as_float(a2 & 0xffff0000u);
-              }
               const int col = n0 + c0 + j * 8 + e * 2;
               if (p.flags & CNB_CONV_BIAS) {
                 f0 += (col < p.Kout) ? p.bias[col] : 0.f;
@@ -756,14 +756,14 @@ static int fprop_block_n(int Kout, bool grouped) {
   return Kout <= 64 ? 64 : (Kout <= 128 ? 128 : 256);
 }
 
-template <int BLOCK_N, int STAGES, bool IM2COL, bool PLAIN>
+template <int BLOCK_N, int STAGES, bool IM2COL, int EPI>
 static int launch_fprop_persist_inst(const FpropParams& prm, cudaStream_t st) {
   constexpr int STAGE_BYTES = A_TILE_BYTES + BLOCK_N * TILE_K * 2;
   constexpr size_t smem = (size_t)STAGES * STAGE_BYTES + (size_t)TILE_M * BLOCK_N * 2 +
                           (2 * STAGES + 4) * 8 + 16 + 1024;
   static_assert(smem <= 232448, "exceeds the 227 KB dynamic shared memory limit");
   static bool attr_done = false;
-  auto kern = conv_fprop_tc_persist_k<BLOCK_N, STAGES, IM2COL, PLAIN>;
+  auto kern = conv_fprop_tc_persist_k<BLOCK_N, STAGES, IM2COL, EPI>;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cudaFuncSetAttribute(fprop persistent): %s",
@@ -775,11 +775,11 @@ static int launch_fprop_persist_inst(const FpropParams& prm, cudaStream_t st) {
   return check_launch("conv_fprop_tc_persist");
 }
 
-template <bool IM2COL, bool PLAIN>
+template <bool IM2COL, int EPI>
 static int launch_fprop_bn(const FpropParams& prm, int BLOCK_N, cudaStream_t st) {
-  if (BLOCK_N == 64) return launch_fprop_persist_inst<64, 8, IM2COL, PLAIN>(prm, st);
-  if (BLOCK_N == 128) return launch_fprop_persist_inst<128, 5, IM2COL, PLAIN>(prm, st);
-  return launch_fprop_persist_inst<256, 3, IM2COL, PLAIN>(prm, st);
+  if (BLOCK_N == 64) return launch_fprop_persist_inst<64, 8, IM2COL, EPI>(prm, st);
+  if (BLOCK_N == 128) return launch_fprop_persist_inst<128, 5, IM2COL, EPI>(prm, st);
+  return launch_fprop_persist_inst<256, 3, IM2COL, EPI>(prm, st);
 }
 
 static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
@@ -834,12 +834,18 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
     prm.off_w[t] = L.off_w[t];
     prm.widx[t] = L.widx[t];
   }
-  const bool plain = prm.flags == 0;
-  if (L.tiled2d)
-    return plain ? launch_fprop_bn<false, true>(prm, BLOCK_N, st)
-                 : launch_fprop_bn<false, false>(prm, BLOCK_N, st);
-  return plain ? launch_fprop_bn<true, true>(prm, BLOCK_N, st)
-               : launch_fprop_bn<true, false>(prm, BLOCK_N, st);
+  // epilogue variant: 1 = plain store, 2 = plain + addend, 0 = bias / ReLU by flags
+  const int epi = prm.flags == 0 ? 1 : (prm.flags == kConvAccum ? 2 : 0);
+  CNB_REQUIRE(epi != 0 || !(prm.flags & kConvAccum), CNB_ERR_UNSUPPORTED,
+              "conv_tc: the accumulating epilogue does not combine with bias / ReLU");
+  if (L.tiled2d) {
+    if (epi == 1) return launch_fprop_bn<false, 1>(prm, BLOCK_N, st);
+    if (epi == 2) return launch_fprop_bn<false, 2>(prm, BLOCK_N, st);
+    return launch_fprop_bn<false, 0>(prm, BLOCK_N, st);
+  }
+  if (epi == 1) return launch_fprop_bn<true, 1>(prm, BLOCK_N, st);
+  if (epi == 2) return launch_fprop_bn<true, 2>(prm, BLOCK_N, st);
+  return launch_fprop_bn<true, 0>(prm, BLOCK_N, st);
 }
 
 // ==========================================================================================
