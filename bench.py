@@ -205,29 +205,48 @@ def conv_flops(d):
     return 2.0 * d["N"] * P * Q * d["K"] * (d["C"] // d["groups"]) * d["R"] * d["S"], P, Q
 
 
+def call_cost(name, a):
+    """Algorithmic (flops, bytes, family key) of one traced C-ABI call, SURVEY.md §8d."""
+    flops = byts = 0.0
+    key = name
+    if name.startswith("cnb_conv2d_") and a and isinstance(a[0], dict):
+        d = a[0]
+        flops, P, Q = conv_flops(d)
+        es = 2 if d["dtype"] == 1 else 4
+        # input pixels the layer actually needs (SURVEY.md Appendix A): a strided 1x1 conv only
+        # touches every stride-th pixel of its input
+        in_pix = d["N"] * d["H"] * d["W"]
+        if d["R"] == 1 and d["S"] == 1 and d["pad_h"] == 0 and d["pad_w"] == 0:
+            in_pix = d["N"] * P * Q
+        byts = (in_pix * d["C"] + d["N"] * P * Q * d["K"]) * es + \
+            d["K"] * (d["C"] // d["groups"]) * d["R"] * d["S"] * es
+        if name == "cnb_conv2d_dgrad_add":
+            byts += d["N"] * d["H"] * d["W"] * d["C"] * es   # the skip-gradient addend
+        if d["groups"] == d["C"] and d["groups"] > 1:
+            key = name + "(depthwise)"
+    elif name.startswith("cnb_bn_") and a and isinstance(a[0], dict):
+        # external tensors only (SURVEY.md §8d): fwd x -> y (+ residual in, + 1-bit ReLU mask
+        # out); bwd x, dy (+ mask in) -> dx (+ d_residual out).  The forward output y is read by
+        # backward only when no bit mask exists (fp32-IO, or C % 8 != 0).
+        d = a[0]
+        es = 2 if d["dtype"] == 1 else 4
+        n_t = {"cnb_bn_fwd_train": 2, "cnb_bn_fwd_eval": 2, "cnb_bn_bwd": 3}[name]
+        if d["flags"] & 2:
+            n_t += 1  # residual read (fwd) / residual-gradient write (bwd)
+        byts = n_t * d["M"] * d["C"] * es
+        if d["flags"] & 1 and name != "cnb_bn_fwd_eval":
+            if d["dtype"] == 1 and d["C"] % 8 == 0:
+                byts += d["M"] * d["C"] / 8          # bit mask written (fwd) / read (bwd)
+            elif name == "cnb_bn_bwd":
+                byts += d["M"] * d["C"] * es         # no mask: backward reads y
+    return flops, byts, key
+
+
 def summarise_trace(trace, pk):
     """Group the traced C-ABI calls into kernel families; algorithmic flops / bytes per SURVEY §8d."""
     fam = {}
     for name, a, ms in trace:
-        flops = byts = 0.0
-        key = name
-        if name.startswith("cnb_conv2d_") and a and isinstance(a[0], dict):
-            d = a[0]
-            flops, P, Q = conv_flops(d)
-            es = 2 if d["dtype"] == 1 else 4
-            byts = (d["N"] * d["H"] * d["W"] * d["C"] + d["N"] * P * Q * d["K"]) * es + \
-                d["K"] * (d["C"] // d["groups"]) * d["R"] * d["S"] * es
-            if d["groups"] == d["C"] and d["groups"] > 1:
-                key = name + "(depthwise)"
-        elif name.startswith("cnb_bn_") and a and isinstance(a[0], dict):
-            d = a[0]
-            es = 2 if d["dtype"] == 1 else 4
-            n_t = {"cnb_bn_fwd_train": 2, "cnb_bn_fwd_eval": 2, "cnb_bn_bwd": 3}[name]
-            if d["flags"] & 2:
-                n_t += 1  # residual read (fwd) / residual-gradient write (bwd)
-            if name == "cnb_bn_bwd" and d["flags"] & 1:
-                n_t += 1  # y read for the ReLU mask
-            byts = n_t * d["M"] * d["C"] * es
+        flops, byts, key = call_cost(name, a)
         f = fam.setdefault(key, {"calls": 0, "ms": 0.0, "flops": 0.0, "bytes": 0.0})
         f["calls"] += 1
         f["ms"] += ms

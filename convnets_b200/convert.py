@@ -53,10 +53,9 @@ _BODY_NAMES = ("res_block", "res_bottleneck", "se_bottleneck", "sk_bottleneck")
 
 
 # Identity-shortcut blocks: fold the skip gradient into the first conv's data-grad epilogue
-# (functional._Conv2dSkipFn) instead of letting autograd add the two gradients of the block input.
-# Opt-in (CNB_FUSED_SKIP_GRAD=1) until tools/check_dgrad_add.py and the train-step parity tests have
-# run with it on a GPU.
-_FUSED_SKIP = os.environ.get("CNB_FUSED_SKIP_GRAD", "0") == "1"
+# (functional._Conv2dSkipFn) instead of letting autograd add the two gradients of the block input
+# (tests/test_gpu_fused_paths.py::test_dgrad_add_epilogue).  CNB_FUSED_SKIP_GRAD=0 = autograd's add.
+_FUSED_SKIP = os.environ.get("CNB_FUSED_SKIP_GRAD", "1") == "1"
 
 
 def _can_fold_skip(blocks, x) -> bool:
@@ -71,7 +70,7 @@ def _can_fold_skip(blocks, x) -> bool:
 
 def _residual_forward_folded(self, blocks, x):
     first = list(blocks[0].children())
-    out, identity = first[0].forward_with_skip(x)
+    out, identity = first[0](x, with_skip=True)
     for m in first[1:]:
         out = m(out)
     last = blocks[-1]

@@ -223,8 +223,9 @@ class _Conv2dSkipFn(torch.autograd.Function):
     """conv2d that also hands its input on as a second output (the identity shortcut of a residual
     block, reference src/resnet.py:139-156,176-196).  Autograd then calls ONE backward with both
     gradients, and the data-grad epilogue adds the skip gradient (cnb_conv2d_dgrad_add) instead of
-    a separate element-wise add over the block input.  Used only when CNB_FUSED_SKIP_GRAD=1
-    (convert._residual_forward); everything but the data-grad is _Conv2dFn."""
+    a separate element-wise add over the block input.  Used by convert._residual_forward for
+    identity-shortcut blocks (CNB_FUSED_SKIP_GRAD=0 turns it off); everything but the data-grad is
+    _Conv2dFn."""
 
     @staticmethod
     def forward(ctx, x, weight, bias, wpack, stride, padding, dilation, groups, algo, want_stats,
@@ -384,7 +385,7 @@ def conv2d_input_rows(x, weight, bias=None, stride=1, padding=0, dilation=1, dty
     """The network's first convolution as an R x 1 convolution over the row-im2col of the batch
     (see rowim2col): same result as conv2d_input, a third of the bytes.  The filter is rearranged by
     differentiable torch ops ([K, C, R, S] -> [K, S*C (+pad), R, 1]), so the weight gradient flows
-    back through them.  Opt-in (layers: CNB_STEM_ROWS=1) until validated on the GPU."""
+    back through them.  The default stem path (layers: CNB_STEM_ROWS=0 selects conv2d_input)."""
     stride, padding, dilation = _pair(stride), _pair(padding), _pair(dilation)
     k, c, r, s_ = weight.shape
     x2 = rowim2col(x, s_, stride[1], padding[1], dilation[1], dtype)

@@ -118,6 +118,11 @@ class StepGraph:
         if y.data_ptr() != self.y.data_ptr():
             self.y.copy_(y, non_blocking=True)
         self.graph.replay()
+        # The replayed Adam step changed every weight without running any Python: neither the
+        # optimizer post-step hook nor the tensor version counter moved.  Advance the weight epoch so
+        # that the next EAGER forward (valid_model, a ragged last batch) re-packs its bf16 operand
+        # copies instead of reusing the ones this replay built from the pre-step weights.
+        L._bump_weight_epoch()
         return self.loss, self.logits
 
 

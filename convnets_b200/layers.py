@@ -40,12 +40,13 @@ def invalidate_packed_weights() -> None:
 
 
 # One launch re-packs every tensor-core filter of a model (cnb_pack_filters) instead of one KB-sized
-# launch per layer.  Off by default until it has been through the GPU parity suite
-# (tools/check_batched_pack.py); CNB_BATCHED_PACK=1 turns it on.
-_BATCHED_PACK = os.environ.get("CNB_BATCHED_PACK", "0") == "1"
-# RGB stems through the row im2col (functional.conv2d_input_rows) instead of the full im2col matrix;
-# opt-in until validated on the GPU (tools/gpu_next_round.sh).
-_STEM_ROWS = os.environ.get("CNB_STEM_ROWS", "0") == "1"
+# launch per layer (bit-identical to the per-layer cnb_pack_filter:
+# tests/test_gpu_fused_paths.py::test_batched_pack_equals_per_layer_pack).  CNB_BATCHED_PACK=0 = per layer.
+_BATCHED_PACK = os.environ.get("CNB_BATCHED_PACK", "1") == "1"
+# RGB stems through the row im2col (functional.conv2d_input_rows) instead of the full im2col matrix
+# (a third of the bytes; tests/test_gpu_fused_paths.py::test_rgb_stem_vs_oracle holds both to the
+# float64 oracle).  CNB_STEM_ROWS=0 = full im2col matrix.
+_STEM_ROWS = os.environ.get("CNB_STEM_ROWS", "1") == "1"
 
 
 class PackGroup:
@@ -137,20 +138,19 @@ class Conv2d(nn.Conv2d):
             self.__dict__["_cnb_pack"] = cache
         return cache[1]
 
-    def forward_with_skip(self, x: torch.Tensor):
-        """(conv(x), alias of x for the identity shortcut): the residual blocks' first conv when
-        the skip gradient is folded into its data-grad (functional._Conv2dSkipFn)."""
-        stats = self.emit_bn_stats and self.training
-        wpack, wpack_t = self._packed(x.dtype)
-        y, part, xs = F_.conv2d_with_skip(x, self.weight, self.bias, self.stride, self.padding,
-                                          self.dilation, self.groups, wpack=wpack, algo=self.algo,
-                                          bn_stats=stats, wpack_t=wpack_t)
-        return self._tag((y, part)), xs
-
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, with_skip: bool = False):
+        """`with_skip`: also return an alias of x for the identity shortcut of a residual block —
+        (conv(x), x_skip) — so that the skip gradient is folded into this layer's data-grad
+        (functional._Conv2dSkipFn)."""
         if self.padding_mode != "zeros" or isinstance(self.padding, str):
             raise NotImplementedError("convnets_b200.Conv2d supports integer zero padding only")
         stats = self.emit_bn_stats and self.training
+        if with_skip:
+            wpack, wpack_t = self._packed(x.dtype)
+            y, part, xs = F_.conv2d_with_skip(x, self.weight, self.bias, self.stride, self.padding,
+                                              self.dilation, self.groups, wpack=wpack, algo=self.algo,
+                                              bn_stats=stats, wpack_t=wpack_t)
+            return self._tag((y, part)), xs
         if self.cast_input and self.compute_dtype is not None and not x.requires_grad:
             # network entry: fp32 NCHW batch -> compute dtype NHWC.  A stem whose channel count
             # cannot feed the tensor-core path (RGB: 16-byte TMA rows need C % 8 == 0) goes through

@@ -40,7 +40,12 @@ def diag(name, got, ref):
 
 
 def main():
-    case = json.loads(sys.argv[1])
+    cases = json.loads(sys.argv[1])
+    for case in (cases if isinstance(cases, list) else [cases]):
+        probe(case)
+
+
+def probe(case):
     torch.manual_seed(case.get("seed", 0))
     dev = torch.device("cuda:0")
     dtype = torch.bfloat16 if case.get("dtype", "bf16") == "bf16" else torch.float32
@@ -71,7 +76,7 @@ def main():
     res["wgrad"] = diag("wgrad", wd.grad, dw_ref)
     if b is not None:
         res["bgrad"] = diag("bgrad", bd.grad, db_ref)
-    print("PROBE_RESULT " + json.dumps(res))
+    print("PROBE_RESULT " + json.dumps(res), flush=True)
 
 
 if __name__ == "__main__":

@@ -143,4 +143,4 @@ def test_batched_pack_table_layout(lib):
         assert wt.shape == (c, r * s, k)
         first += h.cnb_pack_filter_blocks(k, r * s, c)
     assert group.n_blocks == first
-    assert L._BATCHED_PACK is False                # stays opt-in until validated on the GPU
+    assert L._BATCHED_PACK is True                 # the default since tests/test_gpu_fused_paths.py

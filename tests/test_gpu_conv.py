@@ -55,6 +55,19 @@ TC_CASES = [
     c(2, 64, 12, 12, 128, 3, pad=1, groups=2, bias=True),        # Cg 32 -> Kg 64, bias
 ]
 
+# the 22 tensor-core signatures of ResNet-50 @224 at their real H x W (batch 2;
+# the 3 -> 64 7x7 stem is covered by tests/test_gpu_fused_paths.py::test_rgb_stem_vs_oracle at 224)
+APPENDIX_A = [
+    c(2, 64, 56, 56, 64, 1), c(2, 64, 56, 56, 64, 3, pad=1), c(2, 64, 56, 56, 256, 1),
+    c(2, 256, 56, 56, 64, 1), c(2, 256, 56, 56, 128, 1), c(2, 128, 56, 56, 128, 3, pad=1, stride=2),
+    c(2, 128, 28, 28, 512, 1), c(2, 256, 56, 56, 512, 1, stride=2), c(2, 512, 28, 28, 128, 1),
+    c(2, 128, 28, 28, 128, 3, pad=1), c(2, 512, 28, 28, 256, 1), c(2, 256, 28, 28, 256, 3, pad=1, stride=2),
+    c(2, 256, 14, 14, 1024, 1), c(2, 512, 28, 28, 1024, 1, stride=2), c(2, 1024, 14, 14, 256, 1),
+    c(2, 256, 14, 14, 256, 3, pad=1), c(2, 1024, 14, 14, 512, 1), c(2, 512, 14, 14, 512, 3, pad=1, stride=2),
+    c(2, 512, 7, 7, 2048, 1), c(2, 1024, 14, 14, 2048, 1, stride=2), c(2, 2048, 7, 7, 512, 1),
+    c(2, 512, 7, 7, 512, 3, pad=1),
+]
+
 # CUDA-core cases: fp32-IO mode, grouped, tiny channel counts, stems
 SIMT_CASES = [
     c(2, 3, 17, 17, 24, 3, pad=1, stride=2, dtype="f32"),              # RGB stem
@@ -93,6 +106,17 @@ def run_probe(case, timeout=180):
     return json.loads(line[-1][len("PROBE_RESULT "):])
 
 
+def run_probe_many(cases, timeout=600):
+    """All `cases` in ONE subprocess (one `import torch`), one PROBE_RESULT line per case."""
+    p = subprocess.run([sys.executable, PROBE, json.dumps(cases)], capture_output=True, text=True,
+                       timeout=timeout, env=dict(os.environ))
+    lines = [l for l in p.stdout.splitlines() if l.startswith("PROBE_RESULT ")]
+    if p.returncode != 0 or len(lines) != len(cases):
+        pytest.fail(f"probe failed rc={p.returncode} ({len(lines)}/{len(cases)} results)\nstdout:\n"
+                    f"{p.stdout[-2000:]}\nstderr:\n{p.stderr[-3000:]}")
+    return [json.loads(l[len("PROBE_RESULT "):]) for l in lines]
+
+
 def check(res, tol):
     msgs = []
     for k in ("fwd", "dgrad", "wgrad", "bgrad"):
@@ -110,6 +134,20 @@ def test_conv_tensor_core(case):
     res = run_probe(case)
     assert res["uses_tc"] == [True, True, True]
     check(res, 1e-2)
+
+
+@pytest.mark.gpu
+def test_conv_resnet50_signatures_at_real_size():
+    """every tensor-core signature of ResNet-50 @224 at its real H x W,
+    forward / data-grad / weight-grad against the float64 oracle (rel-L2 <= 1e-2)."""
+    results = run_probe_many([dict(cs, dtype="bf16", algo="tc") for cs in APPENDIX_A])
+    worst = {}
+    for res in results:
+        assert res["uses_tc"] == [True, True, True]
+        check(res, 1e-2)
+        for k in ("fwd", "dgrad", "wgrad"):
+            worst[k] = max(worst.get(k, 0.0), res[k]["rel_l2"])
+    print("Appendix A worst rel-L2:", {k: f"{v:.2e}" for k, v in worst.items()})
 
 
 @pytest.mark.gpu

@@ -58,7 +58,11 @@ def test_batch_norm_train(dtype, shape, relu, res):
     assert y.shape == x.shape and y.is_contiguous(memory_format=CL)
     assert O.rel_l2(y, y_ref) <= tol
     assert O.rel_l2(rmd, rm_ref) <= 1e-5 and O.rel_l2(rvd, rv_ref) <= 1e-4
-    assert O.rel_l2(xd.grad, dx_ref) <= (tol if dtype == torch.float32 else 2e-2)
+    # bf16: the only error source is the bf16 rounding of the stored dx (measured floor: the fp64
+    # result rounded to bf16, ~1.7e-3); the bound is north_star's 1e-2 or twice that floor
+    dx_floor = O.rel_l2(dx_ref.to(dtype), dx_ref)
+    e_dx = O.rel_l2(xd.grad, dx_ref)
+    assert e_dx <= max(tol, 2 * dx_floor), (e_dx, dx_floor)
     assert O.rel_l2(gd.grad, dg_ref) <= tol and O.rel_l2(bd.grad, db_ref) <= tol
     if res:
         assert O.rel_l2(rd.grad, dr_ref) <= tol

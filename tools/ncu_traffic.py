@@ -15,6 +15,9 @@ def main(path, family, kps, cps, out):
         if r["Metric Name"].startswith("dram__bytes"):
             v *= {"byte": 1, "kbyte": 1e3, "mbyte": 1e6, "gbyte": 1e9}[u]
         per.setdefault(int(r["ID"]), {})[r["Metric Name"]] = v
+    if len(per) < kps:
+        sys.exit(f"ncu_traffic: {path} holds {len(per)} launches with dram__bytes metrics, expected >= "
+                 f"{kps} (empty or truncated capture — re-run ncu; refusing to write {out})")
     ids = sorted(per)[-kps:]
     rd = sum(per[i].get("dram__bytes_read.sum", 0.0) for i in ids)
     wr = sum(per[i].get("dram__bytes_write.sum", 0.0) for i in ids)
