@@ -3,4 +3,4 @@ architecture zoo.  See DESIGN.md."""
 __version__ = "0.1.0"
 
 from .convert import convert  # noqa: E402,F401
-from .graph import StepGraph, enable_step_graph  # noqa: E402,F401
+from .graph import EvalGraph, StepGraph, enable_eval_graph, enable_step_graph  # noqa: E402,F401

@@ -173,6 +173,9 @@ def _fuse_bn_relu(seq: nn.Sequential) -> None:
         ma, mb = seq._modules[a], seq._modules[b]
         if isinstance(ma, L.Conv2d) and isinstance(mb, L.BatchNorm2d):
             ma.emit_bn_stats = True  # conv -> bn: statistics come out of the conv epilogue
+            # inference: the conv folds this BatchNorm into its filter (not registered as a child:
+            # the module tree and the state_dict keys must not change)
+            ma.__dict__["_cnb_bn"] = mb
         if isinstance(ma, L.BatchNorm2d) and type(mb) in (nn.ReLU, L.ReLU):
             ma.fuse_relu = True
             seq._modules[b] = L.Identity()

@@ -9,6 +9,8 @@
 //   apply   : y = [relu](x*scale + shift [+ residual])
 //   bwd     : reduce (sum dy', sum dy'*(x-mean)) + last-CTA merge (dgamma, dbeta, coefficients) -> dx
 // The merges sum in a fixed order (no floating-point atomics): results are bit-reproducible.
+#include <string.h>
+
 #include "common.cuh"
 
 namespace cnb {
@@ -83,15 +85,11 @@ struct BnBwdFin {
   float* dgamma; float* dbeta; float* c1; float* c2; float* c3;
 };
 
-// Block-level tail shared by the two reduction kernels: tree-reduce the per-thread (s, q) over the
-// row lanes, store the CTA's partial, and let the last-arriving CTA of this channel block sum all
-// partials in split order (fixed order => bit-reproducible) in fp64.  Returns true in the threads
-// that own a finished channel (S, Q valid).
+// Block-level tail shared by the reduction kernels, part 1: tree-reduce the per-thread (s, q) over
+// the row lanes and store the CTA's partial row ([split][2][C] floats).
 template <int V>
-__device__ __forceinline__ bool bn_block_merge(float (&s)[V], float (&q)[V], float* red,
-                                               float* __restrict__ part, int C, int splits,
-                                               int* __restrict__ counter, int& c_out, double& S,
-                                               double& Q) {
+__device__ __forceinline__ void bn_block_partial(float (&s)[V], float (&q)[V], float* red,
+                                                 float* __restrict__ part, int C) {
   const int cx = blockDim.x, ry = blockDim.y;
   const int W = cx * V;
   const int t = threadIdx.y * cx + threadIdx.x;
@@ -118,17 +116,18 @@ __device__ __forceinline__ bool bn_block_merge(float (&s)[V], float (&q)[V], flo
     if (cbase + col < C)
       part[((int64_t)blockIdx.y * 2 + which) * C + cbase + col] = red[which * W + col];
   }
-  __threadfence();
-  __syncthreads();
-  __shared__ int s_last;
-  if (t == 0) {
-    int prev = atomicAdd(counter + blockIdx.x, 1);
-    s_last = (prev == splits - 1);
-    if (s_last) counter[blockIdx.x] = 0;  // leave the slot clean for the next call
-  }
-  __syncthreads();
-  if (!s_last) return false;
-  __threadfence();
+}
+
+// Part 2: sum the partial rows of this CTA's channel block in split order (fixed order => bit-
+// reproducible, and identical in every CTA that runs it) in fp64.  Returns true in the threads that
+// own a finished channel (S, Q valid).  `red` is re-used as 256 x 2 doubles.
+template <int V>
+__device__ __forceinline__ bool bn_merge_partials(float* red, const float* __restrict__ part, int C,
+                                                  int splits, int& c_out, double& S, double& Q) {
+  const int cx = blockDim.x;
+  const int W = cx * V;
+  const int t = threadIdx.y * cx + threadIdx.x;
+  const int cbase = blockIdx.x * W;
   // 256 threads = (256 / W) split-lanes x W channels
   double* dred = reinterpret_cast<double*>(red);
   const int lanes = kBnThreads / W;
@@ -164,6 +163,28 @@ __device__ __forceinline__ bool bn_block_merge(float (&s)[V], float (&q)[V], flo
   }
   c_out = c;
   return true;
+}
+
+// Two-kernel form: the last-arriving CTA of a channel block merges (everyone else leaves).
+template <int V>
+__device__ __forceinline__ bool bn_block_merge(float (&s)[V], float (&q)[V], float* red,
+                                               float* __restrict__ part, int C, int splits,
+                                               int* __restrict__ counter, int& c_out, double& S,
+                                               double& Q) {
+  bn_block_partial<V>(s, q, red, part, C);
+  const int t = threadIdx.y * blockDim.x + threadIdx.x;
+  __threadfence();
+  __syncthreads();
+  __shared__ int s_last;
+  if (t == 0) {
+    int prev = atomicAdd(counter + blockIdx.x, 1);
+    s_last = (prev == splits - 1);
+    if (s_last) counter[blockIdx.x] = 0;  // leave the slot clean for the next call
+  }
+  __syncthreads();
+  if (!s_last) return false;
+  __threadfence();
+  return bn_merge_partials<V>(red, part, C, splits, c_out, S, Q);
 }
 
 // Per-channel epilogue of the forward statistics: S = sum(x - K), Q = sum((x - K)^2).
@@ -603,6 +624,268 @@ bn_bwd_dx_k(const T* __restrict__ x, const T* __restrict__ y, const uint8_t* __r
 
 constexpr int kReduceWaves = 4, kStreamWaves = 8, kReduceCx = 8;
 
+// ---------------------------------------------------------------- backward, single DRAM read
+// One kernel for tensors whose x + dy fit the 126 MB L2 (ResNet-50 at batch 256: the eleven
+// C = 256 @ 14x14 and five C = 512 @ 7x7 layers, which the two-kernel form runs at 1.1 - 1.9 TB/s
+// because launch + last-CTA-merge latency is a third of their 35 - 40 us).  Every CTA reduces its
+// rows (phase 1, exactly bn_bwd_reduce_k), meets the other CTAs OF ITS CHANNEL BLOCK at a counter
+// (no grid-wide barrier: CTAs of different channel blocks never wait for each other), sums the
+// partial rows of the channel block itself — every CTA in the same fixed order, so all of them hold
+// bit-identical coefficients — and walks its rows again for dx (phase 2): the second read of x, dy
+// and the mask is served by L2.  Launched cooperatively (all CTAs co-resident by construction).
+// counter layout: [0, kCountersPerSlot/2) arrivals, [kCountersPerSlot/2, ..) departures.
+template <typename T, int V, int RELU, bool DRES, int U, int MINB>
+__global__ void __launch_bounds__(kBnThreads, MINB)
+bn_bwd_fused_k(const T* __restrict__ x, const T* __restrict__ y, const uint8_t* __restrict__ mask,
+               const T* __restrict__ dy, const float* __restrict__ mean, float* __restrict__ part,
+               T* __restrict__ dx, T* __restrict__ dres, int64_t M, int C, int64_t rows_per_split,
+               int splits, int* __restrict__ counter, BnBwdFin f) {
+  extern __shared__ __align__(16) float red[];
+  __shared__ float coef[3][kBnThreads];   // c1, c2, c3 of this CTA's channels (W <= 256)
+  const int cv = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c0 = cv * V;
+  const int t = threadIdx.y * blockDim.x + threadIdx.x;
+  const int W = blockDim.x * V;
+  const int64_t r0 = blockIdx.y * rows_per_split;
+  int64_t r1 = r0 + rows_per_split;
+  if (r1 > M) r1 = M;
+  constexpr bool bits = RELU == 2 && V == 8;
+  const int ry = blockDim.y;
+  const int64_t stride = (int64_t)ry * C, mstride = stride >> 3;
+  const int64_t e0 = (r0 + threadIdx.y) * C + c0;
+  float s[V], q[V], mu[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) s[j] = q[j] = mu[j] = 0.f;
+  // ---- phase 1: partial sums of dy' and dy' * (x - mean) over this CTA's rows
+  if (c0 < C) {
+#pragma unroll
+    for (int j = 0; j < V; ++j) mu[j] = mean[c0 + j];
+    int64_t r = r0 + threadIdx.y;
+    const T* xp = x + e0;
+    const T* gp = dy + e0;
+    const T* yp = (RELU && !bits) ? y + e0 : nullptr;
+    const uint8_t* mp = bits ? mask + (e0 >> 3) : nullptr;
+    auto accum = [&](const Pack<T, V>& a, const Pack<T, V>& g, uint32_t mb, const Pack<T, V>& o) {
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        float gf = to_f(g.v[j]);
+        if (RELU) {
+          const bool pos = bits ? ((mb >> j) & 1u) : (to_f(o.v[j]) > 0.f);
+          if (!pos) gf = 0.f;
+        }
+        s[j] += gf;
+        q[j] = fmaf(gf, to_f(a.v[j]) - mu[j], q[j]);
+      }
+    };
+    for (; r + (int64_t)(U - 1) * ry < r1; r += (int64_t)U * ry) {
+      Pack<T, V> a[U], g[U], o[U];
+      uint32_t mb[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        a[u] = ld_pack<T, V>(xp + u * stride);
+        g[u] = ld_pack<T, V>(gp + u * stride);
+        mb[u] = 0;
+        if (RELU) {
+          if (bits) mb[u] = mp[u * mstride];
+          else o[u] = ld_pack<T, V>(yp + u * stride);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) accum(a[u], g[u], mb[u], o[u]);
+      xp += U * stride;
+      gp += U * stride;
+      if (RELU) {
+        if (bits) mp += U * mstride;
+        else yp += U * stride;
+      }
+    }
+    for (; r < r1; r += ry) {
+      Pack<T, V> a = ld_pack<T, V>(xp), g = ld_pack<T, V>(gp), o;
+      uint32_t mb = 0;
+      if (RELU) {
+        if (bits) mb = *mp;
+        else o = ld_pack<T, V>(yp);
+      }
+      accum(a, g, mb, o);
+      xp += stride;
+      gp += stride;
+      if (RELU) {
+        if (bits) mp += mstride;
+        else yp += stride;
+      }
+    }
+  }
+  bn_block_partial<V>(s, q, red, part, C);
+  // ---- meet the other CTAs of this channel block
+  __threadfence();
+  __syncthreads();
+  if (t == 0) {
+    atomicAdd(counter + blockIdx.x, 1);
+    int seen;
+    do {
+      asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(counter + blockIdx.x) : "memory");
+      if (seen < splits) __nanosleep(32);
+    } while (seen < splits);
+  }
+  __syncthreads();
+  __threadfence();
+  int c;
+  double S, Q;
+  if (bn_merge_partials<V>(red, part, C, splits, c, S, Q)) {
+    const float rs = f.rstd[c];
+    const float g = f.gamma ? f.gamma[c] : 1.f;
+    const int col = c - blockIdx.x * W;
+    coef[0][col] = g * rs;
+    coef[1][col] = (float)(S / (double)M);
+    coef[2][col] = (float)(Q * (double)rs * (double)rs / (double)M);
+    if (blockIdx.y == 0) {
+      if (f.dbeta) f.dbeta[c] = (float)S;
+      if (f.dgamma) f.dgamma[c] = (float)(Q * (double)rs);
+    }
+  }
+  __syncthreads();
+  if (t == 0) {   // the last CTA to leave the barrier hands the counters back clean
+    const int half = kCountersPerSlot / 2;
+    const int prev = atomicAdd(counter + half + blockIdx.x, 1);
+    if (prev == splits - 1) {
+      counter[blockIdx.x] = 0;
+      counter[half + blockIdx.x] = 0;
+    }
+  }
+  if (c0 >= C) return;
+  // ---- phase 2: dx = c1 * (dy' - c2 - (x - mean) * c3) over the same rows (L2-resident by now)
+  float k1[V], k2[V], k3[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    k1[j] = coef[0][threadIdx.x * V + j];
+    k2[j] = coef[1][threadIdx.x * V + j];
+    k3[j] = coef[2][threadIdx.x * V + j];
+  }
+  {
+    int64_t r = r0 + threadIdx.y;
+    const T* xp = x + e0;
+    const T* gp = dy + e0;
+    const T* yp = (RELU && !bits) ? y + e0 : nullptr;
+    const uint8_t* mp = bits ? mask + (e0 >> 3) : nullptr;
+    T* op = dx + e0;
+    T* dp = DRES ? dres + e0 : nullptr;
+    auto emit = [&](const Pack<T, V>& a, const Pack<T, V>& g, uint32_t mb, const Pack<T, V>& m, T* o_ptr,
+                    T* d_ptr) {
+      Pack<T, V> o, dr;
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        float gf = to_f(g.v[j]);
+        if (RELU) {
+          const bool pos = bits ? ((mb >> j) & 1u) : (to_f(m.v[j]) > 0.f);
+          if (!pos) gf = 0.f;
+        }
+        if (DRES) dr.v[j] = from_f<T>(gf);
+        o.v[j] = from_f<T>(k1[j] * (gf - k2[j] - (to_f(a.v[j]) - mu[j]) * k3[j]));
+      }
+      st_pack<T, V>(o_ptr, o);
+      if (DRES) st_pack<T, V>(d_ptr, dr);
+    };
+    for (; r + (int64_t)(U - 1) * ry < r1; r += (int64_t)U * ry) {
+      Pack<T, V> a[U], g[U], m[U];
+      uint32_t mb[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        a[u] = ld_pack<T, V>(xp + u * stride);
+        g[u] = ld_pack<T, V>(gp + u * stride);
+        mb[u] = 0;
+        if (RELU) {
+          if (bits) mb[u] = mp[u * mstride];
+          else m[u] = ld_pack<T, V>(yp + u * stride);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) emit(a[u], g[u], mb[u], m[u], op + u * stride, DRES ? dp + u * stride : nullptr);
+      xp += U * stride;
+      gp += U * stride;
+      op += U * stride;
+      if (DRES) dp += U * stride;
+      if (RELU) {
+        if (bits) mp += U * mstride;
+        else yp += U * stride;
+      }
+    }
+    for (; r < r1; r += ry) {
+      Pack<T, V> a = ld_pack<T, V>(xp), g = ld_pack<T, V>(gp), m;
+      uint32_t mb = 0;
+      if (RELU) {
+        if (bits) mb = *mp;
+        else m = ld_pack<T, V>(yp);
+      }
+      emit(a, g, mb, m, op, dp);
+      xp += stride;
+      gp += stride;
+      op += stride;
+      if (DRES) dp += stride;
+      if (RELU) {
+        if (bits) mp += mstride;
+        else yp += stride;
+      }
+    }
+  }
+}
+
+// Largest x + dy footprint (bytes) the single-read backward takes; 0 disables it.
+// CNB_BN_BWD_FUSED_MB overrides (sweep: tools/gpu_bn_fused.sh).
+static int64_t bn_bwd_fused_limit() {
+  const char* e = getenv("CNB_BN_BWD_FUSED_MB");   // read per call: the tests switch paths in-process
+  return (int64_t)(e ? atoll(e) : 64) << 20;
+}
+
+template <int RELU, bool DRES>
+static int launch_bn_bwd_fused(const bf16* x, const bf16* y, const uint8_t* mask, const bf16* dy,
+                               const float* mean, float* part, bf16* dx, bf16* dres, int64_t M, int C,
+                               const BnBwdFin& fin, bool* taken, cudaStream_t st) {
+  constexpr int U = 2, MINB = 3;
+  auto kern = bn_bwd_fused_k<bf16, 8, RELU, DRES, U, MINB>;
+  static int per_sm = -1;
+  const int cvs = C / 8;
+  int cx = 1;
+  while (cx * 2 <= cvs && cx * 2 <= kReduceCx) cx *= 2;
+  const int ry = kBnThreads / cx;
+  size_t dyn = (size_t)ry * 2 * cx * 8 * sizeof(float);   // [row lanes][2][channels of the CTA] floats
+  if (dyn < 4096) dyn = 4096;                              // the merge re-uses it for 256 x 2 doubles
+  if (per_sm < 0) {
+    int n = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kern, kBnThreads, 16384);
+    CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cnb_bn_bwd: occupancy query failed: %s", cudaGetErrorString(e));
+    per_sm = n < MINB ? n : MINB;
+  }
+  *taken = false;
+  if (per_sm < 1) return CNB_OK;
+  const int cblocks = (int)ceil_div(cvs, cx);
+  if (cblocks > kCountersPerSlot / 2) return CNB_OK;
+  int64_t splits = (int64_t)sm_count() * per_sm / cblocks;
+  const int64_t max_splits = ceil_div(M, (int64_t)ry * U);
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) return CNB_OK;   // more channel blocks than co-resident CTAs: two-kernel form
+  const int64_t rows_per_split = ceil_div(M, splits);
+  const int nsplit = (int)ceil_div(M, rows_per_split);
+  int* counter = bn_counters(cblocks);
+  CNB_REQUIRE(counter, CNB_ERR_CUDA, "cnb_bn_bwd: cannot allocate the arrival counters");
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(cblocks, nsplit);
+  cfg.blockDim = dim3(cx, ry);
+  cfg.dynamicSmemBytes = dyn;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeCooperative;
+  attr[0].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, x, y, mask, dy, mean, part, dx, dres, M, C,
+                                     rows_per_split, nsplit, counter, fin);
+  CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cnb_bn_bwd(fused): %s", cudaGetErrorString(e));
+  *taken = true;
+  return check_launch("bn_bwd_fused");
+}
+
+
 // Loop shape of the bf16 backward kernels: (rows in flight per thread, resident CTAs per SM).
 // 0: (2, 2)  1: (2, 3)  2: (4, 2)  3: (3, 2)  4: (4, 3).  CNB_BN_BWD_VARIANT overrides the default.
 // Loop shape of the bf16 apply kernel: 0: (4, 2)  1: (2, 3)  2: (4, 3)  3: (2, 4).
@@ -834,8 +1117,24 @@ int cnb_bn_bwd(const cnb_bn_desc* d, const void* x, const void* y, const void* r
   // grids are whole multiples of the CTAs that are resident at once: 2 per SM with the (.., 2)
   // loop shapes, 3 per SM with the (.., 3) ones (80 registers)
   const bool three = hot && (variant == 1 || variant == 4);
-  BnGeom g = bn_geom(M, C, v, three ? 3 : kReduceWaves, kReduceCx);
   float* part = (float*)workspace;
+  if (hot && (int64_t)2 * M * C * 2 <= bn_bwd_fused_limit()) {
+    // x + dy fit L2: one cooperative kernel, one DRAM read of every operand
+    bool taken = false;
+    BnBwdFin fin{gamma, save_rstd, dgamma, dbeta, nullptr, nullptr, nullptr};
+#define FUSED(R, D)                                                                                   \
+  CNB_TRY((launch_bn_bwd_fused<R, D>((const bf16*)x, (const bf16*)y, mask, (const bf16*)dy, save_mean, \
+                                     part, (bf16*)dx, (bf16*)d_residual, M, C, fin, &taken, st)))
+    if (mode == 2 && d_residual) FUSED(2, true);
+    else if (mode == 2) FUSED(2, false);
+    else if (mode == 1 && d_residual) FUSED(1, true);
+    else if (mode == 1) FUSED(1, false);
+    else if (d_residual) FUSED(0, true);
+    else FUSED(0, false);
+#undef FUSED
+    if (taken) return CNB_OK;
+  }
+  BnGeom g = bn_geom(M, C, v, three ? 3 : kReduceWaves, kReduceCx);
   float* c1 = part + (size_t)2 * C * g.splits;
   float* c2 = c1 + C;
   float* c3 = c2 + C;

@@ -149,13 +149,13 @@ def _conv_desc(x_shape, w_shape, stride, padding, dilation, groups, dtype_code, 
 class _Conv2dFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, wpack, stride, padding, dilation, groups, algo, want_stats,
-                wpack_t=None):
+                wpack_t=None, relu=False):
         _cuda(x, wpack, bias)
         lib = _L.load()
         x = _nhwc(x)
         if x.dtype != wpack.dtype:
             raise TypeError(f"conv2d: activation dtype {x.dtype} != packed weight dtype {wpack.dtype}")
-        flags = _L.CNB_CONV_BIAS if bias is not None else 0
+        flags = (_L.CNB_CONV_BIAS if bias is not None else 0) | (_L.CNB_CONV_RELU if relu else 0)
         d = _conv_desc(x.shape, wpack.shape, stride, padding, dilation, groups, _dt(x), flags, algo)
         P, Q = C.c_int32(), C.c_int32()
         _L.check(lib.cnb_conv2d_out_dims(C.byref(d), C.byref(P), C.byref(Q)), "cnb_conv2d_out_dims")
@@ -171,12 +171,17 @@ class _Conv2dFn(torch.autograd.Function):
         ctx.save_for_backward(x, wpack, wpack_t)
         ctx.desc = d
         ctx.has_bias = bias is not None
+        ctx.relu = bool(relu)
         ctx.wshape = tuple(weight.shape)
         ctx.mark_non_differentiable(part)
         return y, part
 
     @staticmethod
     def backward(ctx, dy, _dpart=None):
+        if ctx.relu:
+            raise NotImplementedError(
+                "conv2d(relu=True) is the inference epilogue (BatchNorm folded into the filter, "
+                "reference valid_model runs under no_grad, src/basemodel.py:304); no backward")
         lib = _L.load()
         x, wpack, wpack_t = ctx.saved_tensors
         d = ctx.desc
@@ -201,19 +206,21 @@ class _Conv2dFn(torch.autograd.Function):
                                           ws.numel(), _stream()), "cnb_conv2d_wgrad")
             if tuple(dw.shape) != ctx.wshape:  # zero-padded input channels (RGB stem)
                 dw = dw[:, :ctx.wshape[1]].contiguous(memory_format=_CL)
-        return dx, dw, db, None, None, None, None, None, None, None, None
+        return dx, dw, db, None, None, None, None, None, None, None, None, None
 
 
 def conv2d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, wpack=None,
-           algo=_L.CNB_ALGO_AUTO, bn_stats=False, wpack_t=None):
+           algo=_L.CNB_ALGO_AUTO, bn_stats=False, wpack_t=None, relu=False):
     """Drop-in for F.conv2d as reached from nn.Conv2d (reference src/basemodel.py:974,992).
     `weight` is the fp32 master parameter; `wpack` an optional pre-packed operand copy.
     With `bn_stats` returns (y, partials): the per-tile BatchNorm partial sums emitted by the
-    forward epilogue (None when this conv runs on a path that cannot produce them)."""
+    forward epilogue (None when this conv runs on a path that cannot produce them).  `relu`: fused
+    ReLU epilogue, inference only (the BatchNorm-folded eval path, layers.Conv2d)."""
     if wpack is None:
         wpack = pack_weight(weight, x.dtype)
     y, part = _Conv2dFn.apply(x, weight, bias, wpack, _pair(stride), _pair(padding),
-                              _pair(dilation), int(groups), int(algo), bool(bn_stats), wpack_t)
+                              _pair(dilation), int(groups), int(algo), bool(bn_stats), wpack_t,
+                              bool(relu))
     if bn_stats:
         return y, (part if part.shape[0] > 0 else None)
     return y
@@ -292,7 +299,7 @@ class _InputConvFn(torch.autograd.Function):
     descriptor.  The im2col matrix is kept for the weight gradient; the input gets no gradient."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, padding, dilation, dtype, want_stats):
+    def forward(ctx, x, weight, bias, stride, padding, dilation, dtype, want_stats, relu=False):
         _cuda(x, weight, bias)
         lib = _L.load()
         if x.dtype != torch.float32 or not x.is_contiguous():
@@ -315,7 +322,7 @@ class _InputConvFn(torch.autograd.Function):
         wcol = torch.zeros((k, kd), dtype=torch.float32, device=x.device)
         wcol[:, :rsc] = weight.detach().permute(0, 2, 3, 1).reshape(k, rsc)
         wcol = wcol.to(dtype).view(k, kd, 1, 1)
-        flags = _L.CNB_CONV_BIAS if bias is not None else 0
+        flags = (_L.CNB_CONV_BIAS if bias is not None else 0) | (_L.CNB_CONV_RELU if relu else 0)
         d1 = _L.ConvDesc(n, P, Q, kd, k, 1, 1, 1, 1, 0, 0, 1, 1, 1, code, flags, _L.CNB_ALGO_AUTO)
         y = _empty_nhwc(n, k, P, Q, dtype, x.device)
         ws = _workspace(lib.cnb_conv2d_workspace_bytes(C.byref(d1), _L.CNB_FWD), x.device)
@@ -329,11 +336,14 @@ class _InputConvFn(torch.autograd.Function):
         ctx.desc = d1
         ctx.geom = (k, c, r, s, rsc, kd)
         ctx.has_bias = bias is not None
+        ctx.relu = bool(relu)
         ctx.mark_non_differentiable(part)
         return y, part
 
     @staticmethod
     def backward(ctx, dy, _dpart=None):
+        if ctx.relu:
+            raise NotImplementedError("conv2d_input(relu=True) is the inference epilogue; no backward")
         lib = _L.load()
         (col,) = ctx.saved_tensors
         d = ctx.desc
@@ -347,15 +357,15 @@ class _InputConvFn(torch.autograd.Function):
         _L.check(lib.cnb_conv2d_wgrad(C.byref(d), _p(col), _p(dy), _p(dwc), _p(db), _p(ws), ws.numel(),
                                       _stream()), "cnb_conv2d_wgrad(input)")
         dw = dwc[:, :rsc].view(k, r, s, c).permute(0, 3, 1, 2)
-        return None, dw, db, None, None, None, None, None
+        return None, dw, db, None, None, None, None, None, None
 
 
 def conv2d_input(x, weight, bias=None, stride=1, padding=0, dilation=1, dtype=torch.bfloat16,
-                 bn_stats=False):
+                 bn_stats=False, relu=False):
     """The network's first convolution applied to the fp32 NCHW batch (reference
     src/basemodel.py:185-188 feeds `self(inputs)` with it); see _InputConvFn."""
     y, part = _InputConvFn.apply(x, weight, bias, _pair(stride), _pair(padding), _pair(dilation),
-                                 dtype, bool(bn_stats))
+                                 dtype, bool(bn_stats), bool(relu))
     if bn_stats:
         return y, (part if part.shape[0] > 0 else None)
     return y
@@ -381,7 +391,7 @@ def rowim2col(x, kernel_w, stride_w, pad_w, dil_w, dtype):
 
 
 def conv2d_input_rows(x, weight, bias=None, stride=1, padding=0, dilation=1, dtype=torch.bfloat16,
-                      bn_stats=False):
+                      bn_stats=False, relu=False):
     """The network's first convolution as an R x 1 convolution over the row-im2col of the batch
     (see rowim2col): same result as conv2d_input, a third of the bytes.  The filter is rearranged by
     differentiable torch ops ([K, C, R, S] -> [K, S*C (+pad), R, 1]), so the weight gradient flows
@@ -394,7 +404,7 @@ def conv2d_input_rows(x, weight, bias=None, stride=1, padding=0, dilation=1, dty
     w2 = torch.nn.functional.pad(w2, (0, cd - s_ * c)).permute(0, 2, 1).unsqueeze(-1)
     w2 = w2.contiguous(memory_format=_CL)                      # [K, Cd, R, 1], KRSC storage
     return conv2d(x2, w2, bias, (stride[0], 1), (padding[0], 0), (dilation[0], 1), 1,
-                  wpack=pack_weight(w2, dtype), bn_stats=bn_stats)
+                  wpack=pack_weight(w2, dtype), bn_stats=bn_stats, relu=relu)
 
 
 def conv2d_uses_tc(x_shape, w_shape, stride, padding, dilation, groups, dtype, direction) -> bool:
@@ -557,6 +567,16 @@ class _AddReluFn(torch.autograd.Function):
         _L.check(lib.cnb_add_relu_bwd(_p(y), _p(dy), _p(dx), y.numel(), _dt(y), _stream()),
                  "cnb_add_relu_bwd")
         return dx, dx
+
+
+def add(a, b):
+    """a + b on feature maps, no gradient (inference tail of a residual block without ReLU)."""
+    _cuda(a, b)
+    a = _nhwc(a)
+    b = _like(b, a)
+    y = torch.empty_like(a)
+    _L.check(_L.load().cnb_add(_p(a), _p(b), _p(y), a.numel(), _dt(a), _stream()), "cnb_add")
+    return y
 
 
 def add_relu(a, b):

@@ -126,6 +126,66 @@ class StepGraph:
         return self.loss, self.logits
 
 
+class EvalGraph:
+    """Callable `inputs -> logits` replaying ONE CUDA graph of the inference forward (reference
+    valid_model / test, src/basemodel.py:304-346,601-722) for full batches; other shapes run
+    eagerly.  At 32x32 the zoo's forward is 100-400 kernels of a few microseconds each, so the
+    eager loop is bound by the host's launch rate, not by the GPU.  The folded filters / packed
+    operand copies are built by one eager forward BEFORE the capture and are read-only inside the
+    graph: re-capture (`reset()`) after the weights change."""
+
+    def __init__(self, model):
+        self.model = model
+        self.graph = None
+        self.key = None
+        self.x = self.out = None
+        self.epoch = None
+
+    def reset(self):
+        self.graph = None
+
+    @torch.no_grad()
+    def __call__(self, x):
+        m = self.model
+        if m.training:
+            raise RuntimeError("EvalGraph runs inference: call model.eval() first")
+        key = (tuple(x.shape), x.dtype)
+        if self.graph is not None and (self.key != key or self.epoch != L._WEIGHT_EPOCH[0]):
+            if self.key != key:
+                return m(x)                       # ragged last batch
+            self.reset()                          # weights changed since the capture
+        if self.graph is None:
+            self.x = torch.empty_like(x)
+            self.x.copy_(x)
+            m(self.x)                             # builds every folded / packed operand eagerly
+            F_._workspaces.clear()
+            torch.cuda.synchronize(x.device)
+            g = torch.cuda.CUDAGraph()
+            gc.collect()
+            was = gc.isenabled()
+            gc.disable()
+            try:
+                with torch.cuda.graph(g):
+                    self.out = m(self.x)
+            finally:
+                if was:
+                    gc.enable()
+            F_._workspaces.clear()
+            self.graph, self.key, self.epoch = g, key, L._WEIGHT_EPOCH[0]
+        if x.data_ptr() != self.x.data_ptr():
+            self.x.copy_(x, non_blocking=True)
+        self.graph.replay()
+        return self.out
+
+
+def enable_eval_graph(model) -> EvalGraph:
+    """Make `model.test()` (and anything else that reads `model._cnb_eval_graph`) run full-batch
+    inference forwards through an EvalGraph."""
+    eg = EvalGraph(model)
+    model.__dict__["_cnb_eval_graph"] = eg
+    return eg
+
+
 def enable_step_graph(model, eager_steps: int = 3) -> StepGraph:
     """Make `model.train_model` run its steps through a StepGraph (zoo models only)."""
     sg = StepGraph(model, eager_steps)

@@ -43,10 +43,15 @@ def invalidate_packed_weights() -> None:
 # launch per layer (bit-identical to the per-layer cnb_pack_filter:
 # tests/test_gpu_fused_paths.py::test_batched_pack_equals_per_layer_pack).  CNB_BATCHED_PACK=0 = per layer.
 _BATCHED_PACK = os.environ.get("CNB_BATCHED_PACK", "1") == "1"
-# RGB stems through the row im2col (functional.conv2d_input_rows) instead of the full im2col matrix
-# (a third of the bytes; tests/test_gpu_fused_paths.py::test_rgb_stem_vs_oracle holds both to the
-# float64 oracle).  CNB_STEM_ROWS=0 = full im2col matrix.
-_STEM_ROWS = os.environ.get("CNB_STEM_ROWS", "1") == "1"
+# RGB stems through the row im2col (functional.conv2d_input_rows) instead of the full im2col matrix:
+# a third of the bytes, but 7 k-steps of 64 with 24 valid channels each instead of 3 — measured
+# slower on the ResNet-50 step (profiles/r02a_switches.md: 11 201 vs 11 527 img/s), so it stays an
+# option (CNB_STEM_ROWS=1).  tests/test_gpu_fused_paths.py::test_rgb_stem_vs_oracle holds both
+# paths to the float64 oracle.
+_STEM_ROWS = os.environ.get("CNB_STEM_ROWS", "0") == "1"
+# Inference: fold BatchNorm running statistics into the producing convolution (Conv2d._folded).
+# CNB_FOLD_BN=0 keeps the separate cnb_bn_fwd_eval pass.
+_FOLD_BN = os.environ.get("CNB_FOLD_BN", "1") == "1"
 
 
 class PackGroup:
@@ -138,12 +143,49 @@ class Conv2d(nn.Conv2d):
             self.__dict__["_cnb_pack"] = cache
         return cache[1]
 
+    def _folded(self, bn, dtype: torch.dtype):
+        """Inference: (filter, bias, packed operand) with the following BatchNorm2d's running
+        statistics folded in — w' = w * gamma / sqrt(var + eps), b' = beta + (b - mean) * gamma /
+        sqrt(var + eps) — so that conv -> BN -> ReLU is ONE kernel with a bias / ReLU epilogue
+        (reference valid_model / evaluate / test, src/basemodel.py:304-346,508-576,601-722).
+        Rebuilt when the weights or the running statistics change (every training forward bumps
+        num_batches_tracked)."""
+        w = self.weight
+        nbt = bn.num_batches_tracked
+        key = (_WEIGHT_EPOCH[0], w._version, w.data_ptr(), dtype, bn.running_mean._version,
+               bn.running_var._version, -1 if nbt is None else nbt._version,
+               -1 if bn.weight is None else bn.weight._version,
+               -1 if bn.bias is None else bn.bias._version)
+        cache = self.__dict__.get("_cnb_fold")
+        if cache is None or cache[0] != key:
+            with torch.no_grad():
+                scale = torch.rsqrt(bn.running_var.float() + bn.eps)
+                if bn.weight is not None:
+                    scale = scale * bn.weight.float()
+                shift = -bn.running_mean.float() * scale
+                if bn.bias is not None:
+                    shift = shift + bn.bias.float()
+                if self.bias is not None:
+                    shift = shift + self.bias.float() * scale
+                wf = (w.detach().float() * scale.view(-1, 1, 1, 1)).contiguous(memory_format=torch.channels_last)
+                dense_tc = (dtype == torch.bfloat16 and self.groups == 1 and w.shape[0] % 8 == 0
+                            and w.shape[1] % 8 == 0)
+                wpack = F_.pack_filter(wf, transposed=False)[0] if dense_tc else F_.pack_weight(wf, dtype)
+            cache = (key, (wf, shift.contiguous(), wpack))
+            self.__dict__["_cnb_fold"] = cache
+        return cache[1]
+
     def forward(self, x: torch.Tensor, with_skip: bool = False):
         """`with_skip`: also return an alias of x for the identity shortcut of a residual block —
         (conv(x), x_skip) — so that the skip gradient is folded into this layer's data-grad
         (functional._Conv2dSkipFn)."""
         if self.padding_mode != "zeros" or isinstance(self.padding, str):
             raise NotImplementedError("convnets_b200.Conv2d supports integer zero padding only")
+        bn = self.__dict__.get("_cnb_bn")
+        if (bn is not None and not self.training and not bn.training and bn.track_running_stats
+                and bn.running_mean is not None and not torch.is_grad_enabled() and not with_skip
+                and _FOLD_BN):
+            return self._forward_folded(x, bn)
         stats = self.emit_bn_stats and self.training
         if with_skip:
             wpack, wpack_t = self._packed(x.dtype)
@@ -166,6 +208,24 @@ class Conv2d(nn.Conv2d):
                                    bn_stats=stats, wpack_t=wpack_t))
 
 
+    def _forward_folded(self, x: torch.Tensor, bn) -> torch.Tensor:
+        relu = bool(bn.fuse_relu)
+        if self.cast_input and self.compute_dtype is not None:
+            if self.compute_dtype == torch.bfloat16 and self.groups == 1 and x.shape[1] % 8:
+                wf, bf, _ = self._folded(bn, self.compute_dtype)
+                entry = F_.conv2d_input_rows if _STEM_ROWS else F_.conv2d_input
+                y = entry(x, wf, bf, self.stride, self.padding, self.dilation, self.compute_dtype,
+                          relu=relu)
+                y._cnb_bn_folded = bn
+                return y
+            x = F_.to_nhwc(x, self.compute_dtype)
+        wf, bf, wpack = self._folded(bn, x.dtype)
+        y = F_.conv2d(x, wf, bf, self.stride, self.padding, self.dilation, self.groups, wpack=wpack,
+                      algo=self.algo, relu=relu)
+        y._cnb_bn_folded = bn
+        return y
+
+
 class BatchNorm2d(nn.BatchNorm2d):
     """nn.BatchNorm2d (per-replica batch statistics, as in the reference) with an optional fused
     ReLU: `fuse_relu` is set by convert() when the next module is nn.ReLU."""
@@ -176,6 +236,14 @@ class BatchNorm2d(nn.BatchNorm2d):
                 relu: bool | None = None) -> torch.Tensor:
         self._check_input_dim(x)
         training = self.training or (self.running_mean is None and self.running_var is None)
+        if not training and getattr(x, "_cnb_bn_folded", None) is self:
+            # inference: the producing convolution already applied this layer (and its fused ReLU)
+            # through its folded filter / bias epilogue (Conv2d._folded); what is left is the
+            # residual tail of a block, `output += identity; F.relu(output)` (src/resnet.py:191-194)
+            r = self.fuse_relu if relu is None else relu
+            if residual is not None:
+                return F_.add_relu(x, residual) if r else F_.add(x, residual)
+            return F_.relu(x) if (r and not self.fuse_relu) else x
         momentum = 0.0 if self.momentum is None else self.momentum
         if self.training and self.track_running_stats and self.num_batches_tracked is not None:
             self.num_batches_tracked.add_(1)

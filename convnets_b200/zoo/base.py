@@ -210,6 +210,51 @@ class MultiClassBaseModel(nn.Module):
         return epoch_loss / n, epoch_score / n
 
 
+    # ------------------------------------------------------------------ the reference's benchmark
+    def inference_time(self, total_times_ms, num_instances):
+        """Reference src/basemodel.py:579-599.  `total_times_ms` are cuda.Event.elapsed_time values,
+        i.e. MILLISECONDS — the reference prints and stores them as seconds (:595-597), which is why
+        data/results.xlsx's `speed` is really ms/image and `fps` images/ms.
+        Returns (entire_time, mean per image, std per image, images per time unit) in that same unit."""
+        bs = self.setting.batch_size
+        n = max(len(total_times_ms), 1)
+        entire = float(sum(total_times_ms))
+        per = [t / bs for t in total_times_ms]
+        mean = sum(per) / n
+        std = (sum((p - mean) ** 2 for p in per) / n) ** 0.5
+        return entire, mean, std, (num_instances / entire if entire > 0 else float("inf"))
+
+    @torch.no_grad()
+    def test(self, dataloader, repetitions=50):
+        """The timing half of reference test() (src/basemodel.py:601-722): 50 warm-up forwards on a
+        random batch (:644-648), then per batch cuda.Event.record -> forward + argmax -> record ->
+        synchronize -> elapsed_time (:659-668).  Returns (accuracy, total_times_ms, images per ms).
+        The sklearn classification report / confusion matrix (:696-708) are out of scope.  With
+        convnets_b200.enable_eval_graph(model) the forward of a full batch is one CUDA-graph replay."""
+        self.eval()
+        bs, (ch, h, w) = self.setting.batch_size, self.setting.input_size
+        rand_input = self.setting.device.move(torch.randn(bs, ch, h, w, dtype=torch.float))
+        fwd = getattr(self, "_cnb_eval_graph", None) or self
+        for _ in range(repetitions):
+            fwd(rand_input)
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        times, correct, seen = [], 0, 0
+        for batch in dataloader:
+            inputs, targets = self.setting.device.move(batch)
+            start.record()
+            outputs = fwd(inputs)
+            predictions = outputs.argmax(dim=1)
+            end.record()
+            torch.cuda.synchronize()
+            times.append(start.elapsed_time(end))
+            correct += int((predictions == targets).sum().item())
+            seen += int(targets.numel())
+            if self.setting.sanity_check:
+                break
+        _, _, _, fps = self.inference_time(times, seen)
+        return correct / max(seen, 1), times, fps
+
+
 class Conv2dBlock(nn.Sequential):
     """Named-children variant of conv2d_block: `conv`, [`bn`], [`relu`] (basemodel.py:1045-1067)."""
 

@@ -164,6 +164,67 @@ def test_train_step_parity_config_size(family, kind, hw, batch):
     _parity(family, kind, hw, batch, torch.bfloat16)
 
 
+def _randomise_running_stats(sd, seed=4):
+    """Non-trivial running statistics (a fresh model has mean 0 / var 1: folding would be a no-op)."""
+    g = torch.Generator().manual_seed(seed)
+    out = dict(sd)
+    for k, v in sd.items():
+        if k.endswith("running_mean"):
+            out[k] = 0.2 * torch.randn(v.shape, generator=g)
+        elif k.endswith("running_var"):
+            out[k] = 0.5 + torch.rand(v.shape, generator=g)
+        elif k.endswith("bn.weight") or (k.endswith(".weight") and v.dim() == 1):
+            out[k] = 0.5 + torch.rand(v.shape, generator=g)
+        elif k.endswith(".bias") and v.dim() == 1:
+            out[k] = 0.2 * torch.randn(v.shape, generator=g)
+    return out
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("family,kind,hw,batch", CASES)
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16], ids=["f32", "bf16"])
+@pytest.mark.parametrize("fold", [True, False], ids=["folded", "bn-kernel"])
+def test_eval_parity(family, kind, hw, batch, dtype, fold, monkeypatch):
+    """Inference forward (reference valid_model / evaluate / test, src/basemodel.py:304-346,508-576,
+    601-722): BatchNorm on running statistics, folded into the producing convolution's filter and
+    bias / ReLU epilogue (`folded`) or as a separate cnb_bn_fwd_eval pass, against the fp64 oracle's
+    eval-mode logits.  Bound: max(tolerance, 2 x the floor of the same graph in fp32)."""
+    from convnets_b200 import layers as LY
+    monkeypatch.setattr(LY, "_FOLD_BN", fold)
+    model, sd, s = _build(family, kind, hw, dtype)
+    sd = _randomise_running_stats(sd)
+    model.load_state_dict(sd)
+    g = torch.Generator().manual_seed(21)
+    x = torch.randn(batch, 3, hw, hw, generator=g)
+    bf16 = dtype == torch.bfloat16
+    storage = torch.bfloat16 if bf16 else None
+    tol = 1e-2 if bf16 else 1e-4
+    sd64 = {k: (v.double() if v.is_floating_point() else v) for k, v in sd.items()}
+    with torch.no_grad():
+        lg64 = Z.forward(family, sd64, x.double(), kind, training=False, storage=storage)[0]
+        lg32 = Z.forward(family, sd, x, kind, training=False, storage=storage)[0]
+        exact = Z.forward(family, sd64, x.double(), kind, training=False)[0]
+    floor = O.rel_l2(lg32, lg64)
+    model.eval()
+    before = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    with torch.no_grad():
+        out = model(x.cuda())
+    torch.cuda.synchronize()
+    err = O.rel_l2(out, lg64)
+    print(f"EVAL {family}-{kind} {'bf16' if bf16 else 'f32'} {'folded' if fold else 'bn-kernel'}: ours {err:.2e} "
+          f"floor {floor:.2e} (vs un-rounded fp64: {O.rel_l2(out, exact):.2e})")
+    # bf16 + folding rounds w * gamma / sigma once instead of w and y separately: compare against the
+    # un-rounded oracle too, where neither rounding order is privileged
+    bound = max(tol, 2 * floor)
+    if bf16 and fold:
+        assert err <= bound or O.rel_l2(out, exact) <= max(bound, 2 * O.rel_l2(lg64, exact)), (err, floor)
+    else:
+        assert err <= bound, (err, floor)
+    after = model.state_dict()
+    for k, v in before.items():     # inference must not touch parameters or running statistics
+        assert torch.equal(after[k], v), k
+
+
 @pytest.mark.gpu
 def test_state_dict_and_optimizer_see_same_parameters():
     """convert() keeps Parameter objects, names and state_dict keys (reference

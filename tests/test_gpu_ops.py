@@ -38,7 +38,12 @@ def rnd(*shape, dtype=torch.float32, scale=1.0, shift=0.0):
 @pytest.mark.parametrize("shape", [(4, 64, 14, 14), (3, 60, 7, 5), (2, 10, 9, 9), (8, 32, 1, 1),
                                    (2, 256, 28, 28), (1, 2048, 7, 7), (8, 64, 56, 56), (4, 128, 37, 41)])
 @pytest.mark.parametrize("relu,res", [(False, False), (True, False), (True, True), (False, True)])
-def test_batch_norm_train(dtype, shape, relu, res):
+@pytest.mark.parametrize("fused_bwd", [True, False], ids=["bwd1pass", "bwd2pass"])
+def test_batch_norm_train(dtype, shape, relu, res, fused_bwd, monkeypatch):
+    # backward: the single-read cooperative kernel (tensors that fit L2) / the reduce + dx pair
+    monkeypatch.setenv("CNB_BN_BWD_FUSED_MB", "64" if fused_bwd else "0")
+    if fused_bwd and dtype != torch.bfloat16:
+        pytest.skip("the single-read backward is the bf16 hot path")
     torch.manual_seed(1)
     n, c, h, w = shape
     x = rnd(*shape, dtype=dtype, scale=2.0, shift=3.0)  # mean >> 0: exercises the shifted sums
