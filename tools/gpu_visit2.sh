@@ -4,11 +4,10 @@ set -u
 TAG=${1:-r02b}
 O=gpurun_out
 mkdir -p $O
-timeout 1500 python -m pytest tests -m gpu -q -rf --timeout=600 > $O/pytest_$TAG.log 2>&1
+timeout 1500 python -m pytest tests -m gpu -q -rfP --timeout=600 > $O/pytest_$TAG.log 2>&1
 echo "pytest rc=$?"; grep -E "^FAILED|^ERROR" $O/pytest_$TAG.log | cut -c1-400 | head -40; tail -1 $O/pytest_$TAG.log
 grep -E "^PARITY|^LAYERS|^EVAL|Appendix A|on-vs-off" $O/pytest_$TAG.log > $O/parity_$TAG.txt
-timeout 900 python -m pytest tests -m gpu -q -s --timeout=600 -k "test_train_step_parity or test_every_layer or test_conv_resnet50 or test_switches or test_eval_parity" 2>&1 | grep -E "^PARITY|^LAYERS|^EVAL|Appendix A|on-vs-off|passed|failed" > $O/parity_$TAG.txt
-tail -2 $O/parity_$TAG.txt
+wc -l $O/parity_$TAG.txt
 for mb in 0 64 128; do
   CNB_BN_BWD_FUSED_MB=$mb timeout 200 python tools/layer_bench.py --only bn --reps 5 > $O/bn_fused_${mb}_$TAG.txt 2>&1
   echo "bn sweep $mb rc=$?"; grep "bn bwd" $O/bn_fused_${mb}_$TAG.txt | grep -E "C 256 H 14|C 512 H  7|C 128 H 28|C2048" | head -8
