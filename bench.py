@@ -36,6 +36,9 @@ import torch  # noqa: E402
 
 METRIC = "train images/sec (ResNet-50 224x224)"
 UNIT = "images/sec"
+# dataset statistics the reference normalises with (src/mngrdata.py:61-62)
+CINIC_MEAN = (0.47889522, 0.47227842, 0.43047404)
+CINIC_STD = (0.24205776, 0.23828046, 0.25874835)
 
 # model name -> (zoo class name, kind, default per-GPU batch)
 WORKLOADS = {
@@ -64,6 +67,9 @@ def parse():
     ap.add_argument("--cpu-steps", type=int, default=4)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--input", default="u8", choices=["u8", "f32"],
+                    help="host batches of the e2e leg: uint8 NHWC pixels normalised on the device "
+                         "(PrefetchLoader(normalize=...)) or fp32 NCHW already normalised on the host")
     ap.add_argument("--no-graph", action="store_true",
                     help="enqueue every step eagerly instead of replaying one CUDA graph per step")
     ap.add_argument("--trace-out", default="", help="write the per-call device-time table here")
@@ -294,9 +300,17 @@ def run_ours(args):
 
     g = torch.Generator().manual_seed(21 + rank)
     n_host = 2
-    host = [(torch.randn(B, 3, args.hw, args.hw, generator=g).pin_memory(),
-             torch.randint(0, 10, (B,), generator=g).pin_memory()) for _ in range(n_host)]
-    resident = [(x.to(dev), y.to(dev)) for x, y in host]
+    if args.input == "u8":
+        # decoded-image layout (what ImageFolder holds before ToTensor); the model sees the same
+        # fp32 NCHW tensor in both legs: ToTensor + Normalize (CINIC-10 statistics) on the device
+        from convnets_b200 import functional as CF
+        host = [(torch.randint(0, 256, (B, args.hw, args.hw, 3), generator=g, dtype=torch.uint8).pin_memory(),
+                 torch.randint(0, 10, (B,), generator=g).pin_memory()) for _ in range(n_host)]
+        resident = [(CF.normalize_u8(x.to(dev), CINIC_MEAN, CINIC_STD, nhwc=True), y.to(dev)) for x, y in host]
+    else:
+        host = [(torch.randn(B, 3, args.hw, args.hw, generator=g).pin_memory(),
+                 torch.randint(0, 10, (B,), generator=g).pin_memory()) for _ in range(n_host)]
+        resident = [(x.to(dev), y.to(dev)) for x, y in host]
 
     def step(batch):
         model.optimizer.zero_grad()
@@ -354,10 +368,11 @@ def run_ours(args):
     if not args.no_e2e:
         from convnets_b200.loader import PrefetchLoader
         # pinned host batches -> device on a side stream, one batch ahead of the step that uses it
-        loader = PrefetchLoader(HostLoader([host[i % n_host] for i in range(args.steps)]), dev)
+        lk = dict(normalize=(CINIC_MEAN, CINIC_STD), nhwc=True) if args.input == "u8" else {}
+        loader = PrefetchLoader(HostLoader([host[i % n_host] for i in range(args.steps)]), dev, **lk)
         # warm the path with enough batches for the prefetch queue / caching allocator to reach
         # their steady state (each in-flight batch is a fresh 154 MB device block)
-        model.train_model(PrefetchLoader(HostLoader([host[i % n_host] for i in range(min(args.steps, 6))]), dev))
+        model.train_model(PrefetchLoader(HostLoader([host[i % n_host] for i in range(min(args.steps, 6))]), dev, **lk))
         barrier()
         t0 = time.perf_counter()
         e0.record()
@@ -374,6 +389,8 @@ def run_ours(args):
                "h2d_bytes_per_step": x0.numel() * x0.element_size() + y0.numel() * y0.element_size(),
                "d2h_bytes_per_step": 4 + 8, "ms_per_step": ms_e / args.steps,
                "wall_ms_per_step": float(t[1].item()) / args.steps,
+               "input": ("uint8 NHWC pixels; ToTensor + Normalize on the device (cnb_normalize_u8)"
+                         if args.input == "u8" else "fp32 NCHW, normalised on the host"),
                "api": "MultiClassBaseModel.train_model(PrefetchLoader(pinned host batches)): H2D of "
                       "every batch on a side stream, overlapped with the previous step"}
 

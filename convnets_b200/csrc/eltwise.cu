@@ -89,6 +89,59 @@ __global__ void cast_f32_bf16_v4(const float* __restrict__ s, bf16* __restrict__
   }
 }
 
+// ------------------------------------------------------------------ uint8 image batch -> fp32 NCHW
+// The reference normalises on the host (transforms.ToTensor + Normalize inside the DataLoader
+// workers, src/mngrdata.py:139-165) and ships fp32 over PCIe; here the uint8 pixels cross the bus
+// (a quarter of the bytes) and this kernel restates the two transforms bit for bit:
+// ToTensor = float(u8) / 255, Normalize = (t - mean[c]) / std[c], both IEEE fp32, plus the index
+// arithmetic of RandomCrop(size, padding) (zero fill) and RandomHorizontalFlip with the offsets /
+// flips drawn by the caller.  A thread owns 4 adjacent output pixels of every channel.
+struct U8NormP {
+  int N, C, H, W, Ho, Wo, pad, nhwc;
+  float mean[4], std[4];
+};
+__global__ void u8_normalize_k(const uint8_t* __restrict__ src, float* __restrict__ dst,
+                               const int32_t* __restrict__ aug, U8NormP p, int64_t total) {
+  const int wq = (p.Wo + 3) >> 2;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int jq = (int)(i % wq);
+    const int64_t t = i / wq;
+    const int oi = (int)(t % p.Ho);
+    const int n = (int)(t / p.Ho);
+    int top = 0, left = 0, flip = 0;
+    if (aug) {
+      top = aug[n * 3 + 0];
+      left = aug[n * 3 + 1];
+      flip = aug[n * 3 + 2];
+    }
+    const int h = oi + top - p.pad;
+    const bool row_in = h >= 0 && h < p.H;
+    const uint8_t* img = src + (int64_t)n * p.C * p.H * p.W;
+    for (int c = 0; c < p.C; ++c) {
+      float v[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int oj = jq * 4 + k;
+        const int cj = flip ? p.Wo - 1 - oj : oj;   // column of the crop this output shows
+        const int w = cj + left - p.pad;
+        uint8_t u = 0;
+        if (row_in && oj < p.Wo && w >= 0 && w < p.W)
+          u = p.nhwc ? img[((int64_t)h * p.W + w) * p.C + c] : img[((int64_t)c * p.H + h) * p.W + w];
+        v[k] = __fdiv_rn(__fsub_rn(__fdiv_rn((float)u, 255.f), p.mean[c]), p.std[c]);
+      }
+      float* o = dst + (((int64_t)n * p.C + c) * p.Ho + oi) * p.Wo + jq * 4;
+      if ((p.Wo & 3) == 0) {
+        *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (jq * 4 + k < p.Wo) o[k] = v[k];
+      }
+    }
+  }
+}
+
 // ------------------------------------------------------------------ NCHW fp32 -> NHWC T
 // One block transposes a [C x 32] (channels x pixels) slab through shared memory so both the
 // NCHW reads (pixel-contiguous) and the NHWC writes (channel-contiguous) are coalesced.
@@ -834,6 +887,31 @@ int cnb_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t 
   size_t smem = (size_t)C * 33 * sizeof(float);
   CNB_DISPATCH_T(dtype, (nchw_to_nhwc_k<T><<<grid, 256, smem, (cudaStream_t)stream>>>(src, (T*)dst, C, C_dst, HW)));
   return check_launch("nchw_to_nhwc");
+}
+
+int cnb_normalize_u8(const uint8_t* src, float* dst, int32_t N, int32_t C, int32_t H, int32_t W,
+                     int32_t src_nhwc, int32_t H_out, int32_t W_out, int32_t pad,
+                     const float* mean_host, const float* std_host, const int32_t* aug,
+                     void* stream) {
+  CNB_REQUIRE(src && dst && mean_host && std_host, CNB_ERR_INVALID, "cnb_normalize_u8: null pointer");
+  CNB_REQUIRE(N > 0 && C > 0 && C <= 4 && H > 0 && W > 0 && H_out > 0 && W_out > 0 && pad >= 0,
+              CNB_ERR_INVALID, "cnb_normalize_u8: bad args (C must be 1..4)");
+  CNB_REQUIRE(aug || (pad == 0 && H_out == H && W_out == W), CNB_ERR_INVALID,
+              "cnb_normalize_u8: a crop (output %dx%d of %dx%d, pad %d) needs the per-image offsets",
+              H_out, W_out, H, W, pad);
+  CNB_REQUIRE(H_out <= H + 2 * pad && W_out <= W + 2 * pad, CNB_ERR_INVALID,
+              "cnb_normalize_u8: crop larger than the padded image");
+  CNB_REQUIRE(((uintptr_t)dst & 15) == 0, CNB_ERR_INVALID, "cnb_normalize_u8: dst must be 16-byte aligned");
+  U8NormP p;
+  p.N = N; p.C = C; p.H = H; p.W = W; p.Ho = H_out; p.Wo = W_out; p.pad = pad; p.nhwc = src_nhwc ? 1 : 0;
+  for (int c = 0; c < 4; ++c) {
+    p.mean[c] = c < C ? mean_host[c] : 0.f;
+    p.std[c] = c < C ? std_host[c] : 1.f;
+    CNB_REQUIRE(p.std[c] != 0.f, CNB_ERR_INVALID, "cnb_normalize_u8: std[%d] is zero", c);
+  }
+  const int64_t total = (int64_t)N * H_out * ((W_out + 3) / 4);
+  u8_normalize_k<<<grid_for(total, kThreads, 16), kThreads, 0, (cudaStream_t)stream>>>(src, dst, aug, p, total);
+  return check_launch("u8_normalize");
 }
 
 int cnb_im2col_nchw(const cnb_conv_desc* d, const float* src, void* dst, int32_t K_dst,

@@ -91,6 +91,42 @@ def to_nhwc(x: torch.Tensor, dtype: torch.dtype, c_dst: Optional[int] = None) ->
     return y
 
 
+def normalize_u8(x: torch.Tensor, mean, std, nhwc: bool = False, crop: Optional[int] = None,
+                 padding: int = 0, aug: Optional[torch.Tensor] = None,
+                 out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """uint8 image batch on the device -> the fp32 NCHW tensor transforms.ToTensor + Normalize
+    would have produced on the host (reference src/mngrdata.py:151-153), bit for bit.  `x` is
+    [N, C, H, W] or, with nhwc=True, [N, H, W, C] (decoded-image layout).  `aug` (int32 [N, 3] on
+    the device: top, left, flip) applies RandomCrop(crop, padding) / RandomHorizontalFlip
+    (src/mngrdata.py:146-147) with the caller's random draws; without it the geometry is
+    unchanged."""
+    _cuda(x)
+    if x.dtype != torch.uint8 or x.dim() != 4 or not x.is_contiguous():
+        raise ValueError("normalize_u8 expects a contiguous 4-D uint8 tensor")
+    if nhwc:
+        n, h, w, c = x.shape
+    else:
+        n, c, h, w = x.shape
+    ho = wo = int(crop) if crop else None
+    if ho is None:
+        ho, wo = h, w
+    mean_a = (C.c_float * c)(*[float(v) for v in mean])
+    std_a = (C.c_float * c)(*[float(v) for v in std])
+    if aug is not None:
+        _cuda(aug)
+        if aug.dtype != torch.int32 or tuple(aug.shape) != (n, 3) or not aug.is_contiguous():
+            raise ValueError("aug must be a contiguous int32 [N, 3] tensor (top, left, flip)")
+    if out is None:
+        out = torch.empty((n, c, ho, wo), dtype=torch.float32, device=x.device)
+    elif out.dtype != torch.float32 or tuple(out.shape) != (n, c, ho, wo) or not out.is_contiguous():
+        raise ValueError("out must be a contiguous fp32 [N, C, H_out, W_out] tensor")
+    lib = _L.load()
+    _L.check(lib.cnb_normalize_u8(_p(x), _p(out), n, c, h, w, 1 if nhwc else 0, ho, wo, int(padding),
+                                  mean_a, std_a, _p(aug) if aug is not None else None, _stream()),
+             "cnb_normalize_u8")
+    return out
+
+
 def cast(src: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
     """Element-wise precision conversion preserving strides (dense tensors only)."""
     _cuda(src)

@@ -83,6 +83,7 @@ SIGNATURES = {
     "cnb_channel_shuffle": (_I, [_P, _P, _I64, _I32, _I32, _I, _P]),
     "cnb_copy_channels": (_I, [_P, _I32, _I32, _P, _I32, _I32, _I64, _I32, _I, _P]),
     "cnb_nchw_to_nhwc": (_I, [_P, _P, _I32, _I32, _I32, _I32, _I32, _I, _P]),
+    "cnb_normalize_u8": (_I, [_P, _P, _I32, _I32, _I32, _I32, _I32, _I32, _I32, _I32, _P, _P, _P, _P]),
     "cnb_im2col_nchw": (_I, [C.POINTER(ConvDesc), _P, _P, _I32, _P]),
     "cnb_cast": (_I, [_P, _I, _P, _I, _I64, _P]),
     "cnb_se_scale_fwd": (_I, [_P, _P, _P, _I32, _I32, _I32, _I, _P]),

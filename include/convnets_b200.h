@@ -195,6 +195,18 @@ int cnb_copy_channels(const void* src, int32_t src_C, int32_t src_off, void* dst
  * tensor-core path, whose TMA rows must be multiples of 16 bytes) */
 int cnb_nchw_to_nhwc(const float* src, void* dst, int32_t N, int32_t C, int32_t H, int32_t W,
                      int32_t C_dst, int dtype, void* stream);
+/* network input from uint8 pixels: src [N,C,H,W] (src_nhwc = 0) or [N,H,W,C] (src_nhwc = 1, what a
+ * decoded image is) -> dst fp32 NCHW [N,C,H_out,W_out] = ((float)u8 / 255 - mean[c]) / std[c], the
+ * fp32 arithmetic of transforms.ToTensor + transforms.Normalize (reference src/mngrdata.py:151-153,
+ * :177-179) bit for bit, so the batch crosses PCIe as bytes and `DeviceMngr.move`
+ * (src/mngrdevice.py:30-36) ships a quarter of the traffic.  `aug` (device, int32 [N][3] = top, left,
+ * flip; may be NULL when H_out = H, W_out = W, pad = 0) applies RandomCrop(H_out, padding=pad)
+ * (zero fill) and RandomHorizontalFlip (src/mngrdata.py:146-147) with offsets drawn by the caller.
+ * mean / std are HOST arrays of C <= 4 floats. */
+int cnb_normalize_u8(const uint8_t* src, float* dst, int32_t N, int32_t C, int32_t H, int32_t W,
+                     int32_t src_nhwc, int32_t H_out, int32_t W_out, int32_t pad,
+                     const float* mean_host, const float* std_host, const int32_t* aug,
+                     void* stream);
 /* explicit im2col of the network input for a first layer whose channel count cannot feed the
  * tensor-core path (RGB stems: reference src/resnet.py:66 7x7 s2; src/vggnet.py 3x3; ...):
  * src fp32 NCHW [N,C,H,W] -> dst `d->dtype` [N*P*Q, K_dst], column (r*S + s)*C + c, zero for padding

@@ -196,3 +196,31 @@ def rel_l2(a, b) -> float:
     if den == 0.0:
         return 0.0 if num == 0.0 else float("inf")
     return num / den
+
+
+# --- f4: the DataLoader transforms of reference src/mngrdata.py:139-165 -------------------------
+def to_tensor_normalize(img_u8_nhwc, mean, std):
+    """transforms.ToTensor + transforms.Normalize on a batch of decoded images [N, H, W, C] uint8,
+    restated from their published definitions (torchvision is absent here: ToTensor is
+    `img.permute(2, 0, 1).contiguous().to(float32).div(255)`, Normalize is
+    `tensor.sub_(mean[:, None, None]).div_(std[:, None, None])` with fp32 mean / std tensors).
+    Stays in fp32 on purpose: the CUDA kernel is held to it bit for bit."""
+    x = torch.as_tensor(img_u8_nhwc).permute(0, 3, 1, 2).contiguous().to(torch.float32).div(255)
+    m = torch.as_tensor(mean, dtype=torch.float32)[None, :, None, None]
+    s = torch.as_tensor(std, dtype=torch.float32)[None, :, None, None]
+    return x.sub_(m).div_(s)
+
+
+def random_crop_flip(img_u8_nhwc, size, padding, aug):
+    """RandomCrop(size, padding) (zero fill, src/mngrdata.py:146) then RandomHorizontalFlip (:147) with
+    the draws already made: aug[n] = (top, left, flip).  Plain numpy indexing on the uint8 image."""
+    a = np.asarray(img_u8_nhwc)
+    n, h, w, c = a.shape
+    padded = np.zeros((n, h + 2 * padding, w + 2 * padding, c), dtype=a.dtype)
+    padded[:, padding:padding + h, padding:padding + w] = a
+    out = np.empty((n, size, size, c), dtype=a.dtype)
+    for i in range(n):
+        top, left, flip = (int(v) for v in aug[i])
+        crop = padded[i, top:top + size, left:left + size]
+        out[i] = crop[:, ::-1] if flip else crop
+    return out

@@ -393,3 +393,51 @@ def test_conv_bn_partials_and_relu_mask(shape, k, ks, stride, relu, res):
     assert O.rel_l2(gd.grad, dg) <= 1e-2 and O.rel_l2(bd.grad, db) <= 1e-2
     if res:
         assert O.rel_l2(rd.grad, dr) <= 1e-2
+
+
+# ------------------------------------------------------------------ uint8 input pipeline (f4)
+CINIC_MEAN = (0.47889522, 0.47227842, 0.43047404)
+CINIC_STD = (0.24205776, 0.23828046, 0.25874835)
+
+
+@pytest.mark.parametrize("shape", [(4, 32, 32, 3), (2, 224, 224, 3), (3, 17, 23, 3), (2, 9, 10, 1)])
+@pytest.mark.parametrize("nhwc", [True, False])
+def test_normalize_u8_bit_exact(shape, nhwc):
+    """cnb_normalize_u8 == ToTensor + Normalize (src/mngrdata.py:151-153), every bit."""
+    g = torch.Generator().manual_seed(5)
+    img = torch.randint(0, 256, shape, generator=g, dtype=torch.uint8)
+    c = shape[3]
+    ref = O.to_tensor_normalize(img, CINIC_MEAN[:c], CINIC_STD[:c])
+    src = img if nhwc else img.permute(0, 3, 1, 2).contiguous()
+    got = F_().normalize_u8(src.cuda(), CINIC_MEAN[:c], CINIC_STD[:c], nhwc=nhwc).cpu()
+    assert got.shape == ref.shape and got.dtype == torch.float32
+    assert torch.equal(got.view(torch.int32), ref.view(torch.int32))
+
+
+@pytest.mark.parametrize("n,hw,size,pad", [(16, 32, 32, 4), (5, 32, 28, 0), (3, 30, 32, 4)])
+def test_normalize_u8_crop_flip_bit_exact(n, hw, size, pad):
+    """RandomCrop(32, padding=4) + RandomHorizontalFlip (src/mngrdata.py:146-147) as index arithmetic."""
+    from convnets_b200.loader import PrefetchLoader
+    g = torch.Generator().manual_seed(9)
+    img = torch.randint(0, 256, (n, hw, hw, 3), generator=g, dtype=torch.uint8)
+    ld = PrefetchLoader([], "cuda", crop=size, padding=pad, flip_p=0.5, generator=g)
+    aug = ld.draw_augmentation(n, hw, hw)
+    assert int(aug[:, 0].max()) <= hw + 2 * pad - size and int(aug[:, 2].max()) <= 1
+    ref = O.to_tensor_normalize(O.random_crop_flip(img.numpy(), size, pad, aug.numpy()), CINIC_MEAN, CINIC_STD)
+    got = F_().normalize_u8(img.cuda(), CINIC_MEAN, CINIC_STD, nhwc=True, crop=size, padding=pad,
+                            aug=aug.cuda()).cpu()
+    assert torch.equal(got.view(torch.int32), ref.view(torch.int32))
+
+
+def test_prefetch_loader_normalizes_uint8_batches():
+    from convnets_b200.loader import PrefetchLoader
+    g = torch.Generator().manual_seed(3)
+    batches = [(torch.randint(0, 256, (8, 32, 32, 3), generator=g, dtype=torch.uint8).pin_memory(),
+                torch.randint(0, 10, (8,), generator=g).pin_memory()) for _ in range(5)]
+    out = list(PrefetchLoader(batches, "cuda", normalize=(CINIC_MEAN, CINIC_STD), nhwc=True))
+    torch.cuda.synchronize()
+    assert len(out) == 5
+    for (x, y), (xh, yh) in zip(out, batches):
+        assert x.is_cuda and x.dtype == torch.float32 and tuple(x.shape) == (8, 3, 32, 32)
+        assert torch.equal(x.cpu(), O.to_tensor_normalize(xh, CINIC_MEAN, CINIC_STD))
+        assert torch.equal(y.cpu(), yh)
