@@ -224,4 +224,7 @@ def convert(model: nn.Module, dtype: torch.dtype = torch.bfloat16, fuse: bool = 
         head.register_forward_pre_hook(lambda mod, args: tuple(
             a.float() if torch.is_tensor(a) and a.dtype == torch.bfloat16 else a for a in args))
     model._cnb_dtype = dtype
+    opt = getattr(model, "optimizer", None)
+    if hasattr(opt, "attach"):
+        opt.attach(model)   # optim.FusedAdam built before convert(): let it maintain the operand copies
     return model

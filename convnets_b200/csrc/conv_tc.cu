@@ -205,67 +205,78 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
+  // Both issuing roles run their loops with the WHOLE warp (uniform control flow, every lane polls
+  // the mbarriers) and hand only the TMA / tcgen05 instructions to one lane chosen by elect.sync.
+  // Addresses, coordinates and descriptors are then warp-uniform values in uniform registers; under
+  // `if (lane == 0)` the compiler has to treat them as per-thread values and wraps every UTMALDG /
+  // UTCHMMA in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop (~30 dependent instructions per MMA: the
+  // issuing warp, not the tensor pipe, bounded every layer — ncu r02b: 19 % pipe-active on 64
+  // -channel 3x3 layers with 84 % of the MMA warp's samples inside its own issue loop).
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
-      const int a_c0 = p.grp_out > 0 ? (n0 / p.grp_out) * p.grp_in : 0;
-      uint32_t it = 0;
-      for (int mt = m_first; mt < p.m_tiles; mt += m_step) {
-        const int m0 = mt * TILE_M;
-        int bn = 0, bh = 0, bw = 0;
-        if (IM2COL) {
-          int j = m0 % p.outQ;
-          int t = m0 / p.outQ;
-          int i = t % p.outP;
-          bn = t / p.outP;
-          bh = p.lower_h + i * p.trav_h;
-          bw = p.lower_w + j * p.trav_w;
-        }
-        for (int tap = 0; tap < p.num_taps; ++tap) {
-          for (int cb = 0; cb < p.num_cblk; ++cb, ++it) {
-            const int s = it % STAGES;
-            const uint32_t use = it / STAGES;
-            mbar_wait(&empty_bar[s], (use & 1) ^ 1);
-            uint8_t* sa = smem + s * STAGE_BYTES;
-            uint8_t* sb = sa + A_TILE_BYTES;
-            mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+    const int a_c0 = p.grp_out > 0 ? (n0 / p.grp_out) * p.grp_in : 0;
+    const uint32_t smem0 = smem_u32(smem), full0 = smem_u32(full_bar), empty0 = smem_u32(empty_bar);
+    uint32_t s = 0, ph = 1;   // ring slot and the parity a free slot shows
+    for (int mt = m_first; mt < p.m_tiles; mt += m_step) {
+      const int m0 = mt * TILE_M;
+      int bn = 0, bh = 0, bw = 0;
+      if (IM2COL) {
+        int j = m0 % p.outQ;
+        int t = m0 / p.outQ;
+        int i = t % p.outP;
+        bn = t / p.outP;
+        bh = p.lower_h + i * p.trav_h;
+        bw = p.lower_w + j * p.trav_w;
+      }
+      for (int tap = 0; tap < p.num_taps; ++tap) {
+        const int widx = (int)p.widx[tap];
+        const uint16_t ow = (uint16_t)p.off_w[tap], oh = (uint16_t)p.off_h[tap];
+        for (int cb = 0; cb < p.num_cblk; ++cb) {
+          mbar_wait_u32(empty0 + s * 8, ph);
+          if (elect_one()) {
+            const uint32_t sa = smem0 + s * STAGE_BYTES;
+            const uint32_t fb = full0 + s * 8;
+            mbar_expect_tx_u32(fb, STAGE_BYTES);
             if (IM2COL)
-              tma_load_im2col_4d(&p.tmA, &full_bar[s], sa, a_c0 + cb * TILE_K, bw, bh, bn,
-                                 (uint16_t)p.off_w[tap], (uint16_t)p.off_h[tap]);
+              tma_load_im2col_4d_u32(&p.tmA, fb, sa, a_c0 + cb * TILE_K, bw, bh, bn, ow, oh);
             else
-              tma_load_2d(&p.tmA, &full_bar[s], sa, a_c0 + cb * TILE_K, m0);
-            tma_load_3d(&p.tmB, &full_bar[s], sb, cb * TILE_K, (int)p.widx[tap], n0);
+              tma_load_2d_u32(&p.tmA, fb, sa, a_c0 + cb * TILE_K, m0);
+            tma_load_3d_u32(&p.tmB, fb, sa + A_TILE_BYTES, cb * TILE_K, widx, n0);
           }
+          __syncwarp();
+          if (++s == STAGES) { s = 0; ph ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     constexpr uint32_t idesc = make_idesc_bf16(TILE_M, BLOCK_N, 0, 0);
-    uint32_t it = 0, lt = 0;
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t full0 = smem_u32(full_bar), empty0 = smem_u32(empty_bar);
+    const uint32_t tfull0 = smem_u32(tmem_full_bar), tempty0 = smem_u32(tmem_empty_bar);
+    // descriptor low words (start address >> 4) of slot 0's A / B tiles; + STAGE_BYTES/16 per slot,
+    // + 2 per 16-element k-step.  The high word (SBO 1024, version 1, SWIZZLE_128B) is a constant.
+    const uint32_t a_lo0 = (smem_u32(smem) >> 4), b_lo0 = ((smem_u32(smem) + A_TILE_BYTES) >> 4);
+    constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
+    uint32_t s = 0, ph = 0, lt = 0;
     for (int mt = m_first; mt < p.m_tiles; mt += m_step, ++lt) {
       const uint32_t buf = lt & 1;
-      mbar_wait(&tmem_empty_bar[buf], ((lt >> 1) & 1) ^ 1);  // epilogue has drained this buffer
+      mbar_wait_u32(tempty0 + buf * 8, ((lt >> 1) & 1) ^ 1);  // epilogue has drained this buffer
       tc_fence_after();
-      const uint32_t acc = tmem_base + buf * BLOCK_N;
-      for (int k_it = 0; k_it < num_iters; ++k_it, ++it) {
-        const int s = it % STAGES;
-        const uint32_t use = it / STAGES;
-        mbar_wait(&full_bar[s], use & 1);
+      const uint32_t acc = tmem_u + buf * BLOCK_N;
+      for (int k_it = 0; k_it < num_iters; ++k_it) {
+        mbar_wait_u32(full0 + s * 8, ph);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t a_base = smem_u32(smem + s * STAGE_BYTES);
-          const uint32_t b_base = a_base + A_TILE_BYTES;
+        if (elect_one()) {
+          const uint32_t a_lo = a_lo0 + s * (STAGE_BYTES >> 4), b_lo = b_lo0 + s * (STAGE_BYTES >> 4);
 #pragma unroll
-          for (int k = 0; k < TILE_K / 16; ++k) {
-            uint64_t da = make_smem_desc_sw128(a_base + k * 32, 0, 1024);
-            uint64_t db = make_smem_desc_sw128(b_base + k * 32, 0, 1024);
-            umma_bf16(acc, da, db, idesc, (k_it | k) != 0 ? 1u : 0u);
-          }
-          umma_commit(&empty_bar[s]);
-          if (k_it == num_iters - 1) umma_commit(&tmem_full_bar[buf]);
+          for (int k = 0; k < TILE_K / 16; ++k)
+            umma_bf16_lohi(acc, a_lo + 2 * k, b_lo + 2 * k, DESC_HI, idesc, (k_it | k) != 0 ? 1u : 0u);
+          umma_commit_u32(empty0 + s * 8);
+          if (k_it == num_iters - 1) umma_commit_u32(tfull0 + buf * 8);
         }
         __syncwarp();
+        if (++s == STAGES) { s = 0; ph ^= 1; }
       }
     }
   } else {
@@ -277,7 +288,9 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
     constexpr int HALF_N = BLOCK_N / 2;
     constexpr int NCH = HALF_N / 32;          // 32-column chunks per warp: 1, 2 or 4
     const int row = quarter * 32 + lane;
-    const bool storer = (warp == 2 && lane == 0);
+    // TMA stores: issued, committed and waited for by the lane elect.sync picks in warp 2 (the
+    // election is deterministic for a given member mask, so it is the same thread every time)
+    const bool store_warp = warp == 2;
     const uint32_t st_base = smem_u32(stage_out);
     const uint32_t row_addr = st_base + row * 128;
     const uint32_t row7 = (uint32_t)(row & 7);
@@ -303,7 +316,10 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
       mbar_wait(&tmem_full_bar[buf], (lt >> 1) & 1);
       tc_fence_after();
       // the previous tile's TMA store must have finished READING the staging buffer
-      if (storer) tma_store_wait_read0();
+      if (store_warp) {
+        if (elect_one()) tma_store_wait_read0();
+        __syncwarp();
+      }
       asm volatile("bar.sync 1, 256;" ::: "memory");
       const uint32_t tcol = lane_taddr + buf * BLOCK_N + (uint32_t)(chalf * HALF_N);
       uint32_t v[2][32];
@@ -363,12 +379,16 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
       mbar_arrive(&tmem_empty_bar[buf]);
       fence_proxy_async_smem();
       asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (storer) {
-        for (int b = 0; b < BLOCK_N / 64; ++b) {
-          if (n0 + b * 64 < p.Kout)
-            tma_store_2d(&p.tmD, stage_out + b * (TILE_M * 128), n0 + b * 64, m0);
+      if (store_warp) {
+        if (elect_one()) {
+#pragma unroll
+          for (int b = 0; b < BLOCK_N / 64; ++b) {
+            if (n0 + b * 64 < p.Kout)
+              tma_store_2d_u32(&p.tmD, st_base + b * (TILE_M * 128), n0 + b * 64, m0);
+          }
+          tma_store_commit();
         }
-        tma_store_commit();
+        __syncwarp();
       }
       if (want_stats) {
         // BatchNorm statistics of this tile from the staged (bf16-rounded, i.e. as stored) values.
@@ -391,7 +411,10 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
         as0 += s0; as1 += s1; aq0 += q0; aq1 += q1;  // two-level sum: per tile, then per CTA
       }
     }
-    if (storer) tma_store_wait0();
+    if (store_warp) {
+      if (elect_one()) tma_store_wait0();
+      __syncwarp();
+    }
     if (want_stats) {
       // combine the row groups in fixed order and write this CTA's partial row
       asm volatile("bar.sync 1, 256;" ::: "memory");  // staging is idle (last store completed)
@@ -507,107 +530,115 @@ conv_wgrad_tc_k(const __grid_constant__ WgradParams p) {
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
+  // issuing roles: whole-warp loops, one elected lane per TMA / tcgen05 instruction (see the note in
+  // conv_fprop_tc_persist_k)
   if (warp == 0) {
-    if (lane == 0) {
-      int itb = 0;
-      for (int pb = 0; pb < npb; ++pb) {
-        const int pix0 = (pb0 + pb) * PIX;
-        {  // dy tile: two 64-channel boxes
-          const int s = pb % SA;
-          const uint32_t use = pb / SA;
-          mbar_wait(&emptyA[s], (use & 1) ^ 1);
-          mbar_expect_tx(&fullA[s], DY_BYTES);
-          uint8_t* dst = sA + s * DY_BYTES;
-          tma_load_2d(&p.tmDy, &fullA[s], dst, cout0, pix0);
-          tma_load_2d(&p.tmDy, &fullA[s], dst + PIX * 128, cout0 + 64, pix0);
-        }
-        int bn = 0, bh = 0, bw = 0;
-        if (IM2COL) {
-          int j = pix0 % p.outQ;
-          int t = pix0 / p.outQ;
-          int i = t % p.outP;
-          bn = t / p.outP;
-          bh = p.lower_h + i * p.trav_h;
-          bw = p.lower_w + j * p.trav_w;
-        }
-        if (TS > 1) {
-          const int s = itb % SB;
-          const uint32_t use = itb / SB;
-          mbar_wait(&emptyB[s], (use & 1) ^ 1);
-          mbar_expect_tx(&fullB[s], (uint32_t)ntap * PIX * 128);
-          uint8_t* dst = sB + s * X_BYTES;
+    const uint32_t sA0 = smem_u32(sA), sB0 = smem_u32(sB);
+    const uint32_t fullA0 = smem_u32(fullA), emptyA0 = smem_u32(emptyA);
+    const uint32_t fullB0 = smem_u32(fullB), emptyB0 = smem_u32(emptyB);
+    uint32_t sa = 0, pha = 1, sb = 0, phb = 1;   // ring slots and the parity their free state shows
+    for (int pb = 0; pb < npb; ++pb) {
+      const int pix0 = (pb0 + pb) * PIX;
+      mbar_wait_u32(emptyA0 + sa * 8, pha);
+      if (elect_one()) {  // dy tile: two 64-channel boxes
+        const uint32_t fb = fullA0 + sa * 8, dst = sA0 + sa * DY_BYTES;
+        mbar_expect_tx_u32(fb, DY_BYTES);
+        tma_load_2d_u32(&p.tmDy, fb, dst, cout0, pix0);
+        tma_load_2d_u32(&p.tmDy, fb, dst + PIX * 128, cout0 + 64, pix0);
+      }
+      __syncwarp();
+      if (++sa == SA) { sa = 0; pha ^= 1; }
+      int bn = 0, bh = 0, bw = 0;
+      if (IM2COL) {
+        int j = pix0 % p.outQ;
+        int t = pix0 / p.outQ;
+        int i = t % p.outP;
+        bn = t / p.outP;
+        bh = p.lower_h + i * p.trav_h;
+        bw = p.lower_w + j * p.trav_w;
+      }
+      if (TS > 1) {
+        mbar_wait_u32(emptyB0 + sb * 8, phb);
+        if (elect_one()) {
+          const uint32_t fb = fullB0 + sb * 8, dst = sB0 + sb * X_BYTES;
+          mbar_expect_tx_u32(fb, (uint32_t)ntap * PIX * 128);
           for (int tp = 0; tp < ntap; ++tp)
-            tma_load_im2col_4d(&p.tmX, &fullB[s], dst + tp * PIX * 128, xc0, bw, bh, bn,
-                               (uint16_t)p.off_w[tap0 + tp], (uint16_t)p.off_h[tap0 + tp]);
-          ++itb;
-          continue;
+            tma_load_im2col_4d_u32(&p.tmX, fb, dst + tp * PIX * 128, xc0, bw, bh, bn,
+                                   (uint16_t)p.off_w[tap0 + tp], (uint16_t)p.off_h[tap0 + tp]);
         }
-        for (int tp = 0; tp < ntap; ++tp, ++itb) {
-          const int s = itb % SB;
-          const uint32_t use = itb / SB;
-          mbar_wait(&emptyB[s], (use & 1) ^ 1);
-          mbar_expect_tx(&fullB[s], X_BYTES);
-          uint8_t* dst = sB + s * X_BYTES;
+        __syncwarp();
+        if (++sb == SB) { sb = 0; phb ^= 1; }
+        continue;
+      }
+      for (int tp = 0; tp < ntap; ++tp) {
+        mbar_wait_u32(emptyB0 + sb * 8, phb);
+        if (elect_one()) {
+          const uint32_t fb = fullB0 + sb * 8, dst = sB0 + sb * X_BYTES;
+          mbar_expect_tx_u32(fb, X_BYTES);
 #pragma unroll
           for (int b = 0; b < NT / 64; ++b) {
             if (IM2COL)
-              tma_load_im2col_4d(&p.tmX, &fullB[s], dst + b * PIX * 128, xc0 + b * 64, bw, bh, bn,
-                                 (uint16_t)p.off_w[tap0 + tp], (uint16_t)p.off_h[tap0 + tp]);
+              tma_load_im2col_4d_u32(&p.tmX, fb, dst + b * PIX * 128, xc0 + b * 64, bw, bh, bn,
+                                     (uint16_t)p.off_w[tap0 + tp], (uint16_t)p.off_h[tap0 + tp]);
             else
-              tma_load_2d(&p.tmX, &fullB[s], dst + b * PIX * 128, xc0 + b * 64, pix0);
+              tma_load_2d_u32(&p.tmX, fb, dst + b * PIX * 128, xc0 + b * 64, pix0);
           }
         }
+        __syncwarp();
+        if (++sb == SB) { sb = 0; phb ^= 1; }
       }
     }
   } else if (warp == 1) {
     constexpr uint32_t idesc = make_idesc_bf16(TILE_M, NT, 1, 1);  // both operands MN-major
-    int itb = 0;
+    const uint32_t idesc_mt = make_idesc_bf16(TILE_M, (uint32_t)ntap * 64u, 1, 1);
+    const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);
+    const uint32_t fullA0 = smem_u32(fullA), emptyA0 = smem_u32(emptyA);
+    const uint32_t fullB0 = smem_u32(fullB), emptyB0 = smem_u32(emptyB);
+    const uint32_t tfull = smem_u32(tmem_full_bar);
+    // MN-major SW128 descriptors: 16 pixel rows = 2 swizzle atoms of 1024 B (SBO); the next
+    // 64-channel box sits PIX*128 bytes further (LBO).  Low word = address >> 4 | LBO >> 4 << 16.
+    constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
+    constexpr uint32_t LBO_BITS = ((uint32_t)(PIX * 128) >> 4) << 16;
+    const uint32_t a_lo0 = (smem_u32(sA) >> 4) | LBO_BITS, b_lo0 = (smem_u32(sB) >> 4) | LBO_BITS;
+    uint32_t sa = 0, pha = 0, sb = 0, phb = 0;
     for (int pb = 0; pb < npb; ++pb) {
-      const int sa = pb % SA;
-      mbar_wait(&fullA[sa], (pb / SA) & 1);
+      mbar_wait_u32(fullA0 + sa * 8, pha);
+      const uint32_t a_lo = a_lo0 + sa * (DY_BYTES >> 4);
       if (TS > 1) {
-        const int sb = itb % SB;
-        mbar_wait(&fullB[sb], (itb / SB) & 1);
+        mbar_wait_u32(fullB0 + sb * 8, phb);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t idesc_mt = make_idesc_bf16(TILE_M, (uint32_t)ntap * 64u, 1, 1);
-          const uint32_t a_base = smem_u32(sA + sa * DY_BYTES);
-          const uint32_t b_base = smem_u32(sB + sb * X_BYTES);
+        if (elect_one()) {
+          const uint32_t b_lo = b_lo0 + sb * (X_BYTES >> 4);
 #pragma unroll
-          for (int k = 0; k < PIX / 16; ++k) {
-            uint64_t da = make_smem_desc_sw128(a_base + k * 2048, PIX * 128, 1024);
-            uint64_t db = make_smem_desc_sw128(b_base + k * 2048, PIX * 128, 1024);
-            umma_bf16(tmem_base, da, db, idesc_mt, (pb | k) != 0 ? 1u : 0u);
-          }
-          umma_commit(&emptyB[sb]);
-          umma_commit(&emptyA[sa]);
-          if (pb == npb - 1) umma_commit(tmem_full_bar);
+          for (int k = 0; k < PIX / 16; ++k)
+            umma_bf16_lohi(tmem_u, a_lo + k * (2048 >> 4), b_lo + k * (2048 >> 4), DESC_HI, idesc_mt,
+                           (pb | k) != 0 ? 1u : 0u);
+          umma_commit_u32(emptyB0 + sb * 8);
+          umma_commit_u32(emptyA0 + sa * 8);
+          if (pb == npb - 1) umma_commit_u32(tfull);
         }
         __syncwarp();
-        ++itb;
+        if (++sb == SB) { sb = 0; phb ^= 1; }
+        if (++sa == SA) { sa = 0; pha ^= 1; }
         continue;
       }
-      for (int tp = 0; tp < ntap; ++tp, ++itb) {
-        const int sb = itb % SB;
-        mbar_wait(&fullB[sb], (itb / SB) & 1);
+      for (int tp = 0; tp < ntap; ++tp) {
+        mbar_wait_u32(fullB0 + sb * 8, phb);
         tc_fence_after();
-        if (lane == 0) {
-          const uint32_t a_base = smem_u32(sA + sa * DY_BYTES);
-          const uint32_t b_base = smem_u32(sB + sb * X_BYTES);
+        if (elect_one()) {
+          const uint32_t b_lo = b_lo0 + sb * (X_BYTES >> 4);
 #pragma unroll
-          for (int k = 0; k < PIX / 16; ++k) {
-            // MN-major SW128: 16 pixel rows = 2 swizzle atoms of 1024 B (SBO); the next
-            // 64-channel box sits PIX*128 bytes further (LBO).
-            uint64_t da = make_smem_desc_sw128(a_base + k * 2048, PIX * 128, 1024);
-            uint64_t db = make_smem_desc_sw128(b_base + k * 2048, PIX * 128, 1024);
-            umma_bf16(tmem_base + (uint32_t)(tp * NT), da, db, idesc, (pb | k) != 0 ? 1u : 0u);
-          }
-          umma_commit(&emptyB[sb]);
-          if (tp == ntap - 1) umma_commit(&emptyA[sa]);
-          if (pb == npb - 1 && tp == ntap - 1) umma_commit(tmem_full_bar);
+          for (int k = 0; k < PIX / 16; ++k)
+            umma_bf16_lohi(tmem_u + (uint32_t)(tp * NT), a_lo + k * (2048 >> 4), b_lo + k * (2048 >> 4),
+                           DESC_HI, idesc, (pb | k) != 0 ? 1u : 0u);
+          umma_commit_u32(emptyB0 + sb * 8);
+          if (tp == ntap - 1) umma_commit_u32(emptyA0 + sa * 8);
+          if (pb == npb - 1 && tp == ntap - 1) umma_commit_u32(tfull);
         }
         __syncwarp();
+        if (++sb == SB) { sb = 0; phb ^= 1; }
       }
+      if (++sa == SA) { sa = 0; pha ^= 1; }
     }
   } else {
     // Epilogue: TMEM -> registers -> swizzled fp32 staging (the operand rings are idle by now:
@@ -617,14 +648,17 @@ conv_wgrad_tc_k(const __grid_constant__ WgradParams p) {
     // by the tensor map.
     const int quarter = warp % 4;
     const int row = quarter * 32 + lane;  // out-channel within the tile
-    const bool storer = (warp == 2 && lane == 0);
+    const bool store_warp = warp == 2;
     if (npb > 0) {
       mbar_wait(tmem_full_bar, 0);
       tc_fence_after();
     }
     uint8_t* staging = smem;
     for (int tp = 0; tp < ntap; ++tp) {
-      if (storer) tma_store_wait_read0();
+      if (store_warp) {
+        if (elect_one()) tma_store_wait_read0();
+        __syncwarp();
+      }
       asm volatile("bar.sync 1, 128;" ::: "memory");
 #pragma unroll 1
       for (int c0 = 0; c0 < NT; c0 += 32) {
@@ -645,15 +679,21 @@ conv_wgrad_tc_k(const __grid_constant__ WgradParams p) {
       }
       fence_proxy_async_smem();
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (storer) {
-        for (int c0 = 0; c0 < NT; c0 += 32)
-          if (cin0 + c0 < p.Cg)
-            tma_store_4d(&p.tmOut, staging + (c0 / 32) * (TILE_M * 128), cin0 + c0, tap0 + tp, cout0,
-                         split);
-        tma_store_commit();
+      if (store_warp) {
+        if (elect_one()) {
+          for (int c0 = 0; c0 < NT; c0 += 32)
+            if (cin0 + c0 < p.Cg)
+              tma_store_4d(&p.tmOut, staging + (c0 / 32) * (TILE_M * 128), cin0 + c0, tap0 + tp, cout0,
+                           split);
+          tma_store_commit();
+        }
+        __syncwarp();
       }
     }
-    if (storer) tma_store_wait0();
+    if (store_warp) {
+      if (elect_one()) tma_store_wait0();
+      __syncwarp();
+    }
     tc_fence_before();
   }
   __syncthreads();

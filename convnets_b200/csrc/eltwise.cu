@@ -776,6 +776,133 @@ pack_filters_batched_k(const cnb_pack_item* __restrict__ items, int n_items) {
   }
 }
 
+// ------------------------------------------------------------------ multi-tensor Adam (cnb_adam_step)
+// The whole optimiser step of a model in two launches: `adam_tick_k` advances the step counter and
+// derives the step's scalars in double (as the reference's Python does, torch/optim/adam.py
+// _single_tensor_adam reached from src/basemodel.py:58-66,284), `adam_step_k` updates every
+// parameter and writes the bf16 operand copies of the tensor-core filters in the same pass — the
+// separate pack pass over the weights disappears.  Per element, fp32, in the reference's order:
+//   g' = fma(wd, p, g);  m = fma(1 - b1, g' - m, m);  v = fma((1 - b2) * g', g', v * b2);
+//   p += (-step_size * m) / (sqrt(v) / sqrt(1 - b2^t) + eps),  step_size = lr / (1 - b1^t)
+// state (doubles, device): [0] t  [1] lr  [2] b1  [3] b2  [4] eps  [5] wd  | derived, written by the tick:
+// [8] 1-b1  [9] b2  [10] 1-b2  [11] step_size  [12] sqrt(1-b2^t)  [13] eps  [14] wd
+__global__ void adam_tick_k(double* __restrict__ st) {
+  const double t = st[0] + 1.0;
+  st[0] = t;
+  const double b1 = st[2], b2 = st[3];
+  st[8] = (double)(float)(1.0 - b1);
+  st[9] = (double)(float)b2;
+  st[10] = (double)(float)(1.0 - b2);
+  st[11] = (double)(float)(st[1] / (1.0 - pow(b1, t)));
+  st[12] = (double)(float)sqrt(1.0 - pow(b2, t));
+  st[13] = (double)(float)st[4];
+  st[14] = (double)(float)st[5];
+}
+
+struct AdamK {
+  float w1, b2, w2, step_size, bc2_sqrt, eps, wd;
+};
+__device__ __forceinline__ float adam_update(float& p, float g, float& m, float& v, const AdamK& k) {
+  // operation order and fusion of torch's CPU vector kernels (pinned in tests/test_optim.py)
+  if (k.wd != 0.f) g = __fmaf_rn(k.wd, p, g);
+  m = __fmaf_rn(k.w1, __fsub_rn(g, m), m);                                   // lerp_, weight < 0.5
+  v = __fmaf_rn(__fmul_rn(k.w2, g), g, __fmul_rn(v, k.b2));                  // mul_ then addcmul_
+  const float denom = __fadd_rn(__fdiv_rn(__fsqrt_rn(v), k.bc2_sqrt), k.eps);
+  p = __fadd_rn(p, __fdiv_rn(__fmul_rn(-k.step_size, m), denom));            // addcdiv_
+  return p;
+}
+
+constexpr int kAdamFlat = 4096;   // elements per block of a flat item
+constexpr int kAdamChunk = 56;    // items per launch: the table travels as a kernel parameter (< 4 KB),
+struct AdamChunk {                // so a captured step holds it by value — no device table to keep alive
+  cnb_adam_item items[kAdamChunk];
+  int n;
+};
+__global__ void __launch_bounds__(256)
+adam_step_k(const __grid_constant__ AdamChunk ch, const double* __restrict__ st) {
+  __shared__ bf16 tile[32][34];
+  const cnb_adam_item* items = ch.items;
+  int lo = 0, hi = ch.n - 1;
+  const int b = blockIdx.x;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (items[mid].first_block <= b) lo = mid;
+    else hi = mid - 1;
+  }
+  const cnb_adam_item it = items[lo];
+  const int lb = b - it.first_block;
+  AdamK k;
+  k.w1 = (float)st[8]; k.b2 = (float)st[9]; k.w2 = (float)st[10]; k.step_size = (float)st[11];
+  k.bc2_sqrt = (float)st[12]; k.eps = (float)st[13]; k.wd = (float)st[14];
+  bf16* wb = (bf16*)it.w_bf16;
+  if (it.RS == 0) {   // flat item: K * C contiguous elements (K = 1 for plain tensors)
+    const int64_t n = (int64_t)it.K * it.C;
+    const int64_t e0 = (int64_t)lb * kAdamFlat;
+    const bool vec = ((((uintptr_t)it.p | (uintptr_t)it.g | (uintptr_t)it.m | (uintptr_t)it.v) & 15) == 0);
+#pragma unroll
+    for (int u = 0; u < kAdamFlat / 1024; ++u) {
+      const int64_t e = e0 + (int64_t)u * 1024 + threadIdx.x * 4;
+      if (e >= n) break;
+      if (vec && e + 4 <= n) {
+        float4 p4 = *reinterpret_cast<const float4*>(it.p + e);
+        const float4 g4 = *reinterpret_cast<const float4*>(it.g + e);
+        float4 m4 = *reinterpret_cast<const float4*>(it.m + e);
+        float4 v4 = *reinterpret_cast<const float4*>(it.v + e);
+        adam_update(p4.x, g4.x, m4.x, v4.x, k);
+        adam_update(p4.y, g4.y, m4.y, v4.y, k);
+        adam_update(p4.z, g4.z, m4.z, v4.z, k);
+        adam_update(p4.w, g4.w, m4.w, v4.w, k);
+        *reinterpret_cast<float4*>(it.p + e) = p4;
+        *reinterpret_cast<float4*>(it.m + e) = m4;
+        *reinterpret_cast<float4*>(it.v + e) = v4;
+        if (wb) {
+          wb[e] = __float2bfloat16_rn(p4.x); wb[e + 1] = __float2bfloat16_rn(p4.y);
+          wb[e + 2] = __float2bfloat16_rn(p4.z); wb[e + 3] = __float2bfloat16_rn(p4.w);
+        }
+      } else {
+        for (int j = 0; j < 4 && e + j < n; ++j) {
+          float p = it.p[e + j], m = it.m[e + j], v = it.v[e + j];
+          adam_update(p, it.g[e + j], m, v, k);
+          it.p[e + j] = p; it.m[e + j] = m; it.v[e + j] = v;
+          if (wb) wb[e + j] = __float2bfloat16_rn(p);
+        }
+      }
+    }
+    return;
+  }
+  // filter item [K][RS][C]: one [32 out-ch x 32 in-ch] tile of one tap (layout of pack_filters_batched_k)
+  const int ctiles = (it.C + 31) / 32, ktiles = (it.K + 31) / 32;
+  const int ct = lb % ctiles;
+  const int t2 = lb / ctiles;
+  const int kt = t2 % ktiles;
+  const int rs = t2 / ktiles;
+  if (rs >= it.RS) return;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int k0 = kt * 32, c0 = ct * 32;
+  bf16* wt = (bf16*)it.wt_bf16;
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int kk = k0 + ty + 8 * q, c = c0 + tx;
+    bf16 o = __float2bfloat16_rn(0.f);
+    if (kk < it.K && c < it.C) {
+      const int64_t i = ((int64_t)kk * it.RS + rs) * it.C + c;
+      float p = it.p[i], m = it.m[i], v = it.v[i];
+      adam_update(p, it.g[i], m, v, k);
+      it.p[i] = p; it.m[i] = m; it.v[i] = v;
+      o = __float2bfloat16_rn(p);
+      if (wb) wb[i] = o;
+    }
+    tile[ty + 8 * q][tx] = o;
+  }
+  if (!wt) return;
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int c = c0 + ty + 8 * q, kk = k0 + tx;
+    if (c < it.C && kk < it.K) wt[((int64_t)c * it.RS + rs) * it.K + kk] = tile[tx][ty + 8 * q];
+  }
+}
+
 }  // namespace cnb
 
 using namespace cnb;
@@ -853,6 +980,41 @@ int cnb_pack_filters(const cnb_pack_item* items_device, int32_t n_items, int32_t
               total_blocks);
   pack_filters_batched_k<<<(unsigned)total_blocks, 256, 0, (cudaStream_t)stream>>>(items_device, n_items);
   return check_launch("pack_filters");
+}
+
+int64_t cnb_adam_item_blocks(int32_t K, int32_t RS, int32_t C) {
+  if (K <= 0 || RS < 0 || C <= 0) return 0;
+  if (RS == 0) return ceil_div((int64_t)K * C, (int64_t)kAdamFlat);
+  return (int64_t)RS * ceil_div(K, 32) * ceil_div(C, 32);
+}
+
+int cnb_adam_step(const cnb_adam_item* items_host, int32_t n_items, double* state_device,
+                  void* stream) {
+  CNB_REQUIRE(items_host && state_device && n_items > 0, CNB_ERR_INVALID,
+              "cnb_adam_step: bad args (items=%p state=%p n=%d)", (const void*)items_host,
+              (const void*)state_device, n_items);
+  for (int i = 0; i < n_items; ++i) {
+    const cnb_adam_item& it = items_host[i];
+    CNB_REQUIRE(it.p && it.g && it.m && it.v && it.K > 0 && it.C > 0 && it.RS >= 0, CNB_ERR_INVALID,
+                "cnb_adam_step: item %d is incomplete", i);
+  }
+  adam_tick_k<<<1, 1, 0, (cudaStream_t)stream>>>(state_device);
+  int rc = check_launch("adam_tick");
+  for (int i0 = 0; i0 < n_items && rc == CNB_OK; i0 += kAdamChunk) {
+    AdamChunk ch;
+    ch.n = n_items - i0 < kAdamChunk ? n_items - i0 : kAdamChunk;
+    int64_t blocks = 0;
+    for (int i = 0; i < ch.n; ++i) {
+      ch.items[i] = items_host[i0 + i];
+      ch.items[i].first_block = (int32_t)blocks;
+      blocks += cnb_adam_item_blocks(ch.items[i].K, ch.items[i].RS, ch.items[i].C);
+    }
+    CNB_REQUIRE(blocks > 0 && blocks < (int64_t)INT32_MAX, CNB_ERR_INVALID, "cnb_adam_step: %lld blocks",
+                (long long)blocks);
+    adam_step_k<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(ch, state_device);
+    rc = check_launch("adam_step");
+  }
+  return rc;
 }
 
 int cnb_cast(const void* src, int sdt, void* dst, int ddt, int64_t n, void* stream) {

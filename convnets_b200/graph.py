@@ -66,6 +66,15 @@ class StepGraph:
         self.x.copy_(x)
         self.y.copy_(y)
         _invalidate_packs(m)
+        opt = m.optimizer
+        if hasattr(opt, "sync_hyperparams"):
+            # optim.FusedAdam: hyper-parameters go to the device now (not capturable), and the bf16
+            # operand copies it maintains are brought up to date eagerly — inside the graph the
+            # forward then finds them valid and the Adam step rewrites them: no pack kernel per replay
+            opt.sync_hyperparams()
+            opt.ensure_state()
+            for grp in opt._groups_in_use():
+                grp.refresh()
         F_._workspaces.clear()      # scratch must come from the graph's private pool
         torch.cuda.synchronize(dev)
         g = torch.cuda.CUDAGraph()
@@ -117,12 +126,15 @@ class StepGraph:
             self.x.copy_(x, non_blocking=True)
         if y.data_ptr() != self.y.data_ptr():
             self.y.copy_(y, non_blocking=True)
+        opt = self.model.optimizer
+        if hasattr(opt, "sync_hyperparams"):
+            opt.sync_hyperparams()      # a learning rate changed by the scheduler reaches the replay
         self.graph.replay()
         # The replayed Adam step changed every weight without running any Python: neither the
         # optimizer post-step hook nor the tensor version counter moved.  Advance the weight epoch so
         # that the next EAGER forward (valid_model, a ragged last batch) re-packs its bf16 operand
         # copies instead of reusing the ones this replay built from the pre-step weights.
-        L._bump_weight_epoch()
+        L._bump_weight_epoch(opt)
         return self.loss, self.logits
 
 
@@ -174,6 +186,9 @@ class EvalGraph:
             self.graph, self.key, self.epoch = g, key, L._WEIGHT_EPOCH[0]
         if x.data_ptr() != self.x.data_ptr():
             self.x.copy_(x, non_blocking=True)
+        opt = self.model.optimizer
+        if hasattr(opt, "sync_hyperparams"):
+            opt.sync_hyperparams()      # a learning rate changed by the scheduler reaches the replay
         self.graph.replay()
         return self.out
 

@@ -24,8 +24,12 @@ from . import lib as _L
 _WEIGHT_EPOCH = [0]
 
 
-def _bump_weight_epoch(*_args, **_kwargs) -> None:
+def _bump_weight_epoch(opt=None, *_args, **_kwargs) -> None:
     _WEIGHT_EPOCH[0] += 1
+    # an optimizer that wrote the operand copies itself (optim.FusedAdam) re-validates them
+    restamp = getattr(opt, "restamp", None)
+    if restamp is not None:
+        restamp()
 
 
 from torch.optim.optimizer import register_optimizer_step_post_hook as _reg_post_hook  # noqa: E402

@@ -40,6 +40,13 @@ class PackItem(C.Structure):
                 ("K", C.c_int32), ("RS", C.c_int32), ("C", C.c_int32), ("first_block", C.c_int32)]
 
 
+class AdamItem(C.Structure):
+    """cnb_adam_item (include/convnets_b200.h): one parameter of a cnb_adam_step call."""
+    _fields_ = [("p", C.c_void_p), ("g", C.c_void_p), ("m", C.c_void_p), ("v", C.c_void_p),
+                ("w_bf16", C.c_void_p), ("wt_bf16", C.c_void_p),
+                ("K", C.c_int32), ("RS", C.c_int32), ("C", C.c_int32), ("first_block", C.c_int32)]
+
+
 _P = C.c_void_p
 _I = C.c_int
 _I32 = C.c_int32
@@ -85,6 +92,8 @@ SIGNATURES = {
     "cnb_nchw_to_nhwc": (_I, [_P, _P, _I32, _I32, _I32, _I32, _I32, _I, _P]),
     "cnb_normalize_u8": (_I, [_P, _P, _I32, _I32, _I32, _I32, _I32, _I32, _I32, _I32, _P, _P, _P, _P]),
     "cnb_im2col_nchw": (_I, [C.POINTER(ConvDesc), _P, _P, _I32, _P]),
+    "cnb_adam_item_blocks": (_I64, [_I32, _I32, _I32]),
+    "cnb_adam_step": (_I, [_P, _I32, _P, _P]),
     "cnb_cast": (_I, [_P, _I, _P, _I, _I64, _P]),
     "cnb_se_scale_fwd": (_I, [_P, _P, _P, _I32, _I32, _I32, _I, _P]),
     "cnb_se_scale_bwd": (_I, [_P, _P, _P, _P, _P, _I32, _I32, _I32, _I, _P]),

@@ -18,6 +18,7 @@ tuner are out of scope.
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 import torch.nn as nn
@@ -113,10 +114,16 @@ class MultiClassBaseModel(nn.Module):
         # multi-tensor ("fused") implementation runs it in a handful of launches instead of ~10
         # per parameter
         fused = bool(params) and all(p.is_cuda for p in params)
-        # capturable: the step counters live on the device, so the update can sit inside the CUDA
-        # graph of a whole training step (convnets_b200.graph.StepGraph)
-        self.optimizer = torch.optim.Adam(params, lr=s.learning_rate, weight_decay=s.weight_decay,
-                                          fused=fused, capturable=fused)
+        if fused and os.environ.get("CNB_FUSED_ADAM", "1") == "1":
+            # the library's multi-tensor Adam: the whole update in 1 + ceil(n / 56) launches, writing
+            # the bf16 operand copies of the tensor-core filters in the same pass (optim.FusedAdam)
+            from ..optim import FusedAdam
+            self.optimizer = FusedAdam(params, lr=s.learning_rate, weight_decay=s.weight_decay, model=self)
+        else:
+            # capturable: the step counters live on the device, so the update can sit inside the
+            # CUDA graph of a whole training step (convnets_b200.graph.StepGraph)
+            self.optimizer = torch.optim.Adam(params, lr=s.learning_rate, weight_decay=s.weight_decay,
+                                              fused=fused, capturable=fused)
         self.lr_scheduler = torch.optim.lr_scheduler.ReduceLROnPlateau(
             self.optimizer, mode="min" if s.loss_optim else "max", factor=s.lr_factor,
             patience=s.lr_patience)

@@ -239,6 +239,30 @@ typedef struct cnb_pack_item {
 int64_t cnb_pack_filter_blocks(int32_t K, int32_t RS, int32_t C);
 int cnb_pack_filters(const cnb_pack_item* items_device, int32_t n_items, int32_t total_blocks,
                      void* stream);
+/* the optimiser step (reference src/basemodel.py:58-66 `optim.Adam(lr, weight_decay)`, stepped at
+ * :284) for every parameter of a model in one call, writing the bf16 operand copies of the
+ * tensor-core filters in the same pass (replaces cnb_pack_filters + torch's Adam kernels).
+ * `items_host` is a HOST array (it travels to the device as kernel parameters, 56 items per launch,
+ * so a CUDA-graph capture of the step holds it by value); first_block is filled in by the library.
+ * Item: p / g / m / v fp32, same physical layout.  RS = 0: flat tensor of K*C elements (w_bf16, if
+ * given, receives the cast copy; wt_bf16 ignored).  RS > 0: filter [K][RS][C] as in cnb_pack_item.
+ * `state_device`: 16 doubles; the caller sets [0] step count so far, [1] lr, [2] beta1, [3] beta2,
+ * [4] eps, [5] weight_decay; the call increments [0] and uses [8..15] as scratch.  Arithmetic is
+ * fp32 in the order of torch's single-tensor Adam (the reference's CPU path); bias corrections in
+ * double. */
+typedef struct cnb_adam_item {
+  float* p;
+  const float* g;
+  float* m;
+  float* v;
+  void* w_bf16;
+  void* wt_bf16;
+  int32_t K, RS, C;
+  int32_t first_block;
+} cnb_adam_item;
+int64_t cnb_adam_item_blocks(int32_t K, int32_t RS, int32_t C);
+int cnb_adam_step(const cnb_adam_item* items_host, int32_t n_items, double* state_device,
+                  void* stream);
 /* element-wise precision conversion (fp32 master weights -> bf16 operand copy, etc.) */
 int cnb_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n, void* stream);
 

@@ -224,3 +224,26 @@ def random_crop_flip(img_u8_nhwc, size, padding, aug):
         crop = padded[i, top:top + size, left:left + size]
         out[i] = crop[:, ::-1] if flip else crop
     return out
+
+
+# --- a4 / f2: optim.Adam as the reference steps it (src/basemodel.py:58-66,284) -------------------
+def adam_step(p, g, m, v, step, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0):
+    """One update of torch's single-tensor Adam (torch/optim/adam.py `_single_tensor_adam`, the
+    path a CPU model takes) restated on numpy float32 arrays, operation by operation; `step` is
+    the 1-based count of this update.  Returns (p, m, v) as new float32 arrays.  Pinned against
+    torch.optim.Adam on CPU in tests/test_optim.py."""
+    f, d = np.float32, np.float64
+    p, g, m, v = (np.asarray(a, dtype=f).copy() for a in (p, g, m, v))
+
+    def fma(a, b, c):   # the CPU vector kernels fuse these (product of two fp32 is exact in fp64)
+        return (np.asarray(a, dtype=f).astype(d) * np.asarray(b, dtype=f).astype(d) + c.astype(d)).astype(f)
+
+    if weight_decay != 0:
+        g = fma(f(weight_decay), p, g)                           # grad.add(param, alpha=wd)
+    m = fma(f(1 - beta1), g - m, m)                              # exp_avg.lerp_(grad, 1 - beta1)
+    v = fma(f(1 - beta2) * g, g, v * f(beta2))                   # mul_(beta2).addcmul_(g, g, value=1 - beta2)
+    bc1 = 1 - beta1 ** step
+    bc2_sqrt = (1 - beta2 ** step) ** 0.5
+    denom = np.sqrt(v) / f(bc2_sqrt) + f(eps)                    # (sqrt / bc2_sqrt).add_(eps)
+    p = p + (f(-(lr / bc1)) * m) / denom                         # addcdiv_(exp_avg, denom, value=-step_size)
+    return p.astype(f), m.astype(f), v.astype(f)

@@ -130,7 +130,21 @@ def test_every_layer_in_a_real_step(family, kind, hw, batch):
             prod = by_out.get(r["x"].data_ptr())
             if prod is not None and "dy" in rec[prod] and dx_ref.norm().item() > 0:
                 floor = O.rel_l2(dx_ref.bfloat16(), dx_ref) if lowp else 0.0   # bf16 rounding of the stored dx
-                note("bn dx", name, O.rel_l2(rec[prod]["dy"], dx_ref), max(tol, 2 * floor))
+                rows = xin.numel() // xin.shape[1]
+                if rows < 32:
+                    # statistics over a handful of rows (the SK attention's [B, C, 1, 1] descriptor at
+                    # batch 2): dx = c1 * (dy - mean(dy) - xhat * mean(dy * xhat)) cancels almost
+                    # completely (exactly, for 2 rows and eps = 0), so the result is a rounding residue
+                    # of its terms.  The error is measured against the un-cancelled magnitude
+                    # |gamma * rstd * dy|, which is what any fp32 evaluation can be held to.
+                    xd = xin.double()
+                    var = xd.var(dim=(0, 2, 3), unbiased=False)
+                    c1 = (gam.double() / torch.sqrt(var + m.eps)).view(1, -1, 1, 1)
+                    scale = (c1 * _cpu(r["dy"]).double()).norm().item()
+                    err = (_cpu(rec[prod]["dy"]).double() - dx_ref.double()).norm().item() / max(scale, 1e-30)
+                    note("bn dx (few rows)", name, err, max(tol, 2 * floor))
+                else:
+                    note("bn dx", name, O.rel_l2(rec[prod]["dy"], dx_ref), max(tol, 2 * floor))
     assert n_conv > 10 and n_bn > 10
     print(f"LAYERS {family}-{kind} {hw}x{hw} B{batch}: {n_conv} convs, {n_bn} batch-norms; worst " +
           ", ".join(f"{k} {v[0]:.2e} ({v[1]})" for k, v in sorted(worst.items())))

@@ -89,14 +89,17 @@ def _parity(family, kind, hw, batch, dtype):
     with torch.backends.mkldnn.flags(enabled=False):                                        # fp32, ATen native
         lg_b, _, g_b, buf_b = Z.loss_and_grads(family, sd, x, y, kind, storage=storage)
     floors.append((lg_b, g_b, buf_b))
-    if not bf16 and hw <= 64:
+    if hw <= 64:
         # conditioning of the reference graph itself: ONE pre-activation within a few ulps of zero
         # flips its ReLU mask between two executions and moves everything upstream of it.  The
-        # fp64 oracle on the input scaled by (1 + 1e-6 randn) (~8 fp32 ulps) measures that spread.
+        # fp64 oracle on the input scaled by (1 + 1e-6 randn) (~8 fp32 ulps; bf16 storage: 2e-3,
+        # half a bf16 ulp) measures that spread — two more samples of the floor, which matters for
+        # the max over a few hundred parameters (a heavy-tailed statistic estimated from 2 runs).
         for seed in (1, 2):
             gp_ = torch.Generator().manual_seed(seed)
-            xp = x.double() * (1 + 1e-6 * torch.randn(x.shape, generator=gp_, dtype=torch.float64))
-            lg_p, _, g_p, buf_p = Z.loss_and_grads(family, sd64, xp, y, kind)
+            eps_ = 2e-3 if bf16 else 1e-6
+            xp = x.double() * (1 + eps_ * torch.randn(x.shape, generator=gp_, dtype=torch.float64))
+            lg_p, _, g_p, buf_p = Z.loss_and_grads(family, sd64, xp, y, kind, storage=storage)
             floors.append((lg_p, g_p, buf_p))
     lfloor = max(O.rel_l2(f[0], lg64) for f in floors[:2])
 
@@ -134,15 +137,19 @@ def _parity(family, kind, hw, batch, dtype):
     print(f"PARITY {tag}: running stats worst ours {worst_buf[0]:.2e} floor {worst_buf[1]:.2e} ({worst_buf[2]})")
     # gradients: quantile against quantile (see the module docstring)
     gsum = sum(v.norm().item() for v in g64.values() if v is not None)
-    ours_all, floor_all = [], []
+    ours_all, floor_all, names_all = [], [], []
     for k, p in model.named_parameters():
         ref = g64[k]
         assert p.grad is not None, k
         if ref.norm().item() < 1e-6 * max(1.0, gsum):
             continue   # analytically-zero gradient (ShuffleNet has one): no relative error exists
+        names_all.append(k)
         ours_all.append(O.rel_l2(p.grad, ref))
         floor_all.append(max(O.rel_l2(f[1][k], ref) for f in floors))
     oq, fq = _quantiles(ours_all), _quantiles(floor_all)
+    worst_i = max(range(len(ours_all)), key=lambda i: ours_all[i])
+    print(f"PARITY {tag}: worst gradient {names_all[worst_i]} ours {ours_all[worst_i]:.2e} "
+          f"its floor {floor_all[worst_i]:.2e}")
     print(f"PARITY {tag}: grads median/p90/max ours {oq[0]:.2e}/{oq[1]:.2e}/{oq[2]:.2e} "
           f"floor {fq[0]:.2e}/{fq[1]:.2e}/{fq[2]:.2e}")
     for name, o, f in zip(("median", "p90", "max"), oq, fq):
@@ -355,9 +362,16 @@ def test_eval_between_graph_replays_uses_current_weights(family, kind):
         graphed.eval()
         with torch.no_grad():
             lg = graphed(xe)
-        for m in convs:   # the copy the eval forward just used == the current weight, rounded
-            wb = m.__dict__["_cnb_pack"][1][0]
-            assert torch.equal(wb.float(), m.weight.detach().to(wb.dtype).float()), (rnd, tuple(m.weight.shape))
+        for m in convs:   # the copy the eval forward just used was built from the current weight
+            fold = m.__dict__.get("_cnb_fold")
+            if fold is not None:   # conv -> BatchNorm: the filter with the running statistics folded in
+                bn = m.__dict__["_cnb_bn"]
+                scale = torch.rsqrt(bn.running_var.float() + bn.eps) * bn.weight.detach().float()
+                want = m.weight.detach().float() * scale.view(-1, 1, 1, 1)
+                assert torch.equal(fold[1][0], want), (rnd, tuple(m.weight.shape))
+            else:
+                wb = m.__dict__["_cnb_pack"][1][0]
+                assert torch.equal(wb.float(), m.weight.detach().to(wb.dtype).float()), (rnd, tuple(m.weight.shape))
         # an eager twin that only ever loads the weights (its optimizer never steps between the checks)
         twin.load_state_dict(graphed.state_dict())
         twin.eval()
