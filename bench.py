@@ -43,7 +43,8 @@ CINIC_STD = (0.24205776, 0.23828046, 0.25874835)
 # model name -> (zoo class name, kind, default per-GPU batch)
 WORKLOADS = {
     "resnet50": ("ResNet", "50", 256),          # BASELINE.json configs[1] — the headline (default)
-    "vgg11": ("VGGNet", "11", 64),              # configs[0] shape when run with --hw 32
+    "vgg11": ("VGGNet", "11", 64),              # configs[0] shape when run with --hw 32 --dtype f32
+    "vgg16": ("VGGNet", "16", 64),              # configs[0], the deeper variant (src/vggnet.py:148-151)
     "mobilenet": ("MobileNetV1", "", 256),      # configs[2]
     "shufflenet_g3": ("ShuffleNetV1", "g3", 256),   # configs[3]
     "resnext50": ("ResNeXt", "50", 128),        # configs[3]

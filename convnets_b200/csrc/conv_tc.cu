@@ -11,7 +11,7 @@
 //    (+bias, ReLU) -> bf16 -> swizzled smem -> TMA store into the NHWC output (a plain
 //    [M, K] matrix).  The same kernel computes data-grad: stride-1 dgrad is a forward conv of dy
 //    with the transposed filter; strided dgrad is decomposed by output parity class into stride-1
-//    sub-convolutions whose results are interleaved by a small scatter kernel.
+//    sub-convolutions whose epilogues scatter their rows to the class's pixels of dx.
 //  * conv_wgrad_tc_k : per tap, D[M = out-channels(128), N = in-channels(NT)] += dy^T x_tap with
 //    the GEMM-K dimension = output pixels; both operands are "MN-major" smem tiles
 //    ([64 pixels x 64 ch] TMA boxes), one TMEM accumulator per tap, split-K over pixel ranges
@@ -137,6 +137,10 @@ struct FpropParams {
   int grp_out, grp_in;  // grouped conv: output / reduction channels per group (0 = dense)
   int Kout;
   int flags;
+  // EPI == 3 (parity class of a strided data-grad): output pixel (n, i, j) of this launch is pixel
+  // (n, i * sc_sh + sc_a, j * sc_sw + sc_b) of the [N, sc_H, sc_W, Kout] tensor `scatter`
+  bf16* scatter;
+  int sc_H, sc_W, sc_sh, sc_sw, sc_a, sc_b;
   int16_t off_h[kMaxTaps], off_w[kMaxTaps];
   uint8_t widx[kMaxTaps];
 };
@@ -157,7 +161,9 @@ struct FpropParams {
 template <int BLOCK_N, int STAGES, bool IM2COL, int EPI>
 __global__ void __launch_bounds__(kPersistThreads, 1)
 conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
-  // EPI: 0 = bias / ReLU by flags, 1 = plain store, 2 = plain + addend (data-grad + skip gradient)
+  // EPI: 0 = bias / ReLU by flags, 1 = plain store, 2 = plain + addend (data-grad + skip gradient),
+  //      3 = plain, rows scattered to the strided pixel positions of a larger tensor (one parity
+  //          class of a strided data-grad writes dx directly: no compact copy, no interleave pass)
   constexpr bool PLAIN = EPI != 0;   // rows past the end of the tensor stay zero (no bias added)
   constexpr int B_TILE_BYTES = BLOCK_N * TILE_K * 2;
   constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
@@ -316,7 +322,7 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
       mbar_wait(&tmem_full_bar[buf], (lt >> 1) & 1);
       tc_fence_after();
       // the previous tile's TMA store must have finished READING the staging buffer
-      if (store_warp) {
+      if (EPI != 3 && store_warp) {
         if (elect_one()) tma_store_wait_read0();
         __syncwarp();
       }
@@ -379,7 +385,32 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
       mbar_arrive(&tmem_empty_bar[buf]);
       fence_proxy_async_smem();
       asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (store_warp) {
+      if (EPI == 3) {
+        // staged tile -> dx: a thread moves one 16-byte chunk of 4 pixel rows per 64-channel box; the 8
+        // lanes of a pixel write its 128 contiguous bytes, a warp 4 full lines.  The next tile's
+        // writers meet every reader at the bar.sync above before they touch the staging buffer.
+        const int chunk = et & 7, r0 = et >> 3;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int r = r0 + 32 * q;
+          const int m = m0 + r;
+          if (m < p.M) {
+            const int j = m % p.outQ;
+            const int t = m / p.outQ;
+            const int i = t % p.outP;
+            const int n = t / p.outP;
+            const int64_t pix = ((int64_t)n * p.sc_H + (i * p.sc_sh + p.sc_a)) * p.sc_W + (j * p.sc_sw + p.sc_b);
+            bf16* dst = p.scatter + pix * p.Kout + n0 + chunk * 8;
+#pragma unroll
+            for (int b = 0; b < BLOCK_N / 64; ++b) {
+              if (n0 + b * 64 + chunk * 8 < p.Kout) {
+                const uint4 v = lds_v4(st_base + b * (TILE_M * 128) + r * 128 + ((chunk ^ (r & 7)) << 4));
+                *reinterpret_cast<uint4*>(dst + b * 64) = v;
+              }
+            }
+          }
+        }
+      } else if (store_warp) {
         if (elect_one()) {
 #pragma unroll
           for (int b = 0; b < BLOCK_N / 64; ++b) {
@@ -411,7 +442,7 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
         as0 += s0; as1 += s1; aq0 += q0; aq1 += q1;  // two-level sum: per tile, then per CTA
       }
     }
-    if (store_warp) {
+    if (EPI != 3 && store_warp) {
       if (elect_one()) tma_store_wait0();
       __syncwarp();
     }
@@ -720,33 +751,22 @@ __global__ void transpose_filter_k(const bf16* __restrict__ w, bf16* __restrict_
   }
 }
 
-// Interleave the parity-class results of a strided dgrad into dx (zeros where no class has taps).
-struct ScatterP {
-  const bf16* src[16];  // per class compact [N, Ha, Wb, C] or nullptr
-  int Ha[16], Wb[16];
+// Strided data-grad: the parity classes that receive no filter tap (1x1 stride 2: three of four)
+// are zero; every other pixel of dx is written by its class's convolution (EPI == 3).
+struct ZeroClassP {
   int N, H, W, C, sh, sw;
+  uint32_t zero_mask;   // bit (a * sw + b): class (a, b) is all zeros
 };
-__global__ void dgrad_interleave_k(ScatterP p, bf16* __restrict__ dx) {
+__global__ void dgrad_zero_classes_k(ZeroClassP p, bf16* __restrict__ dx) {
   const int Cv = p.C / 8;
   const int64_t total = (int64_t)p.N * p.H * p.W * Cv;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
-    int cv = (int)(i % Cv);
-    int64_t pix = i / Cv;
-    int w = (int)(pix % p.W);
-    int64_t t = pix / p.W;
-    int h = (int)(t % p.H);
-    int n = (int)(t / p.H);
-    int a = h % p.sh, b = w % p.sw;
-    int cls = a * p.sw + b;
-    uint4 v = make_uint4(0, 0, 0, 0);
-    const bf16* s = p.src[cls];
-    if (s) {
-      int ii = h / p.sh, jj = w / p.sw;
-      v = *reinterpret_cast<const uint4*>(
-          s + (((int64_t)n * p.Ha[cls] + ii) * p.Wb[cls] + jj) * p.C + cv * 8);
-    }
-    *reinterpret_cast<uint4*>(dx + i * 8) = v;
+    const int64_t pix = i / Cv;
+    const int w = (int)(pix % p.W);
+    const int h = (int)((pix / p.W) % p.H);
+    const int cls = (h % p.sh) * p.sw + (w % p.sw);
+    if ((p.zero_mask >> cls) & 1u) *reinterpret_cast<uint4*>(dx + i * 8) = make_uint4(0, 0, 0, 0);
   }
 }
 
@@ -780,6 +800,8 @@ struct FpropLaunch {
   int flags;
   bool tiled2d;                  // pure GEMM: A is the [M, C] matrix itself
   int grp_out, grp_in, wC;       // grouped: out / reduction channels per group, expanded filter width
+  void* scatter;                 // strided data-grad class: the full dx tensor (EPI 3), else nullptr
+  int sc_H, sc_W, sc_sh, sc_sw, sc_a, sc_b;
 };
 
 // Persistent grid: a multiple of n_tiles (every CTA keeps one n-tile), at most one CTA per SM, and
@@ -847,11 +869,16 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
     uint32_t box[3] = {TILE_K, 1, (uint32_t)BLOCK_N};
     CNB_TRY(make_tiled_map(&prm.tmB, L.w, 3, dims, str, box, "B(weights)"));
   }
-  {
+  if (!L.scatter) {
     uint64_t dims[2] = {(uint64_t)L.Kout, (uint64_t)M};
     uint64_t str[1] = {(uint64_t)L.Kout * 2};
     uint32_t box[2] = {64, TILE_M};
     CNB_TRY(make_tiled_map(&prm.tmD, L.out, 2, dims, str, box, "D(output)"));
+  } else {
+    prm.tmD = prm.tmB;   // not used by the scattering epilogue; keep the prefetch target valid
+    prm.scatter = reinterpret_cast<bf16*>(L.scatter);
+    prm.sc_H = L.sc_H; prm.sc_W = L.sc_W; prm.sc_sh = L.sc_sh; prm.sc_sw = L.sc_sw;
+    prm.sc_a = L.sc_a; prm.sc_b = L.sc_b;
   }
   prm.bias = L.bias;
   prm.stats = L.stats;
@@ -878,6 +905,11 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
   const int epi = prm.flags == 0 ? 1 : (prm.flags == kConvAccum ? 2 : 0);
   CNB_REQUIRE(epi != 0 || !(prm.flags & kConvAccum), CNB_ERR_UNSUPPORTED,
               "conv_tc: the accumulating epilogue does not combine with bias / ReLU");
+  if (L.scatter) {
+    CNB_REQUIRE(epi == 1 && !L.tiled2d && !L.stats, CNB_ERR_UNSUPPORTED,
+                "conv_tc: the scattering epilogue is a plain im2col store");
+    return launch_fprop_bn<true, 3>(prm, BLOCK_N, st);
+  }
   if (L.tiled2d) {
     if (epi == 1) return launch_fprop_bn<false, 1>(prm, BLOCK_N, st);
     if (epi == 2) return launch_fprop_bn<false, 2>(prm, BLOCK_N, st);
@@ -1055,12 +1087,7 @@ size_t conv_tc_workspace(const cnb_conv_desc& d, int direction) {
     return d.groups > 1 ? align_up((size_t)d.K * d.R * d.S * grouped_width(d, 0) * 2, 1024) + 1024 : 0;
   if (direction == CNB_DGRAD) {
     size_t wt = dgrad_filter_bytes(d);
-    size_t tmp = 0;
-    if (d.stride_h != 1 || d.stride_w != 1) {
-      // compact per-class results: each at most ceil(H/sh)*ceil(W/sw) pixels
-      int Ha = (d.H + d.stride_h - 1) / d.stride_h, Wb = (d.W + d.stride_w - 1) / d.stride_w;
-      tmp = (size_t)d.stride_h * d.stride_w * align_up((size_t)d.N * Ha * Wb * d.C * 2, 1024);
-    }
+    const size_t tmp = 0;   // strided data-grad writes dx from the class convolutions' epilogues
     return wt + tmp + 1024;
   }
   int NT, tpc, tg, cit, cot, splits, pps;
@@ -1148,7 +1175,6 @@ int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const v
     CNB_TRY(check_launch("transpose_filter"));
     wt = wt_ws;
   }
-  uint8_t* tmp_base = reinterpret_cast<uint8_t*>(wt_ws) + dgrad_filter_bytes(d);
 
   if (d.stride_h == 1 && d.stride_w == 1) {
     FpropLaunch L;
@@ -1179,18 +1205,15 @@ int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const v
     return launch_fprop(L, st);
   }
 
-  // ---- strided: one stride-1 sub-convolution per output parity class (a, b)
-  ScatterP sp;
-  memset(&sp, 0, sizeof(sp));
-  sp.N = d.N; sp.H = d.H; sp.W = d.W; sp.C = d.C; sp.sh = d.stride_h; sp.sw = d.stride_w;
-  const int HaMax = (d.H + d.stride_h - 1) / d.stride_h, WbMax = (d.W + d.stride_w - 1) / d.stride_w;
-  const size_t cls_bytes = align_up((size_t)d.N * HaMax * WbMax * d.C * 2, 1024);
+  // ---- strided: one stride-1 sub-convolution per output parity class (a, b), each writing its
+  // pixels of dx directly; classes without a tap are zero-filled by one small kernel
+  CNB_REQUIRE(!addend, CNB_ERR_UNSUPPORTED, "conv_tc_dgrad: the addend epilogue is stride-1 only");
+  uint32_t zero_mask = 0;
   for (int a = 0; a < d.stride_h; ++a)
     for (int b = 0; b < d.stride_w; ++b) {
       const int cls = a * d.stride_w + b;
       const int Ha = (d.H - a + d.stride_h - 1) / d.stride_h;
       const int Wb = (d.W - b + d.stride_w - 1) / d.stride_w;
-      sp.Ha[cls] = Ha; sp.Wb[cls] = Wb; sp.src[cls] = nullptr;
       if (Ha <= 0 || Wb <= 0) continue;
       // taps of this class: (a + pad_h - r*dil_h) % sh == 0, offset dr = (...) / sh
       int drs[16], rr[16], nr = 0, dss[16], ss[16], ns = 0;
@@ -1208,7 +1231,7 @@ int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const v
           ss[ns++] = s;
         }
       }
-      if (nr == 0 || ns == 0) continue;  // class receives no contribution -> zeros
+      if (nr == 0 || ns == 0) { zero_mask |= 1u << cls; continue; }  // no contribution -> zeros
       int lo_h = drs[0], lo_w = dss[0];
       for (int i = 1; i < nr; ++i) lo_h = drs[i] < lo_h ? drs[i] : lo_h;
       for (int i = 1; i < ns; ++i) lo_w = dss[i] < lo_w ? dss[i] : lo_w;
@@ -1232,15 +1255,21 @@ int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const v
         }
       L.w = wt; L.Kout = d.C; L.RS = RS;
       if (grouped) { L.grp_out = Cg; L.grp_in = Kg; L.wC = wCd; }
-      bf16* tmp = reinterpret_cast<bf16*>(tmp_base + (size_t)cls * cls_bytes);
-      L.out = tmp; L.bias = nullptr; L.flags = 0;
+      L.out = nullptr; L.bias = nullptr; L.flags = 0;
       L.tiled2d = false;
+      L.scatter = dx;
+      L.sc_H = d.H; L.sc_W = d.W; L.sc_sh = d.stride_h; L.sc_sw = d.stride_w; L.sc_a = a; L.sc_b = b;
       CNB_TRY(launch_fprop(L, st));
-      sp.src[cls] = tmp;
     }
-  int64_t total = (int64_t)d.N * d.H * d.W * (d.C / 8);
-  dgrad_interleave_k<<<grid_for(total, 256), 256, 0, st>>>(sp, (bf16*)dx);
-  return check_launch("dgrad_interleave");
+  if (zero_mask) {
+    ZeroClassP zp;
+    zp.N = d.N; zp.H = d.H; zp.W = d.W; zp.C = d.C; zp.sh = d.stride_h; zp.sw = d.stride_w;
+    zp.zero_mask = zero_mask;
+    int64_t total = (int64_t)d.N * d.H * d.W * (d.C / 8);
+    dgrad_zero_classes_k<<<grid_for(total, 256), 256, 0, st>>>(zp, (bf16*)dx);
+    return check_launch("dgrad_zero_classes");
+  }
+  return CNB_OK;
 }
 
 template <int NT, int SA, int SB, bool IM2COL, int TS = 1>
