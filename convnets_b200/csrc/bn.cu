@@ -79,6 +79,7 @@ struct BnFwdFin {
   const float* gamma; const float* beta;
   float* rmean; float* rvar; float* save_mean; float* save_rstd; float* scale; float* shift;
   float eps, momentum;
+  long long* nbt;   // num_batches_tracked (may be null): +1 per training forward, by channel 0's thread
 };
 struct BnBwdFin {
   const float* gamma; const float* rstd;
@@ -198,6 +199,7 @@ __device__ __forceinline__ void bn_finish_fwd(int c, double S, double Q, double 
   const float mu = (float)mean;
   f.save_mean[c] = mu;
   f.save_rstd[c] = rstd;
+  if (f.nbt && c == 0) *f.nbt += 1;
   if (f.rmean) f.rmean[c] = (1.f - f.momentum) * f.rmean[c] + f.momentum * mu;
   if (f.rvar) {
     double unbiased = M > 1 ? var * (double)M / (double)(M - 1) : var;
@@ -973,7 +975,7 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
   CNB_REQUIRE(!relu_mask || v == 8, CNB_ERR_INVALID,
               "cnb_bn_fwd_train: relu_mask needs 16-byte aligned tensors");
   BnFwdFin fin{gamma, beta, running_mean, running_var, save_mean, save_rstd, nullptr, nullptr,
-               d->eps, d->momentum};
+               d->eps, d->momentum, (long long*)d->num_batches_tracked};
   float* part = (float*)workspace;
   float* scale;
   if (conv_partials) {

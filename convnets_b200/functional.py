@@ -458,7 +458,7 @@ def conv2d_uses_tc(x_shape, w_shape, stride, padding, dilation, groups, dtype, d
 class _BatchNormFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps,
-                relu, partials):
+                relu, partials, nbt=None):
         _cuda(x, residual, gamma, beta)
         lib = _L.load()
         x = _nhwc(x)
@@ -468,7 +468,10 @@ class _BatchNormFn(torch.autograd.Function):
             residual = _nhwc(residual)
             if residual.shape != x.shape or residual.dtype != x.dtype:
                 raise RuntimeError("batch_norm: residual must match x in shape and dtype")
-        d = _L.BnDesc(n * h * w, c, _dt(x), flags, float(eps), float(momentum))
+        if nbt is not None and (not training or not nbt.is_cuda or nbt.dtype != torch.int64):
+            raise RuntimeError("batch_norm: num_batches_tracked must be a CUDA int64 scalar (training only)")
+        d = _L.BnDesc(n * h * w, c, _dt(x), flags, float(eps), float(momentum),
+                      None if nbt is None else nbt.data_ptr())
         y = torch.empty_like(x, memory_format=_CL)
         ws = _workspace(lib.cnb_bn_workspace_bytes(C.byref(d)), x.device)
         g32 = None if gamma is None else gamma.detach()
@@ -526,16 +529,18 @@ class _BatchNormFn(torch.autograd.Function):
         _L.check(lib.cnb_bn_bwd(C.byref(d), _p(x), _p(y), _p(mask), _p(dy), _p(gamma), _p(mean),
                                 _p(rstd), _p(dx), _p(dres), _p(dgamma), _p(dbeta), _p(ws), ws.numel(),
                                 _stream()), "cnb_bn_bwd")
-        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None
 
 
 def batch_norm(x, gamma, beta, running_mean, running_var, training, momentum=0.1, eps=1e-5,
-               relu=False, residual=None, partials=None):
+               relu=False, residual=None, partials=None, num_batches_tracked=None):
     """Drop-in for F.batch_norm on NCHW feature maps (+ optional fused residual add / ReLU).
-    `partials`: the per-tile sums the producing conv2d(..., bn_stats=True) emitted for x."""
+    `partials`: the per-tile sums the producing conv2d(..., bn_stats=True) emitted for x.
+    `num_batches_tracked`: the module's int64 counter; the statistics epilogue adds 1 to it."""
     return _BatchNormFn.apply(x, residual, gamma, beta, running_mean, running_var, bool(training),
                               float(momentum), float(eps), bool(relu),
-                              partials if training else None)
+                              partials if training else None,
+                              num_batches_tracked if training else None)
 
 
 # ----------------------------------------------------------------------------- element-wise

@@ -249,16 +249,20 @@ class BatchNorm2d(nn.BatchNorm2d):
                 return F_.add_relu(x, residual) if r else F_.add(x, residual)
             return F_.relu(x) if (r and not self.fuse_relu) else x
         momentum = 0.0 if self.momentum is None else self.momentum
+        nbt = None
         if self.training and self.track_running_stats and self.num_batches_tracked is not None:
-            self.num_batches_tracked.add_(1)
-            if self.momentum is None:
-                momentum = 1.0 / float(self.num_batches_tracked)
+            if self.momentum is None or not self.num_batches_tracked.is_cuda:
+                self.num_batches_tracked.add_(1)
+                if self.momentum is None:   # cumulative average: the factor is read on the host
+                    momentum = 1.0 / float(self.num_batches_tracked)
+            else:
+                nbt = self.num_batches_tracked   # +1 inside the statistics epilogue (no extra launch)
         rm = self.running_mean if (not training or self.track_running_stats) else None
         rv = self.running_var if (not training or self.track_running_stats) else None
         partials = getattr(x, "_cnb_bn_partials", None) if training else None
         return F_.batch_norm(x, self.weight, self.bias, rm, rv, training, momentum, self.eps,
                              relu=self.fuse_relu if relu is None else relu, residual=residual,
-                             partials=partials)
+                             partials=partials, num_batches_tracked=nbt)
 
 
 class ReLU(nn.ReLU):

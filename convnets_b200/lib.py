@@ -31,7 +31,7 @@ class PoolDesc(C.Structure):
 
 class BnDesc(C.Structure):
     _fields_ = [("M", C.c_int64), ("C", C.c_int32), ("dtype", C.c_int32), ("flags", C.c_int32),
-                ("eps", C.c_float), ("momentum", C.c_float)]
+                ("eps", C.c_float), ("momentum", C.c_float), ("num_batches_tracked", C.c_void_p)]
 
 
 class PackItem(C.Structure):

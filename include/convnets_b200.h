@@ -87,6 +87,9 @@ typedef struct cnb_bn_desc {
   int32_t flags;
   float eps;
   float momentum;
+  /* nn.BatchNorm2d.num_batches_tracked (device int64 scalar, may be NULL): the training forward adds 1
+   * in its statistics epilogue, so the module's per-layer `add_(1)` launch disappears */
+  int64_t* num_batches_tracked;
 } cnb_bn_desc;
 
 /* ---- library ------------------------------------------------------------------------- */
