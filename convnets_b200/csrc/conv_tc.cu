@@ -220,6 +220,8 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
   // -channel 3x3 layers with 84 % of the MMA warp's samples inside its own issue loop).
   if (warp == 0) {
     // ===================== TMA producer =====================
+    // every per-tile / per-tap value goes through uni(): the compiler then keeps it in a uniform
+    // register for the whole inner loop instead of moving it there (R2UR) once per k-block
     const int a_c0 = p.grp_out > 0 ? (n0 / p.grp_out) * p.grp_in : 0;
     const uint32_t smem0 = smem_u32(smem), full0 = smem_u32(full_bar), empty0 = smem_u32(empty_bar);
     uint32_t s = 0, ph = 1;   // ring slot and the parity a free slot shows
@@ -230,13 +232,13 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
         int j = m0 % p.outQ;
         int t = m0 / p.outQ;
         int i = t % p.outP;
-        bn = t / p.outP;
-        bh = p.lower_h + i * p.trav_h;
-        bw = p.lower_w + j * p.trav_w;
+        bn = uni(t / p.outP);
+        bh = uni(p.lower_h + i * p.trav_h);
+        bw = uni(p.lower_w + j * p.trav_w);
       }
       for (int tap = 0; tap < p.num_taps; ++tap) {
-        const int widx = (int)p.widx[tap];
-        const uint16_t ow = (uint16_t)p.off_w[tap], oh = (uint16_t)p.off_h[tap];
+        const int widx = uni((int)p.widx[tap]);
+        const uint32_t offs = uni((uint32_t)(uint16_t)p.off_w[tap] | ((uint32_t)(uint16_t)p.off_h[tap] << 16));
         for (int cb = 0; cb < p.num_cblk; ++cb) {
           mbar_wait_u32(empty0 + s * 8, ph);
           if (elect_one()) {
@@ -244,7 +246,8 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
             const uint32_t fb = full0 + s * 8;
             mbar_expect_tx_u32(fb, STAGE_BYTES);
             if (IM2COL)
-              tma_load_im2col_4d_u32(&p.tmA, fb, sa, a_c0 + cb * TILE_K, bw, bh, bn, ow, oh);
+              tma_load_im2col_4d_u32(&p.tmA, fb, sa, a_c0 + cb * TILE_K, bw, bh, bn, (uint16_t)(offs & 0xffff),
+                                     (uint16_t)(offs >> 16));
             else
               tma_load_2d_u32(&p.tmA, fb, sa, a_c0 + cb * TILE_K, m0);
             tma_load_3d_u32(&p.tmB, fb, sa + A_TILE_BYTES, cb * TILE_K, widx, n0);

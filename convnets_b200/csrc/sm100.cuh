@@ -14,6 +14,11 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// warp-uniform value made KNOWN to be uniform (lane 0's copy): lets the compiler keep it in a
+// uniform register across a loop
+__device__ __forceinline__ int uni(int v) { return __shfl_sync(0xffffffffu, v, 0); }
+__device__ __forceinline__ uint32_t uni(uint32_t v) { return __shfl_sync(0xffffffffu, v, 0); }
+
 __device__ __forceinline__ uint32_t elect_one() {
   uint32_t pred = 0;
   asm volatile(
