@@ -158,7 +158,13 @@ struct FpropParams {
 //   grouped convolutions (p.grp_out > 0): the n-tile selects the input-channel slice it reads
 //           (a_c0) and the filter operand is the block-diagonal expansion built by
 //           expand_grouped_filter_k, see "grouped convolutions" below.
-template <int BLOCK_N, int STAGES, bool IM2COL, int EPI>
+//   BRES  : the CTA's whole filter slice (its n-tile x every tap x every channel block, at most
+//           kBresIters tiles) is loaded ONCE and stays in shared memory; the ring then carries the
+//           activation tile only.  A persistent CTA never changes its n-tile, and a 64-channel
+//           3x3 layer re-fetched 8 KB of filter next to every 16 KB activation tile — a third of
+//           the L2 -> SM traffic that bounds these layers (~50 B / clk / SM, ncu r02c).
+constexpr int kBresIters = 9;
+template <int BLOCK_N, int STAGES, bool IM2COL, int EPI, bool BRES = false>
 __global__ void __launch_bounds__(kPersistThreads, 1)
 conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
   // EPI: 0 = bias / ReLU by flags, 1 = plain store, 2 = plain + addend (data-grad + skip gradient),
@@ -166,19 +172,22 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
   //          class of a strided data-grad writes dx directly: no compact copy, no interleave pass)
   constexpr bool PLAIN = EPI != 0;   // rows past the end of the tensor stay zero (no bias added)
   constexpr int B_TILE_BYTES = BLOCK_N * TILE_K * 2;
-  constexpr int STAGE_BYTES = A_TILE_BYTES + B_TILE_BYTES;
+  constexpr int STAGE_BYTES = BRES ? A_TILE_BYTES : A_TILE_BYTES + B_TILE_BYTES;
+  constexpr int BRES_BYTES = BRES ? kBresIters * B_TILE_BYTES : 0;
   constexpr int OUT_BYTES = TILE_M * BLOCK_N * 2;
   constexpr uint32_t TMEM_COLS = 2 * BLOCK_N < 32 ? 32 : 2 * BLOCK_N;
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~(uintptr_t)1023);
-  uint8_t* stage_out = smem + STAGES * STAGE_BYTES;
+  uint8_t* bres = smem + STAGES * STAGE_BYTES;   // resident filter tiles, k-block order (BRES)
+  uint8_t* stage_out = bres + BRES_BYTES;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(stage_out + OUT_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full_bar = empty_bar + STAGES;   // [2]
   uint64_t* tmem_empty_bar = tmem_full_bar + 2;   // [2]
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_empty_bar + 2);
+  uint64_t* bres_bar = tmem_empty_bar + 2;        // [1]
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bres_bar + 1);
 
   const int warp = threadIdx.x / 32;
   const int lane = threadIdx.x % 32;
@@ -200,6 +209,7 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
       mbar_init(&tmem_full_bar[b], 1);
       mbar_init(&tmem_empty_bar[b], kPersistThreads - 64);
     }
+    mbar_init(bres_bar, 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -225,6 +235,17 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
     const int a_c0 = p.grp_out > 0 ? (n0 / p.grp_out) * p.grp_in : 0;
     const uint32_t smem0 = smem_u32(smem), full0 = smem_u32(full_bar), empty0 = smem_u32(empty_bar);
     uint32_t s = 0, ph = 1;   // ring slot and the parity a free slot shows
+    if (BRES) {
+      if (elect_one()) {
+        const uint32_t bb = smem_u32(bres_bar);
+        mbar_expect_tx_u32(bb, (uint32_t)num_iters * B_TILE_BYTES);
+        uint32_t dst = smem_u32(bres);
+        for (int tap = 0; tap < p.num_taps; ++tap)
+          for (int cb = 0; cb < p.num_cblk; ++cb, dst += B_TILE_BYTES)
+            tma_load_3d_u32(&p.tmB, bb, dst, cb * TILE_K, (int)p.widx[tap], n0);
+      }
+      __syncwarp();
+    }
     for (int mt = m_first; mt < p.m_tiles; mt += m_step) {
       const int m0 = mt * TILE_M;
       int bn = 0, bh = 0, bw = 0;
@@ -250,7 +271,7 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
                                      (uint16_t)(offs >> 16));
             else
               tma_load_2d_u32(&p.tmA, fb, sa, a_c0 + cb * TILE_K, m0);
-            tma_load_3d_u32(&p.tmB, fb, sa + A_TILE_BYTES, cb * TILE_K, widx, n0);
+            if (!BRES) tma_load_3d_u32(&p.tmB, fb, sa + A_TILE_BYTES, cb * TILE_K, widx, n0);
           }
           __syncwarp();
           if (++s == STAGES) { s = 0; ph ^= 1; }
@@ -265,7 +286,9 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
     const uint32_t tfull0 = smem_u32(tmem_full_bar), tempty0 = smem_u32(tmem_empty_bar);
     // descriptor low words (start address >> 4) of slot 0's A / B tiles; + STAGE_BYTES/16 per slot,
     // + 2 per 16-element k-step.  The high word (SBO 1024, version 1, SWIZZLE_128B) is a constant.
-    const uint32_t a_lo0 = (smem_u32(smem) >> 4), b_lo0 = ((smem_u32(smem) + A_TILE_BYTES) >> 4);
+    const uint32_t a_lo0 = (smem_u32(smem) >> 4);
+    const uint32_t b_lo0 = BRES ? (smem_u32(bres) >> 4) : ((smem_u32(smem) + A_TILE_BYTES) >> 4);
+    if (BRES) mbar_wait_u32(smem_u32(bres_bar), 0);   // the filter slice has landed (once per kernel)
     constexpr uint32_t DESC_HI = (1024u >> 4) | (1u << 14) | (2u << 29);
     uint32_t s = 0, ph = 0, lt = 0;
     for (int mt = m_first; mt < p.m_tiles; mt += m_step, ++lt) {
@@ -277,7 +300,8 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
         mbar_wait_u32(full0 + s * 8, ph);
         tc_fence_after();
         if (elect_one()) {
-          const uint32_t a_lo = a_lo0 + s * (STAGE_BYTES >> 4), b_lo = b_lo0 + s * (STAGE_BYTES >> 4);
+          const uint32_t a_lo = a_lo0 + s * (STAGE_BYTES >> 4);
+          const uint32_t b_lo = b_lo0 + (BRES ? (uint32_t)k_it * (B_TILE_BYTES >> 4) : s * (STAGE_BYTES >> 4));
 #pragma unroll
           for (int k = 0; k < TILE_K / 16; ++k)
             umma_bf16_lohi(acc, a_lo + 2 * k, b_lo + 2 * k, DESC_HI, idesc, (k_it | k) != 0 ? 1u : 0u);
@@ -821,14 +845,14 @@ static int fprop_block_n(int Kout, bool grouped) {
   return Kout <= 64 ? 64 : (Kout <= 128 ? 128 : 256);
 }
 
-template <int BLOCK_N, int STAGES, bool IM2COL, int EPI>
+template <int BLOCK_N, int STAGES, bool IM2COL, int EPI, bool BRES = false>
 static int launch_fprop_persist_inst(const FpropParams& prm, cudaStream_t st) {
-  constexpr int STAGE_BYTES = A_TILE_BYTES + BLOCK_N * TILE_K * 2;
-  constexpr size_t smem = (size_t)STAGES * STAGE_BYTES + (size_t)TILE_M * BLOCK_N * 2 +
-                          (2 * STAGES + 4) * 8 + 16 + 1024;
+  constexpr int STAGE_BYTES = BRES ? A_TILE_BYTES : A_TILE_BYTES + BLOCK_N * TILE_K * 2;
+  constexpr size_t smem = (size_t)STAGES * STAGE_BYTES + (BRES ? (size_t)kBresIters * BLOCK_N * TILE_K * 2 : 0) +
+                          (size_t)TILE_M * BLOCK_N * 2 + (2 * STAGES + 5) * 8 + 16 + 1024;
   static_assert(smem <= 232448, "exceeds the 227 KB dynamic shared memory limit");
   static bool attr_done = false;
-  auto kern = conv_fprop_tc_persist_k<BLOCK_N, STAGES, IM2COL, EPI>;
+  auto kern = conv_fprop_tc_persist_k<BLOCK_N, STAGES, IM2COL, EPI, BRES>;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cudaFuncSetAttribute(fprop persistent): %s",
@@ -840,8 +864,20 @@ static int launch_fprop_persist_inst(const FpropParams& prm, cudaStream_t st) {
   return check_launch("conv_fprop_tc_persist");
 }
 
+// CNB_BRES=0 keeps the filter tiles in the ring (the r02c kernels) for A/B measurements
+static bool bres_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("CNB_BRES");
+    v = (e && atoi(e) == 0) ? 0 : 1;
+  }
+  return v == 1;
+}
+
 template <bool IM2COL, int EPI>
 static int launch_fprop_bn(const FpropParams& prm, int BLOCK_N, cudaStream_t st) {
+  if (BLOCK_N == 64 && prm.num_taps * prm.num_cblk <= kBresIters && bres_enabled())
+    return launch_fprop_persist_inst<64, 8, IM2COL, EPI, true>(prm, st);
   if (BLOCK_N == 64) return launch_fprop_persist_inst<64, 8, IM2COL, EPI>(prm, st);
   if (BLOCK_N == 128) return launch_fprop_persist_inst<128, 5, IM2COL, EPI>(prm, st);
   return launch_fprop_persist_inst<256, 3, IM2COL, EPI>(prm, st);
@@ -946,6 +982,15 @@ static int grouped_span(int out_total, int out_per_g, int in_per_g, int tile) {
   return mx;
 }
 
+// The A operand's channel coordinate of an n-tile starts at g_lo * in_per_g.  TMA needs the first
+// byte of every box row 16-byte aligned, i.e. that coordinate a multiple of 8 bf16 elements
+// (ShuffleNet-v1 g = 4: 68 channels per group -> 136-byte starts -> "illegal instruction").
+static bool grouped_starts_aligned(int out_total, int out_per_g, int in_per_g, int tile) {
+  for (int n0 = 0; n0 < out_total; n0 += tile)
+    if (((n0 / out_per_g) * in_per_g) % 8 != 0) return false;
+  return true;
+}
+
 constexpr int kGroupTileN = 64;     // fprop / dgrad n-tile of the grouped path
 constexpr int kGroupMaxWidth = 1024; // widest expanded reduction slice
 
@@ -1019,6 +1064,11 @@ bool conv_tc_supported(const cnb_conv_desc& d, int direction, const char** why) 
     if (direction != CNB_WGRAD && grouped_width(d, direction == CNB_DGRAD) > kGroupMaxWidth) {
       *why = "grouped convolution: channel slice wider than 1024"; return false;
     }
+    const int Cg = d.C / d.groups, Kg = d.K / d.groups;
+    const bool ok = direction == CNB_FWD     ? grouped_starts_aligned(d.K, Kg, Cg, kGroupTileN)
+                    : direction == CNB_DGRAD ? grouped_starts_aligned(d.C, Cg, Kg, kGroupTileN)
+                                             : grouped_starts_aligned(d.K, Kg, Cg, TILE_M);
+    if (!ok) { *why = "grouped convolution: a tile's channel slice does not start on a 16-byte boundary"; return false; }
   }
   if (d.R * d.S > kMaxTaps) { *why = "more than 49 filter taps"; return false; }
   int P, Q;

@@ -58,6 +58,12 @@ def test_descriptor_validation_without_a_gpu(lib):
     assert h.cnb_conv2d_uses_tc(C.byref(d), lib.CNB_FWD) == 1
     d.groups = 32  # grouped (2 -> 4 channels per group): tensor cores on a block-diagonal filter
     assert h.cnb_conv2d_uses_tc(C.byref(d), lib.CNB_FWD) == 1
+    # ShuffleNet-v1 g = 4 (68 channels per group): a tile's channel slice would start 136 bytes into a
+    # pixel row, which TMA cannot address -> CUDA cores, in every direction that has the problem
+    g4 = lib.ConvDesc(8, 4, 4, 272, 136, 1, 1, 1, 1, 0, 0, 1, 1, 4, lib.CNB_BF16, 0, lib.CNB_ALGO_AUTO)
+    assert [h.cnb_conv2d_uses_tc(C.byref(g4), k) for k in (lib.CNB_FWD, lib.CNB_DGRAD, lib.CNB_WGRAD)] == [0, 0, 0]
+    g3 = lib.ConvDesc(8, 4, 4, 240, 240, 1, 1, 1, 1, 0, 0, 1, 1, 3, lib.CNB_BF16, 0, lib.CNB_ALGO_AUTO)
+    assert [h.cnb_conv2d_uses_tc(C.byref(g3), k) for k in (lib.CNB_FWD, lib.CNB_DGRAD, lib.CNB_WGRAD)] == [1, 1, 1]
     d.dtype = lib.CNB_F32  # fp32-IO mode -> CUDA cores
     assert h.cnb_conv2d_uses_tc(C.byref(d), lib.CNB_FWD) == 0
     d.dtype = lib.CNB_BF16

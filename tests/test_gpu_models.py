@@ -37,6 +37,7 @@ CASES = [
     ("DenseNet", "121", 64, 8),
     ("MobileNetV1", "", 64, 8),
     ("ShuffleNetV1", "g3", 64, 8),
+    ("ShuffleNetV1", "g4", 32, 8),     # 68 / 136 / 272 channels per group: no 16-byte aligned channel slices
     ("SEResNet", "50", 64, 8),
     ("SENet", "26", 64, 8),
     ("SKResNet", "26", 64, 8),
