@@ -157,7 +157,8 @@ int conv_bias_grad(const cnb_conv_desc& d, const void* dy, float* dbias, cudaStr
 // dwconv.cu
 bool is_depthwise(const cnb_conv_desc& d);
 int dwconv_fwd(const cnb_conv_desc& d, const void* x, const void* w, const float* bias, void* y,
-               cudaStream_t st);
+               float* bn_partials, cudaStream_t st);
+int dwconv_stats_rows(const cnb_conv_desc& d);
 int dwconv_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, void* dx, cudaStream_t st);
 int dwconv_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* dw, void* ws,
                  size_t ws_bytes, cudaStream_t st);

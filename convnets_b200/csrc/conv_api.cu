@@ -74,7 +74,7 @@ size_t cnb_conv2d_workspace_bytes(const cnb_conv_desc* d, int direction) {
 
 int cnb_conv2d_bn_partial_rows(const cnb_conv_desc* d) {
   CNB_TRY(validate_conv(d, "cnb_conv2d_bn_partial_rows"));
-  if (is_depthwise(*d)) return 0;
+  if (is_depthwise(*d)) return dwconv_stats_rows(*d);
   int a = pick_algo(*d, CNB_FWD, "cnb_conv2d_bn_partial_rows");
   if (a < 0) return a;
   return a == 1 ? conv_tc_stats_rows(*d) : 0;
@@ -89,8 +89,7 @@ int cnb_conv2d_fwd(const cnb_conv_desc* d, const void* x, const void* w, const f
   cudaStream_t st = (cudaStream_t)stream;
   if (is_depthwise(*d)) {
     CNB_REQUIRE(d->algo != CNB_ALGO_TC, CNB_ERR_UNSUPPORTED, "cnb_conv2d_fwd: depthwise has no TC path");
-    CNB_REQUIRE(!bn_partials, CNB_ERR_UNSUPPORTED, "cnb_conv2d_fwd: bn_partials on a depthwise conv");
-    return dwconv_fwd(*d, x, w, bias, y, st);
+    return dwconv_fwd(*d, x, w, bias, y, bn_partials, st);
   }
   int a = pick_algo(*d, CNB_FWD, "cnb_conv2d_fwd");
   if (a < 0) return a;

@@ -201,14 +201,50 @@ struct DwS {
 
 // out(oh, q) = sum_{r,s} in(oh*STRIDE - 1 + r, q*STRIDE - 1 + s) * w[r][s]   (FLIP: w[2-r][2-s],
 // which with STRIDE == 1 is exactly the data gradient of the pad-1 convolution)
-template <typename T, int STRIDE, bool FLIP, int TQ = kDwTQ>
+// STATS: the kernel also emits, per CTA row (blockIdx.y), the per-channel sums of the STORED
+// outputs and of their squares — the same [rows][2][C] table the tensor-core conv epilogue writes —
+// so a BatchNorm2d that follows the depthwise conv (Conv2dBlockDW, reference
+// src/mobilenet_v1.py:90-125; ShuffleUnit, src/shufflenet_v1.py:119-141) does not re-read the tensor
+// for its statistics.  Threads keep their sums for their whole lifetime, the CTA combines its strip
+// lanes through shared memory in fixed order (deterministic).
+template <int V>
+__device__ __forceinline__ void dw_emit_stats(const float (&ss)[V], const float (&sq)[V], float* red,
+                                              float* __restrict__ stats, int C, int c0, bool active) {
+  float* mine = red + ((size_t)threadIdx.y * blockDim.x + threadIdx.x) * 2 * V;
+#pragma unroll
+  for (int j = 0; j < V; ++j) { mine[j] = ss[j]; mine[V + j] = sq[j]; }
+  __syncthreads();
+  if (threadIdx.y == 0 && active) {
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      float S = 0.f, Q = 0.f;
+      for (int y = 0; y < (int)blockDim.y; ++y) {
+        const float* r = red + ((size_t)y * blockDim.x + threadIdx.x) * 2 * V;
+        S += r[j];
+        Q += r[V + j];
+      }
+      stats[((int64_t)blockIdx.y * 2 + 0) * C + c0 + j] = S;
+      stats[((int64_t)blockIdx.y * 2 + 1) * C + c0 + j] = Q;
+    }
+  }
+}
+
+template <typename T, int STRIDE, bool FLIP, int TQ = kDwTQ, bool STATS = false>
 __global__ void __launch_bounds__(256, sizeof(T) == 2 ? 2 : 1)
 dw3x3_strip_k(const T* __restrict__ in, const T* __restrict__ w, const float* __restrict__ bias,
-              T* __restrict__ out, DwS p) {
+              T* __restrict__ out, DwS p, float* __restrict__ stats = nullptr) {
   constexpr int V = kDwV;
   constexpr int NCOL = TQ * STRIDE + 3 - STRIDE;
+  extern __shared__ float dw_red[];
   const int cv = blockIdx.x * blockDim.x + threadIdx.x;
-  if (cv >= p.cv_total) return;
+  const bool active = cv < p.cv_total;
+  float ss[V], sq[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) ss[j] = sq[j] = 0.f;
+  if (!active) {
+    if (STATS) dw_emit_stats<V>(ss, sq, dw_red, stats, p.C, 0, false);
+    return;
+  }
   const int c0 = cv * V;
   float wr[9][V];
 #pragma unroll
@@ -270,11 +306,17 @@ dw3x3_strip_k(const T* __restrict__ in, const T* __restrict__ w, const float* __
           float f = acc[q][j];
           if (relu) f = (f > 0.f || f != f) ? f : 0.f;
           o.v[j] = from_f<T>(f);
+          if (STATS) {
+            const float r = to_f(o.v[j]);
+            ss[j] += r;
+            sq[j] = fmaf(r, r, sq[j]);
+          }
         }
         st_pack<T, V>(ob + (int64_t)q * p.C, o);
       }
     }
   }
+  if (STATS) dw_emit_stats<V>(ss, sq, dw_red, stats, p.C, c0, true);
 }
 
 // Stride-1 column walk (bf16): a thread owns 4 channels x 4 output columns and walks kDwRH output
@@ -283,14 +325,22 @@ dw3x3_strip_k(const T* __restrict__ in, const T* __restrict__ w, const float* __
 // requested before the current output row is computed.  Units = (image, row block, column strip).
 constexpr int kDwRH = 8;
 
-template <typename T, bool FLIP>
+template <typename T, bool FLIP, bool STATS = false>
 __global__ void __launch_bounds__(128, 3)
 dw3x3_s1_walk_k(const T* __restrict__ in, const T* __restrict__ w, const float* __restrict__ bias,
-                T* __restrict__ out, DwS p, int row_blocks) {
+                T* __restrict__ out, DwS p, int row_blocks, float* __restrict__ stats = nullptr) {
   constexpr int V = kDwV;
   constexpr int NCOL = kDwTQ + 2;
+  extern __shared__ float dw_red[];
   const int cv = blockIdx.x * blockDim.x + threadIdx.x;
-  if (cv >= p.cv_total) return;
+  const bool active = cv < p.cv_total;
+  float ss[V], sq[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) ss[j] = sq[j] = 0.f;
+  if (!active) {
+    if (STATS) dw_emit_stats<V>(ss, sq, dw_red, stats, p.C, 0, false);
+    return;
+  }
   const int c0 = cv * V;
   float wr[9][V];
 #pragma unroll
@@ -360,6 +410,11 @@ dw3x3_s1_walk_k(const T* __restrict__ in, const T* __restrict__ w, const float* 
               float f = acc[q][j];
               if (relu) f = (f > 0.f || f != f) ? f : 0.f;
               o.v[j] = from_f<T>(f);
+              if (STATS) {
+                const float r = to_f(o.v[j]);
+                ss[j] += r;
+                sq[j] = fmaf(r, r, sq[j]);
+              }
             }
             st_pack<T, V>(ob + ((int64_t)oh * p.OW + q) * p.C, o);
           }
@@ -367,6 +422,7 @@ dw3x3_s1_walk_k(const T* __restrict__ in, const T* __restrict__ w, const float* 
       }
     }
   }
+  if (STATS) dw_emit_stats<V>(ss, sq, dw_red, stats, p.C, c0, true);
 }
 
 // data gradient of the stride-2 / pad-1 3x3 depthwise conv: a strip of 4 dx columns (w0 % 4 == 0)
@@ -608,35 +664,83 @@ size_t dwconv_wgrad_ws(const cnb_conv_desc& d) {
   return (size_t)splits * d.C * d.R * d.S * sizeof(float) + 256;
 }
 
+// launch shape of the forward strip / walk kernels (also the number of BatchNorm partial rows)
+struct DwFwdPlan { DwS q; DwStripGeom g; bool walk; int rbs; int tq; };
+static DwFwdPlan dw_fwd_plan(const cnb_conv_desc& d, const float* bias) {
+  DwP p = make_dw(d);
+  DwFwdPlan f;
+  f.q = DwS{p.N, p.H, p.W, p.P, p.Q, p.C, p.C / kDwV, (int)ceil_div(p.Q, kDwTQ), 0,
+            d.flags & (((d.flags & CNB_CONV_BIAS) && bias ? CNB_CONV_BIAS : 0) | CNB_CONV_RELU)};
+  f.q.total_strips = (int64_t)p.N * p.P * f.q.strips_per_row;
+  f.walk = d.stride_h == 1 && d.dtype == CNB_BF16 && dw_walk_enabled();
+  f.rbs = 0;
+  f.tq = kDwTQ;
+  if (f.walk) {
+    f.rbs = (int)ceil_div(p.P, kDwRH);
+    f.g = dw_strip_geom(f.q.cv_total, (int64_t)p.N * f.rbs * f.q.strips_per_row, 12, 128);
+  } else if (d.stride_h == 1) {
+    f.g = dw_strip_geom(f.q.cv_total, f.q.total_strips, 8);
+  } else {
+    // stride 2: strips of 2 outputs (3 x 5 input vectors) keep two CTAs per SM resident
+    f.tq = 2;
+    f.q.strips_per_row = (int)ceil_div(p.Q, 2);
+    f.q.total_strips = (int64_t)p.N * p.P * f.q.strips_per_row;
+    f.g = dw_strip_geom(f.q.cv_total, f.q.total_strips, 8);
+  }
+  return f;
+}
+
+// rows of the BatchNorm partial table the forward kernel would emit (0: this shape takes the
+// generic kernel, which emits none); pointer alignment is assumed (checked at launch)
+int dwconv_stats_rows(const cnb_conv_desc& d) {
+  static int enabled = -1;   // CNB_DW_STATS=0: BatchNorm computes its own statistics (A/B measurement)
+  if (enabled < 0) {
+    const char* e = getenv("CNB_DW_STATS");
+    enabled = (e && e[0] == '0') ? 0 : 1;
+  }
+  if (!enabled) return 0;
+  if (!(d.R == 3 && d.S == 3 && d.pad_h == 1 && d.pad_w == 1 && d.dil_h == 1 && d.dil_w == 1 &&
+        d.stride_h == d.stride_w && (d.stride_h == 1 || d.stride_h == 2) && d.C % kDwV == 0))
+    return 0;
+  return (int)dw_fwd_plan(d, nullptr).g.grid.y;
+}
+
 int dwconv_fwd(const cnb_conv_desc& d, const void* x, const void* w, const float* bias, void* y,
-               cudaStream_t st) {
+               float* stats, cudaStream_t st) {
   DwP p = make_dw(d);
   if (dw_strip_ok(d, x, y)) {
-    const int v = kDwV;
-    DwS q{p.N, p.H, p.W, p.P, p.Q, p.C, p.C / v, (int)ceil_div(p.Q, kDwTQ), 0,
-          d.flags & (((d.flags & CNB_CONV_BIAS) && bias ? CNB_CONV_BIAS : 0) | CNB_CONV_RELU)};
-    q.total_strips = (int64_t)p.N * p.P * q.strips_per_row;
-    DwStripGeom g = dw_strip_geom(q.cv_total, q.total_strips, 8);
-    if (d.stride_h == 1 && d.dtype == CNB_BF16 && dw_walk_enabled()) {
-      const int rbs = (int)ceil_div(p.P, kDwRH);
-      DwStripGeom gw = dw_strip_geom(q.cv_total, (int64_t)p.N * rbs * q.strips_per_row, 12, 128);
-      dw3x3_s1_walk_k<bf16, false><<<gw.grid, gw.block, 0, st>>>((const bf16*)x, (const bf16*)w, bias,
-                                                                 (bf16*)y, q, rbs);
+    DwFwdPlan f = dw_fwd_plan(d, bias);
+    const DwS& q = f.q;
+    const DwStripGeom& g = f.g;
+    const size_t red = stats ? (size_t)g.block.x * g.block.y * 2 * kDwV * sizeof(float) : 0;
+    if (f.walk) {
+      if (stats)
+        dw3x3_s1_walk_k<bf16, false, true><<<g.grid, g.block, red, st>>>((const bf16*)x, (const bf16*)w, bias,
+                                                                         (bf16*)y, q, f.rbs, stats);
+      else
+        dw3x3_s1_walk_k<bf16, false><<<g.grid, g.block, 0, st>>>((const bf16*)x, (const bf16*)w, bias,
+                                                                 (bf16*)y, q, f.rbs);
       return check_launch("dwconv_fwd(walk)");
     }
-    if (d.stride_h == 1)
-      CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 1, false><<<g.grid, g.block, 0, st>>>(
-                                  (const T*)x, (const T*)w, bias, (T*)y, q)));
-    else {
-      // stride 2: strips of 2 outputs (3 x 5 input vectors) keep two CTAs per SM resident
-      q.strips_per_row = (int)ceil_div(p.Q, 2);
-      q.total_strips = (int64_t)p.N * p.P * q.strips_per_row;
-      g = dw_strip_geom(q.cv_total, q.total_strips, 8);
-      CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 2, false, 2><<<g.grid, g.block, 0, st>>>(
-                                  (const T*)x, (const T*)w, bias, (T*)y, q)));
+    if (d.stride_h == 1) {
+      if (stats)
+        CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 1, false, kDwTQ, true><<<g.grid, g.block, red, st>>>(
+                                    (const T*)x, (const T*)w, bias, (T*)y, q, stats)));
+      else
+        CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 1, false><<<g.grid, g.block, 0, st>>>(
+                                    (const T*)x, (const T*)w, bias, (T*)y, q)));
+    } else {
+      if (stats)
+        CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 2, false, 2, true><<<g.grid, g.block, red, st>>>(
+                                    (const T*)x, (const T*)w, bias, (T*)y, q, stats)));
+      else
+        CNB_DISPATCH_T(d.dtype, (dw3x3_strip_k<T, 2, false, 2><<<g.grid, g.block, 0, st>>>(
+                                    (const T*)x, (const T*)w, bias, (T*)y, q)));
     }
     return check_launch("dwconv_fwd(strip)");
   }
+  CNB_REQUIRE(!stats, CNB_ERR_UNSUPPORTED,
+              "dwconv_fwd: BatchNorm partials are emitted by the 3x3 strip kernels only (16-byte aligned tensors)");
   int v = pick_vec(p.C, dtype_size(d.dtype), x, y);
   int64_t total = (int64_t)p.N * p.P * p.Q * (p.C / v);
   int gr = grid_for(total, kDwThreads);

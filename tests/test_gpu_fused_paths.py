@@ -195,3 +195,33 @@ def test_switches_off_same_result(monkeypatch, family, kind):
         print(f"{family}-{kind}: on-vs-off logits {O.rel_l2(l1, l0):.2e}, grads median {errs[len(errs) // 2]:.2e} "
               f"max {errs[-1]:.2e}")
         assert errs[len(errs) // 2] <= 1e-1, errs[len(errs) // 2]
+
+
+# ------------------------------------------------------------------ depthwise conv -> BatchNorm partials
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("n,c,h,w,stride", [(4, 64, 28, 28, 1), (3, 128, 14, 14, 2), (2, 32, 9, 11, 1),
+                                            (2, 68, 7, 7, 2), (8, 512, 4, 4, 1), (2, 1024, 1, 1, 1)])
+def test_depthwise_emits_batchnorm_partials(n, c, h, w, stride, dtype):
+    """The 3x3 depthwise forward kernels emit the [rows][2][C] table of per-channel sums / sums of
+    squares of the STORED output (Conv2dBlockDW, reference src/mobilenet_v1.py:90-125): the table must
+    reproduce the sums of y, the output itself must be bit-identical to the plain launch, and
+    BatchNorm fed with the table must agree with BatchNorm that reads y."""
+    from convnets_b200 import functional as F
+    g = torch.Generator().manual_seed(c + h)
+    x = torch.randn(n, c, h, w, generator=g).to(dtype).cuda().contiguous(memory_format=CL)
+    wt = (torch.randn(c, 1, 3, 3, generator=g) * 0.4).cuda()
+    y0 = F.conv2d(x, wt, None, stride, 1, 1, c)
+    y1, part = F.conv2d(x, wt, None, stride, 1, 1, c, bn_stats=True)
+    assert part is not None and part.shape[1:] == (2, c) and part.shape[0] >= 1
+    assert torch.equal(y0, y1)
+    yd = y1.double()
+    s_ref, q_ref = yd.sum(dim=(0, 2, 3)), (yd * yd).sum(dim=(0, 2, 3))
+    s, q = part[:, 0].double().sum(0), part[:, 1].double().sum(0)
+    scale = yd.abs().sum(dim=(0, 2, 3)).clamp_min(1e-30)
+    assert ((s - s_ref).abs() / scale).max().item() < 1e-5
+    assert ((q - q_ref).abs() / q_ref.clamp_min(1e-30)).max().item() < 1e-5
+    if n * y1.shape[2] * y1.shape[3] > 1:
+        gam, bet = torch.rand(c).cuda() + 0.5, torch.randn(c).cuda()
+        a = F.batch_norm(y1, gam, bet, None, None, True, 0.1, 1e-5, relu=True, partials=part)
+        b = F.batch_norm(y1, gam, bet, None, None, True, 0.1, 1e-5, relu=True)
+        assert O.rel_l2(a, b) <= (1e-2 if dtype == torch.bfloat16 else 1e-5)
