@@ -155,7 +155,13 @@ def _dense_layer_forward(self, x):
 _BLOCK_FORWARDS = {name: _residual_forward for name in (
     "ResBlock", "ResBottleneck", "SEResBlock", "SEResBottleneck", "SEBlock", "SEBottleneck",
     "SKResBottleneck", "SKBottleneck")}
+def _dense_block_forward(self, x):
+    from .dense import dense_block_forward
+    return dense_block_forward(self, x)
+
+
 _BLOCK_FORWARDS.update({
+    "DenseBlock": _dense_block_forward,
     "SEUnit": _se_unit_forward, "SKConv": _sk_conv_forward, "ShuffleUnit": _shuffle_unit_forward,
     "Fire": _fire_forward, "InceptionBlock": _inception_forward, "DenseLayer": _dense_layer_forward,
 })

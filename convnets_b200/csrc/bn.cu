@@ -831,6 +831,185 @@ bn_bwd_fused_k(const T* __restrict__ x, const T* __restrict__ y, const uint8_t* 
   }
 }
 
+// ================================================================ concat-aware BatchNorm (DenseNet)
+// A dense block keeps its feature maps in ONE [M, C_total] buffer; layer l normalises the channel
+// prefix [0, C_l) of it (reference src/densenet.py:117,131-140: BatchNorm2d over torch.cat([x, out])).
+// Two facts make that cheap: (1) the batch statistics of a channel do not depend on which layer
+// looks at it, so they are computed once — from the producing convolution's epilogue — and every
+// later layer only applies its own gamma / beta; (2) the input gradient of layer l's BatchNorm is a
+// contribution to the gradient of the shared buffer, so the backward pass accumulates in place.
+// These kernels are the row-strided forms of bn_apply_k / bn_bwd_reduce_k / bn_bwd_dx_k (x and dx
+// have a row stride != C); the dense layers keep their tuned kernels.
+__global__ void bn_prefix_coeff_k(const float* __restrict__ gamma, const float* __restrict__ beta,
+                                  const float* __restrict__ mean, const float* __restrict__ rstd,
+                                  float* __restrict__ rmean, float* __restrict__ rvar,
+                                  long long* __restrict__ nbt, float* __restrict__ scale,
+                                  float* __restrict__ shift, int C, int64_t M, float eps, float momentum) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float rs = rstd[c];
+  scale[c] = (gamma ? gamma[c] : 1.f) * rs;
+  shift[c] = beta ? beta[c] : 0.f;
+  if (nbt && c == 0) *nbt += 1;
+  if (rmean) rmean[c] = (1.f - momentum) * rmean[c] + momentum * mean[c];
+  if (rvar) {
+    double var = 1.0 / ((double)rs * (double)rs) - (double)eps;   // biased batch variance
+    if (var < 0.0) var = 0.0;
+    const double unbiased = M > 1 ? var * (double)M / (double)(M - 1) : var;
+    rvar[c] = (1.f - momentum) * rvar[c] + momentum * (float)unbiased;
+  }
+}
+
+template <typename T, int V, bool RELU>
+__global__ void __launch_bounds__(kBnThreads)
+bn_apply_ld_k(const T* __restrict__ x, int64_t ldx, const float* __restrict__ scale,
+              const float* __restrict__ shift, const float* __restrict__ mean, T* __restrict__ y,
+              uint8_t* __restrict__ mask, int64_t M, int C, int64_t rows_per_split) {
+  const int cv = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c0 = cv * V;
+  if (c0 >= C) return;
+  const int64_t r0 = blockIdx.y * rows_per_split;
+  int64_t r1 = r0 + rows_per_split;
+  if (r1 > M) r1 = M;
+  float sc[V], sh[V], mu[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) { sc[j] = scale[c0 + j]; sh[j] = shift[c0 + j]; mu[j] = mean[c0 + j]; }
+  const bool bits_out = RELU && V == 8 && mask != nullptr;
+  const int ry = blockDim.y;
+  auto one = [&](int64_t r, const Pack<T, V>& a) {
+    Pack<T, V> o;
+    uint32_t bits = 0;
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      float v = fmaf(to_f(a.v[j]) - mu[j], sc[j], sh[j]);
+      if (RELU) v = (v > 0.f || v != v) ? v : 0.f;
+      o.v[j] = from_f<T>(v);
+      if (RELU && V == 8) bits |= (to_f(o.v[j]) > 0.f ? 1u : 0u) << j;
+    }
+    st_pack<T, V>(y + r * C + c0, o);
+    if (bits_out) mask[(r * C + c0) >> 3] = (uint8_t)bits;
+  };
+  int64_t r = r0 + threadIdx.y;
+  for (; r + 3 * (int64_t)ry < r1; r += 4 * (int64_t)ry) {
+    Pack<T, V> a[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) a[u] = ld_pack<T, V>(x + (r + (int64_t)u * ry) * ldx + c0);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) one(r + (int64_t)u * ry, a[u]);
+  }
+  for (; r < r1; r += ry) one(r, ld_pack<T, V>(x + r * ldx + c0));
+}
+
+// RELU: 0 = none, 1 = mask from y > 0, 2 = 1-bit mask
+template <typename T, int V, int RELU>
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_reduce_ld_k(const T* __restrict__ x, int64_t ldx, const T* __restrict__ y,
+                   const uint8_t* __restrict__ mask, const T* __restrict__ dy,
+                   const float* __restrict__ mean, float* __restrict__ part, int64_t M, int C,
+                   int64_t rows_per_split, int splits, int* __restrict__ counter, BnBwdFin f) {
+  extern __shared__ __align__(16) float red[];
+  const int cv = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c0 = cv * V;
+  const int64_t r0 = blockIdx.y * rows_per_split;
+  int64_t r1 = r0 + rows_per_split;
+  if (r1 > M) r1 = M;
+  float s[V], q[V], mu[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) s[j] = q[j] = mu[j] = 0.f;
+  if (c0 < C) {
+#pragma unroll
+    for (int j = 0; j < V; ++j) mu[j] = mean[c0 + j];
+    constexpr bool bits = RELU == 2 && V == 8;
+    const int ry = blockDim.y;
+    auto one = [&](int64_t r, const Pack<T, V>& a, const Pack<T, V>& g) {
+      uint32_t mb = 0;
+      Pack<T, V> o;
+      if (RELU) {
+        if (bits) mb = mask[(r * C + c0) >> 3];
+        else o = ld_pack<T, V>(y + r * C + c0);
+      }
+#pragma unroll
+      for (int j = 0; j < V; ++j) {
+        float gf = to_f(g.v[j]);
+        if (RELU) {
+          const bool pos = bits ? ((mb >> j) & 1u) : (to_f(o.v[j]) > 0.f);
+          if (!pos) gf = 0.f;
+        }
+        s[j] += gf;
+        q[j] = fmaf(gf, to_f(a.v[j]) - mu[j], q[j]);
+      }
+    };
+    int64_t r = r0 + threadIdx.y;
+    for (; r + (int64_t)ry < r1; r += 2 * (int64_t)ry) {
+      const Pack<T, V> a0 = ld_pack<T, V>(x + r * ldx + c0), a1 = ld_pack<T, V>(x + (r + ry) * ldx + c0);
+      const Pack<T, V> g0 = ld_pack<T, V>(dy + r * C + c0), g1 = ld_pack<T, V>(dy + (r + ry) * C + c0);
+      one(r, a0, g0);
+      one(r + ry, a1, g1);
+    }
+    for (; r < r1; r += ry) one(r, ld_pack<T, V>(x + r * ldx + c0), ld_pack<T, V>(dy + r * C + c0));
+  }
+  int c;
+  double S, Q;
+  if (!bn_block_merge<V>(s, q, red, part, C, splits, counter, c, S, Q)) return;
+  const float rs = f.rstd[c];
+  const float g = f.gamma ? f.gamma[c] : 1.f;
+  if (f.dbeta) f.dbeta[c] = (float)S;
+  if (f.dgamma) f.dgamma[c] = (float)(Q * (double)rs);
+  f.c1[c] = g * rs;
+  f.c2[c] = (float)(S / (double)M);
+  f.c3[c] = (float)(Q * (double)rs * (double)rs / (double)M);
+}
+
+// dx_acc[r * lddx + c] += c1 * (dy' - c2 - (x - mean) * c3): the sum is formed in fp32 from the stored
+// accumulator and rounded once
+template <typename T, int V, int RELU>
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_dx_ld_k(const T* __restrict__ x, int64_t ldx, const T* __restrict__ y,
+               const uint8_t* __restrict__ mask, const T* __restrict__ dy,
+               const float* __restrict__ mean, const float* __restrict__ c1,
+               const float* __restrict__ c2, const float* __restrict__ c3, T* __restrict__ dx_acc,
+               int64_t lddx, int64_t M, int C, int64_t rows_per_split) {
+  const int cv = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c0 = cv * V;
+  if (c0 >= C) return;
+  const int64_t r0 = blockIdx.y * rows_per_split;
+  int64_t r1 = r0 + rows_per_split;
+  if (r1 > M) r1 = M;
+  float k1[V], k2[V], k3[V], mu[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) { k1[j] = c1[c0 + j]; k2[j] = c2[c0 + j]; k3[j] = c3[c0 + j]; mu[j] = mean[c0 + j]; }
+  constexpr bool bits = RELU == 2 && V == 8;
+  const int ry = blockDim.y;
+  auto one = [&](int64_t r, const Pack<T, V>& a, const Pack<T, V>& g, const Pack<T, V>& acc) {
+    uint32_t mb = 0;
+    Pack<T, V> o, out;
+    if (RELU) {
+      if (bits) mb = mask[(r * C + c0) >> 3];
+      else o = ld_pack<T, V>(y + r * C + c0);
+    }
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      float gf = to_f(g.v[j]);
+      if (RELU) {
+        const bool pos = bits ? ((mb >> j) & 1u) : (to_f(o.v[j]) > 0.f);
+        if (!pos) gf = 0.f;
+      }
+      out.v[j] = from_f<T>(to_f(acc.v[j]) + k1[j] * (gf - k2[j] - (to_f(a.v[j]) - mu[j]) * k3[j]));
+    }
+    st_pack<T, V>(dx_acc + r * lddx + c0, out);
+  };
+  int64_t r = r0 + threadIdx.y;
+  for (; r + (int64_t)ry < r1; r += 2 * (int64_t)ry) {
+    const Pack<T, V> a0 = ld_pack<T, V>(x + r * ldx + c0), a1 = ld_pack<T, V>(x + (r + ry) * ldx + c0);
+    const Pack<T, V> g0 = ld_pack<T, V>(dy + r * C + c0), g1 = ld_pack<T, V>(dy + (r + ry) * C + c0);
+    const Pack<T, V> d0 = ld_pack<T, V>(dx_acc + r * lddx + c0), d1 = ld_pack<T, V>(dx_acc + (r + ry) * lddx + c0);
+    one(r, a0, g0, d0);
+    one(r + ry, a1, g1, d1);
+  }
+  for (; r < r1; r += ry)
+    one(r, ld_pack<T, V>(x + r * ldx + c0), ld_pack<T, V>(dy + r * C + c0), ld_pack<T, V>(dx_acc + r * lddx + c0));
+}
+
 // Largest x + dy footprint (bytes) the single-read backward takes; 0 disables it.
 // CNB_BN_BWD_FUSED_MB overrides (sweep: tools/gpu_bn_fused.sh).
 static int64_t bn_bwd_fused_limit() {
@@ -1054,6 +1233,135 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
   } while (0)
   APPLY_ANY();
   return check_launch("bn_apply");
+}
+
+int cnb_bn_stats_from_partials(const cnb_bn_desc* d, const float* conv_partials, int32_t n_partials,
+                               float* mean, float* rstd, void* workspace, size_t workspace_bytes,
+                               void* stream) {
+  CNB_TRY(validate_bn(d, "cnb_bn_stats_from_partials"));
+  CNB_REQUIRE(conv_partials && n_partials > 0 && mean && rstd && workspace, CNB_ERR_INVALID,
+              "cnb_bn_stats_from_partials: null pointer / no rows");
+  CNB_REQUIRE(workspace_bytes >= bn_ws_bytes(d->C), CNB_ERR_WORKSPACE,
+              "cnb_bn_stats_from_partials: workspace %zu < %zu", workspace_bytes, bn_ws_bytes(d->C));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int C = d->C;
+  BnFwdFin fin{nullptr, nullptr, nullptr, nullptr, mean, rstd, nullptr, nullptr, d->eps, d->momentum, nullptr};
+  float* part = (float*)workspace;
+  BnGeom g;
+  g.V = 1; g.cx = n_partials <= 512 ? 16 : 64; g.ry = kBnThreads / g.cx;
+  g.cblocks = (int)ceil_div(C, g.cx);
+  int64_t splits = ceil_div((int64_t)sm_count() * 2, g.cblocks);
+  int64_t max_splits = ceil_div((int64_t)n_partials, (int64_t)g.ry * 4);
+  if (splits > max_splits) splits = max_splits;
+  if (n_partials <= 512) splits = 1;
+  if (splits < 1) splits = 1;
+  g.rows_per_split = ceil_div((int64_t)n_partials, splits);
+  g.splits = (int)ceil_div((int64_t)n_partials, g.rows_per_split);
+  float* scale = part + (size_t)2 * C * g.splits;
+  fin.scale = scale; fin.shift = scale + C;
+  int* counter = bn_counters(g.cblocks);
+  CNB_REQUIRE(counter, CNB_ERR_CUDA, "cnb_bn_stats_from_partials: cannot allocate the arrival counters");
+  dim3 grid(g.cblocks, g.splits), block(g.cx, g.ry);
+  bn_partials_k<<<grid, block, 4096, st>>>(conv_partials, part, n_partials, d->M, C, g.rows_per_split,
+                                           g.splits, counter, fin);
+  return check_launch("bn_partials(stats only)");
+}
+
+int cnb_bn_fwd_train_prefix(const cnb_bn_desc* d, const void* x, int64_t x_row_stride, const float* mean,
+                            const float* rstd, const float* gamma, const float* beta,
+                            float* running_mean, float* running_var, void* y, void* relu_mask,
+                            void* workspace, size_t workspace_bytes, void* stream) {
+  CNB_TRY(validate_bn(d, "cnb_bn_fwd_train_prefix"));
+  CNB_REQUIRE(x && y && mean && rstd && workspace, CNB_ERR_INVALID, "cnb_bn_fwd_train_prefix: null pointer");
+  CNB_REQUIRE(!(d->flags & CNB_BN_ADD), CNB_ERR_UNSUPPORTED, "cnb_bn_fwd_train_prefix: no residual input");
+  CNB_REQUIRE(x_row_stride >= d->C, CNB_ERR_INVALID, "cnb_bn_fwd_train_prefix: row stride %lld < C=%d",
+              (long long)x_row_stride, d->C);
+  CNB_REQUIRE(workspace_bytes >= bn_ws_bytes(d->C), CNB_ERR_WORKSPACE,
+              "cnb_bn_fwd_train_prefix: workspace %zu < %zu", workspace_bytes, bn_ws_bytes(d->C));
+  const bool relu = d->flags & CNB_BN_RELU;
+  CNB_REQUIRE(!relu_mask || (relu && d->dtype == CNB_BF16 && d->C % 8 == 0), CNB_ERR_INVALID,
+              "cnb_bn_fwd_train_prefix: relu_mask needs CNB_BN_RELU, bf16 and C %% 8 == 0");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int C = d->C;
+  const int64_t M = d->M;
+  const size_t es = dtype_size(d->dtype);
+  int v = pick_vec(C, es, x, y);
+  while (v > 1 && (x_row_stride % v) != 0) v >>= 1;
+  CNB_REQUIRE(!relu_mask || v == 8, CNB_ERR_INVALID, "cnb_bn_fwd_train_prefix: relu_mask needs 16-byte aligned rows");
+  float* scale = (float*)workspace;
+  float* shift = scale + C;
+  bn_prefix_coeff_k<<<(unsigned)ceil_div(C, 128), 128, 0, st>>>(gamma, beta, mean, rstd, running_mean, running_var,
+                                                                (long long*)d->num_batches_tracked, scale, shift,
+                                                                C, M, d->eps, d->momentum);
+  CNB_TRY(check_launch("bn_prefix_coeff"));
+  BnGeom ga = bn_geom(M, C, v, kStreamWaves);
+  dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
+  if (relu)
+    CNB_DISPATCH_TV(d->dtype, v, (bn_apply_ld_k<T, V, true><<<agrid, ablock, 0, st>>>(
+                                     (const T*)x, x_row_stride, scale, shift, mean, (T*)y, (uint8_t*)relu_mask, M, C,
+                                     ga.rows_per_split)));
+  else
+    CNB_DISPATCH_TV(d->dtype, v, (bn_apply_ld_k<T, V, false><<<agrid, ablock, 0, st>>>(
+                                     (const T*)x, x_row_stride, scale, shift, mean, (T*)y, nullptr, M, C,
+                                     ga.rows_per_split)));
+  return check_launch("bn_apply(prefix)");
+}
+
+int cnb_bn_bwd_prefix(const cnb_bn_desc* d, const void* x, int64_t x_row_stride, const void* y,
+                      const void* relu_mask, const void* dy, const float* mean, const float* rstd,
+                      const float* gamma, void* dx_accum, int64_t dx_row_stride, float* dgamma,
+                      float* dbeta, void* workspace, size_t workspace_bytes, void* stream) {
+  CNB_TRY(validate_bn(d, "cnb_bn_bwd_prefix"));
+  CNB_REQUIRE(x && dy && mean && rstd && dx_accum && workspace, CNB_ERR_INVALID, "cnb_bn_bwd_prefix: null pointer");
+  CNB_REQUIRE(!(d->flags & CNB_BN_ADD), CNB_ERR_UNSUPPORTED, "cnb_bn_bwd_prefix: no residual input");
+  CNB_REQUIRE(x_row_stride >= d->C && dx_row_stride >= d->C, CNB_ERR_INVALID, "cnb_bn_bwd_prefix: row stride < C");
+  CNB_REQUIRE(workspace_bytes >= bn_ws_bytes(d->C), CNB_ERR_WORKSPACE,
+              "cnb_bn_bwd_prefix: workspace %zu < %zu", workspace_bytes, bn_ws_bytes(d->C));
+  const bool relu = d->flags & CNB_BN_RELU;
+  CNB_REQUIRE(!relu || y || relu_mask, CNB_ERR_INVALID, "cnb_bn_bwd_prefix: CNB_BN_RELU needs y or the bit mask");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int C = d->C;
+  const int64_t M = d->M;
+  const size_t es = dtype_size(d->dtype);
+  int v = pick_vec(C, es, x, dy, dx_accum, relu && !relu_mask ? y : nullptr);
+  while (v > 1 && ((x_row_stride % v) != 0 || (dx_row_stride % v) != 0)) v >>= 1;
+  const uint8_t* mask = (const uint8_t*)relu_mask;
+  CNB_REQUIRE(!mask || (v == 8 && d->dtype == CNB_BF16), CNB_ERR_INVALID,
+              "cnb_bn_bwd_prefix: the bit mask needs bf16 and 16-byte aligned rows");
+  const int mode = !relu ? 0 : (mask ? 2 : 1);
+  float* part = (float*)workspace;
+  BnGeom g = bn_geom(M, C, v, kReduceWaves, kReduceCx);
+  float* c1 = part + (size_t)2 * C * g.splits;
+  float* c2 = c1 + C;
+  float* c3 = c2 + C;
+  int* counter = bn_counters(g.cblocks);
+  CNB_REQUIRE(counter, CNB_ERR_CUDA, "cnb_bn_bwd_prefix: cannot allocate the arrival counters");
+  {
+    dim3 grid(g.cblocks, g.splits), block(g.cx, g.ry);
+    size_t smem = (size_t)g.ry * 2 * g.cx * v * sizeof(float);
+    if (smem < 4096) smem = 4096;
+    BnBwdFin fin{gamma, rstd, dgamma, dbeta, c1, c2, c3};
+#define RED(R)                                                                                           \
+  CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_reduce_ld_k<T, V, R><<<grid, block, smem, st>>>(                  \
+                                   (const T*)x, x_row_stride, (const T*)y, mask, (const T*)dy, mean, part, M, C, \
+                                   g.rows_per_split, g.splits, counter, fin)))
+    if (mode == 2) RED(2);
+    else if (mode == 1) RED(1);
+    else RED(0);
+#undef RED
+    CNB_TRY(check_launch("bn_bwd_reduce(prefix)"));
+  }
+  BnGeom ga = bn_geom(M, C, v, kStreamWaves);
+  dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
+#define DXL(R)                                                                                            \
+  CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_dx_ld_k<T, V, R><<<agrid, ablock, 0, st>>>(                        \
+                                   (const T*)x, x_row_stride, (const T*)y, mask, (const T*)dy, mean, c1, c2, c3, \
+                                   (T*)dx_accum, dx_row_stride, M, C, ga.rows_per_split)))
+  if (mode == 2) DXL(2);
+  else if (mode == 1) DXL(1);
+  else DXL(0);
+#undef DXL
+  return check_launch("bn_bwd_dx(prefix)");
 }
 
 int cnb_bn_fwd_eval(const cnb_bn_desc* d, const void* x, const void* residual, const float* gamma,

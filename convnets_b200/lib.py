@@ -74,6 +74,9 @@ SIGNATURES = {
     "cnb_bn_workspace_bytes": (_SZ, [C.POINTER(BnDesc)]),
     "cnb_bn_fwd_train": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _P,
                               _SZ, _P]),
+    "cnb_bn_stats_from_partials": (_I, [C.POINTER(BnDesc), _P, _I32, _P, _P, _P, _SZ, _P]),
+    "cnb_bn_fwd_train_prefix": (_I, [C.POINTER(BnDesc), _P, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
+    "cnb_bn_bwd_prefix": (_I, [C.POINTER(BnDesc), _P, _I64, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _P, _P, _SZ, _P]),
     "cnb_bn_fwd_eval": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_bn_bwd": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_relu_fwd": (_I, [_P, _P, _I64, _I, _P]),

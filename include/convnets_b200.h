@@ -144,6 +144,26 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
                      float* save_mean, float* save_rstd, const float* conv_partials,
                      int32_t n_partials, void* relu_mask, void* workspace, size_t workspace_bytes,
                      void* stream);
+/* ---- concat-aware BatchNorm: DenseNet's BatchNorm2d over torch.cat([x, out], 1) (reference
+ * src/densenet.py:117,124,131-140) when the block keeps its feature maps in one [M, C_total] buffer.
+ * Layer l normalises the channel prefix [0, C_l) of the buffer: x has a row stride != C.
+ *   cnb_bn_stats_from_partials: mean / rstd of the C channels a convolution just produced, from the
+ *     partial-sum table its epilogue wrote (cnb_conv2d_fwd bn_partials); nothing else is touched.
+ *   cnb_bn_fwd_train_prefix: batch statistics are GIVEN (a channel's statistics do not depend on the
+ *     layer that reads it, so a block computes them once): running-statistics update + apply.
+ *   cnb_bn_bwd_prefix: dgamma, dbeta and dx ACCUMULATED into dx_accum (row stride dx_row_stride) —
+ *     the gradient of the shared buffer, which every later layer of the block adds to. */
+int cnb_bn_stats_from_partials(const cnb_bn_desc* d, const float* conv_partials, int32_t n_partials,
+                               float* mean, float* rstd, void* workspace, size_t workspace_bytes,
+                               void* stream);
+int cnb_bn_fwd_train_prefix(const cnb_bn_desc* d, const void* x, int64_t x_row_stride, const float* mean,
+                            const float* rstd, const float* gamma, const float* beta,
+                            float* running_mean, float* running_var, void* y, void* relu_mask,
+                            void* workspace, size_t workspace_bytes, void* stream);
+int cnb_bn_bwd_prefix(const cnb_bn_desc* d, const void* x, int64_t x_row_stride, const void* y,
+                      const void* relu_mask, const void* dy, const float* mean, const float* rstd,
+                      const float* gamma, void* dx_accum, int64_t dx_row_stride, float* dgamma,
+                      float* dbeta, void* workspace, size_t workspace_bytes, void* stream);
 /* inference forward with running statistics */
 int cnb_bn_fwd_eval(const cnb_bn_desc* d, const void* x, const void* residual, const float* gamma,
                     const float* beta, const float* running_mean, const float* running_var, void* y,

@@ -37,10 +37,14 @@ def _cpu(t):
 
 
 @pytest.mark.parametrize("family,kind,hw,batch", CASES)
-def test_every_layer_in_a_real_step(family, kind, hw, batch):
+def test_every_layer_in_a_real_step(family, kind, hw, batch, monkeypatch):
     import convnets_b200 as cnb
+    from convnets_b200 import dense
     from convnets_b200 import layers as LY
     from convnets_b200 import zoo as M
+    # DenseNet: the shared-buffer block function bypasses the per-module forwards this test hooks; its
+    # kernels have their own cases (tests/test_gpu_dense.py).  Here the per-layer path is exercised.
+    monkeypatch.setattr(dense, "_ENABLED", False)
     torch.manual_seed(21)
     s = M.Settings(kind=kind, input_size=(3, hw, hw), num_classes=10, dropout_rate=0.0)
     s.device.set_device("cuda:0")
