@@ -80,7 +80,9 @@ def _residual_forward_folded(self, blocks, x):
         conv, bn = _tail(last)
         out = conv(out)
         if bn is not None:
-            return bn(out, residual=identity, relu=True)
+            # `identity` is the alias _Conv2dSkipFn handed out and nothing else reads it: its
+            # gradient can stay implicit (block-output gradient + the ReLU bit mask)
+            return bn(out, residual=identity, relu=True, lazy_residual_grad=True)
         return F_.add_relu(out, identity)
     for blk in blocks[1:]:
         out = blk(out)

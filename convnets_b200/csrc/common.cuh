@@ -170,7 +170,8 @@ int conv_tc_fwd(const cnb_conv_desc& d, const void* x, const void* w, const floa
                 float* stats, void* ws, size_t ws_bytes, cudaStream_t st);
 int conv_tc_stats_rows(const cnb_conv_desc& d);
 int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const void* w_t, void* dx,
-                  void* ws, size_t ws_bytes, cudaStream_t st, const void* addend = nullptr);
+                  void* ws, size_t ws_bytes, cudaStream_t st, const void* addend = nullptr,
+                  const void* addend_mask = nullptr);
 int conv_tc_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* dw, void* ws,
                   size_t ws_bytes, cudaStream_t st);
 

@@ -122,8 +122,8 @@ int cnb_conv2d_dgrad(const cnb_conv_desc* d, const void* dy, const void* w, cons
 }
 
 int cnb_conv2d_dgrad_add(const cnb_conv_desc* d, const void* dy, const void* w, const void* w_t,
-                         const void* addend, void* dx, void* workspace, size_t workspace_bytes,
-                         void* stream) {
+                         const void* addend, const void* addend_mask, void* dx, void* workspace,
+                         size_t workspace_bytes, void* stream) {
   CNB_TRY(validate_conv(d, "cnb_conv2d_dgrad_add"));
   CNB_REQUIRE(dy && w && dx && addend, CNB_ERR_INVALID, "cnb_conv2d_dgrad_add: null tensor pointer");
   CNB_REQUIRE(!is_depthwise(*d) && d->stride_h == 1 && d->stride_w == 1, CNB_ERR_UNSUPPORTED,
@@ -136,7 +136,9 @@ int cnb_conv2d_dgrad_add(const cnb_conv_desc* d, const void* dy, const void* w, 
               CNB_ERR_INVALID, "cnb_conv2d_dgrad_add: tensor pointers must be 16-byte aligned");
   CNB_REQUIRE(!w_t || (uintptr_t)w_t % 16 == 0, CNB_ERR_INVALID,
               "cnb_conv2d_dgrad_add: w_t must be 16-byte aligned");
-  return conv_tc_dgrad(*d, dy, w, w_t, dx, workspace, workspace_bytes, (cudaStream_t)stream, addend);
+  CNB_REQUIRE(!addend_mask || d->C % 32 == 0, CNB_ERR_UNSUPPORTED,
+              "cnb_conv2d_dgrad_add: a masked addend needs C %% 32 == 0 (C=%d)", d->C);
+  return conv_tc_dgrad(*d, dy, w, w_t, dx, workspace, workspace_bytes, (cudaStream_t)stream, addend, addend_mask);
 }
 
 int cnb_conv2d_wgrad(const cnb_conv_desc* d, const void* x, const void* dy, float* dw, float* dbias,

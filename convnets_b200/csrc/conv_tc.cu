@@ -126,6 +126,7 @@ struct FpropParams {
   CUtensorMap tmD;  // output {Kout, M}, box {64, 128}
   const float* bias;
   const bf16* addend;  // optional [M][Kout]: added to the accumulator before the bf16 rounding (kConvAccum)
+  const uint8_t* addend_mask;  // EPI == 4: bit (m * Kout + c) selects which addend elements count (1-bit ReLU mask)
   float* stats;     // optional [persistent CTAs / n_tiles][2][Kout] column sums / sums of squares of the stored output
   int M;            // output pixels in this launch
   int outP, outQ;   // output grid per image (pixel index -> (n, i, j))
@@ -170,6 +171,9 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
   // EPI: 0 = bias / ReLU by flags, 1 = plain store, 2 = plain + addend (data-grad + skip gradient),
   //      3 = plain, rows scattered to the strided pixel positions of a larger tensor (one parity
   //          class of a strided data-grad writes dx directly: no compact copy, no interleave pass)
+  //      4 = 2 with the addend masked by a 1-bit mask: the skip gradient of a residual block is the
+  //          block-output gradient where the output ReLU was active, so BatchNorm backward does not
+  //          have to materialise it (src/resnet.py:191-194 `output += identity; F.relu(output)`)
   constexpr bool PLAIN = EPI != 0;   // rows past the end of the tensor stay zero (no bias added)
   constexpr int B_TILE_BYTES = BLOCK_N * TILE_K * 2;
   constexpr int STAGE_BYTES = BRES ? A_TILE_BYTES : A_TILE_BYTES + B_TILE_BYTES;
@@ -346,6 +350,17 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
     for (int mt = m_first; mt < p.m_tiles; mt += m_step, ++lt) {
       const int m0 = mt * TILE_M;
       const uint32_t buf = lt & 1;
+      if (EPI == 2 || EPI == 4) {
+        // the addend row segment this thread will add comes from HBM (a 100-400 MB tensor): ask for
+        // it now, while the accumulator is still filling, so the loads below hit L2
+        const int64_t grow = (int64_t)m0 + row;
+        if (grow < p.M) {
+          const bf16* ap = p.addend + grow * p.Kout + n0 + chalf * HALF_N;
+#pragma unroll
+          for (int b = 0; b < (HALF_N * 2 + 127) / 128; ++b)
+            if (n0 + chalf * HALF_N + b * 64 < p.Kout) prefetch_l2(ap + b * 64);
+        }
+      }
       mbar_wait(&tmem_full_bar[buf], (lt >> 1) & 1);
       tc_fence_after();
       // the previous tile's TMA store must have finished READING the staging buffer
@@ -368,14 +383,24 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
         // skip-gradient accumulation: this lane's 32 columns of the addend row, 4 x 16 bytes, all
         // requested before the first use (rows past M / columns past Kout are never stored)
         uint4 add4[4];
-        if (EPI == 2) {
+        if (EPI == 2 || EPI == 4) {
           const int64_t grow = (int64_t)m0 + row;
+          uint32_t mbits = 0xffffffffu;   // one bit per column of this 32-column chunk
+          if (EPI == 4 && grow < p.M && n0 + c0 < p.Kout)
+            mbits = __ldg(reinterpret_cast<const uint32_t*>(p.addend_mask + ((grow * p.Kout + n0 + c0) >> 3)));
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const int col = n0 + c0 + j * 8;
             add4[j] = (grow < p.M && col < p.Kout)
                           ? __ldg(reinterpret_cast<const uint4*>(p.addend + grow * p.Kout + col))
                           : make_uint4(0u, 0u, 0u, 0u);
+            if (EPI == 4) {
+              const uint32_t mb = (mbits >> (8 * j)) & 0xffu;
+              add4[j].x &= ((mb & 1u) ? 0x0000ffffu : 0u) | ((mb & 2u) ? 0xffff0000u : 0u);
+              add4[j].y &= ((mb & 4u) ? 0x0000ffffu : 0u) | ((mb & 8u) ? 0xffff0000u : 0u);
+              add4[j].z &= ((mb & 16u) ? 0x0000ffffu : 0u) | ((mb & 32u) ? 0xffff0000u : 0u);
+              add4[j].w &= ((mb & 64u) ? 0x0000ffffu : 0u) | ((mb & 128u) ? 0xffff0000u : 0u);
+            }
           }
         }
 #pragma unroll
@@ -385,7 +410,7 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
           for (int e = 0; e < 4; ++e) {
             float f0 = __uint_as_float(cur[j * 8 + e * 2 + 0]);
             float f1 = __uint_as_float(cur[j * 8 + e * 2 + 1]);
-            if (EPI == 2) {
+            if (EPI == 2 || EPI == 4) {
               const uint32_t a2 = e == 0 ? add4[j].x : (e == 1 ? add4[j].y : (e == 2 ? add4[j].z : add4[j].w));
               f0 += __uint_as_float(a2 << 16);
               f1 += __uint_as_float(a2 & 0xffff0000u);
@@ -823,6 +848,7 @@ struct FpropLaunch {
   void* out;                     // [aN*outP*outQ, Kout] bf16
   const float* bias;
   const void* addend;            // optional [M][Kout] bf16 summed into the output (data-grad + skip gradient)
+  const void* addend_mask;       // optional 1-bit mask over the addend (M*Kout/8 bytes, Kout % 32 == 0)
   float* stats;                  // optional BatchNorm partials (forward only)
   int flags;
   bool tiled2d;                  // pure GEMM: A is the [M, C] matrix itself
@@ -934,7 +960,10 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
   prm.Kout = L.Kout;
   prm.flags = L.flags & ((L.bias ? CNB_CONV_BIAS : 0) | CNB_CONV_RELU);
   prm.addend = reinterpret_cast<const bf16*>(L.addend);
+  prm.addend_mask = reinterpret_cast<const uint8_t*>(L.addend_mask);
   if (L.addend) prm.flags |= kConvAccum;
+  CNB_REQUIRE(!L.addend_mask || (L.addend && L.Kout % 32 == 0), CNB_ERR_UNSUPPORTED,
+              "conv_tc: a masked addend needs the addend and Kout %% 32 == 0 (Kout=%d)", L.Kout);
   for (int t = 0; t < L.ntaps; ++t) {
     prm.off_h[t] = L.off_h[t];
     prm.off_w[t] = L.off_w[t];
@@ -951,10 +980,12 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
   }
   if (L.tiled2d) {
     if (epi == 1) return launch_fprop_bn<false, 1>(prm, BLOCK_N, st);
+    if (epi == 2 && L.addend_mask) return launch_fprop_bn<false, 4>(prm, BLOCK_N, st);
     if (epi == 2) return launch_fprop_bn<false, 2>(prm, BLOCK_N, st);
     return launch_fprop_bn<false, 0>(prm, BLOCK_N, st);
   }
   if (epi == 1) return launch_fprop_bn<true, 1>(prm, BLOCK_N, st);
+  if (epi == 2 && L.addend_mask) return launch_fprop_bn<true, 4>(prm, BLOCK_N, st);
   if (epi == 2) return launch_fprop_bn<true, 2>(prm, BLOCK_N, st);
   return launch_fprop_bn<true, 0>(prm, BLOCK_N, st);
 }
@@ -1201,7 +1232,7 @@ int conv_tc_fwd(const cnb_conv_desc& d, const void* x, const void* w, const floa
 }
 
 int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const void* w_t, void* dx,
-                  void* ws, size_t ws_bytes, cudaStream_t st, const void* addend) {
+                  void* ws, size_t ws_bytes, cudaStream_t st, const void* addend, const void* addend_mask) {
   CNB_REQUIRE(!addend || (d.stride_h == 1 && d.stride_w == 1), CNB_ERR_UNSUPPORTED,
               "conv_tc_dgrad: the accumulating epilogue exists for stride-1 data-grad only");
   CNB_REQUIRE(ws && ws_bytes >= conv_tc_workspace(d, CNB_DGRAD), CNB_ERR_WORKSPACE,
@@ -1254,6 +1285,7 @@ int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const v
     if (grouped) { L.grp_out = Cg; L.grp_in = Kg; L.wC = wCd; }
     L.out = dx; L.bias = nullptr; L.flags = 0;
     L.addend = addend;
+    L.addend_mask = addend_mask;
     L.tiled2d = (RS == 1 && d.pad_h == 0 && d.pad_w == 0);
     return launch_fprop(L, st);
   }

@@ -279,6 +279,9 @@ class _Conv2dSkipFn(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy, _dpart=None, dskip=None):
+        # a lazy skip gradient (see _LAZY_DRES) is taken off the table whatever happens next: the
+        # entry keeps dy alive, so no other tensor can sit at its address while it is registered
+        lazy = _LAZY_DRES.pop(dskip.data_ptr(), None) if dskip is not None else None
         if dskip is None or not ctx.needs_input_grad[0]:
             return _Conv2dFn.backward(ctx, dy, _dpart)
         lib = _L.load()
@@ -287,6 +290,11 @@ class _Conv2dSkipFn(torch.autograd.Function):
         dy = _nhwc(dy)
         if dy.dtype != x.dtype:
             dy = dy.to(x.dtype)
+        amask = None
+        if lazy is not None:
+            if lazy[1] is not dskip and (lazy[1].data_ptr() != dskip.data_ptr() or lazy[1].shape != dskip.shape):
+                raise RuntimeError("lazy skip gradient: the registered tensor is not the one that arrived")
+            amask = lazy[0]
         dskip = _nhwc(dskip)
         if dskip.dtype != x.dtype:
             dskip = dskip.to(x.dtype)
@@ -295,9 +303,13 @@ class _Conv2dSkipFn(torch.autograd.Function):
         ws = _workspace(nws, x.device)
         fused = (d.stride_h == 1 and d.stride_w == 1 and d.algo != _L.CNB_ALGO_SIMT
                  and lib.cnb_conv2d_uses_tc(C.byref(d), _L.CNB_DGRAD) == 1)
+        if amask is not None and not (fused and d.C % 32 == 0):
+            # cannot mask in the epilogue: materialise the masked gradient after all
+            dskip = mask_apply(dskip, amask)
+            amask = None
         if fused:
             _L.check(lib.cnb_conv2d_dgrad_add(C.byref(d), _p(dy), _p(wpack), _p(wpack_t), _p(dskip),
-                                              _p(dx), _p(ws), ws.numel(), _stream()),
+                                              _p(amask), _p(dx), _p(ws), ws.numel(), _stream()),
                      "cnb_conv2d_dgrad_add")
         else:
             _L.check(lib.cnb_conv2d_dgrad(C.byref(d), _p(dy), _p(wpack), _p(wpack_t), _p(dx), _p(ws),
@@ -316,6 +328,15 @@ class _Conv2dSkipFn(torch.autograd.Function):
             if tuple(dw.shape) != ctx.wshape:
                 dw = dw[:, :ctx.wshape[1]].contiguous(memory_format=_CL)
         return dx, dw, db, None, None, None, None, None, None, None, None
+
+
+def mask_apply(t: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
+    """t where bit (m*C + c) of the 1-bit ReLU mask is set, else 0 (torch ops; only the fallback of
+    the lazy skip gradient uses it)."""
+    n, c, h, w = t.shape
+    bits = mask.view(-1, 1).bitwise_right_shift(torch.arange(8, device=mask.device, dtype=torch.uint8)) & 1
+    keep = bits.view(n, h, w, c).permute(0, 3, 1, 2).to(t.dtype)
+    return (t * keep).contiguous(memory_format=_CL)
 
 
 def conv2d_with_skip(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, wpack=None,
@@ -455,10 +476,20 @@ def conv2d_uses_tc(x_shape, w_shape, stride, padding, dilation, groups, dtype, d
 
 
 # ----------------------------------------------------------------------------- batch norm
+# Residual tail `output += identity; F.relu(output)` (reference src/resnet.py:191-194): the gradient of
+# `identity` is the block-output gradient dy masked by the output ReLU.  When the identity is the
+# alias handed out by _Conv2dSkipFn (convert._residual_forward_folded), BatchNorm backward returns dy
+# ITSELF for it and registers the 1-bit mask here, keyed by dy's address; _Conv2dSkipFn.backward pops
+# the entry and lets the data-grad epilogue mask the addend (cnb_conv2d_dgrad_add addend_mask).
+# CNB_LAZY_SKIP_GRAD=0 turns it off (BatchNorm backward writes the masked tensor, as before).
+_LAZY_DRES: dict = {}
+_LAZY_SKIP = __import__("os").environ.get("CNB_LAZY_SKIP_GRAD", "1") == "1"
+
+
 class _BatchNormFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps,
-                relu, partials, nbt=None):
+                relu, partials, nbt=None, lazy_dres=False):
         _cuda(x, residual, gamma, beta)
         lib = _L.load()
         x = _nhwc(x)
@@ -506,6 +537,9 @@ class _BatchNormFn(torch.autograd.Function):
         ctx.desc = d
         ctx.has_res = residual is not None
         ctx.affine = gamma is not None
+        # lazy residual gradient: see _LAZY_DRES
+        ctx.lazy_dres = bool(lazy_dres and training and residual is not None and relu
+                             and x.dtype == torch.bfloat16 and c % 32 == 0)
         return y
 
     @staticmethod
@@ -521,7 +555,9 @@ class _BatchNormFn(torch.autograd.Function):
         if dy.dtype != x.dtype:
             dy = dy.to(x.dtype)
         dx = torch.empty_like(x, memory_format=_CL)
-        dres = torch.empty_like(x, memory_format=_CL) if (ctx.has_res and ctx.needs_input_grad[1]) else None
+        lazy = getattr(ctx, "lazy_dres", False) and mask is not None and ctx.needs_input_grad[1]
+        dres = torch.empty_like(x, memory_format=_CL) if (ctx.has_res and ctx.needs_input_grad[1]
+                                                           and not lazy) else None
         c = x.shape[1]
         dgamma = torch.empty(c, dtype=torch.float32, device=x.device) if ctx.affine else None
         dbeta = torch.empty(c, dtype=torch.float32, device=x.device) if ctx.affine else None
@@ -529,18 +565,27 @@ class _BatchNormFn(torch.autograd.Function):
         _L.check(lib.cnb_bn_bwd(C.byref(d), _p(x), _p(y), _p(mask), _p(dy), _p(gamma), _p(mean),
                                 _p(rstd), _p(dx), _p(dres), _p(dgamma), _p(dbeta), _p(ws), ws.numel(),
                                 _stream()), "cnb_bn_bwd")
-        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None
+        if lazy:
+            # d_residual = dy where the output ReLU was active.  Its only consumer is the skip-gradient
+            # epilogue of the block's first convolution (_Conv2dSkipFn), which can apply the 1-bit mask
+            # itself: hand it dy and the mask instead of writing a tensor the size of the block output.
+            if len(_LAZY_DRES) > 256:
+                _LAZY_DRES.clear()
+            _LAZY_DRES[dy.data_ptr()] = (mask, dy)
+            dres = dy
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None, None
 
 
 def batch_norm(x, gamma, beta, running_mean, running_var, training, momentum=0.1, eps=1e-5,
-               relu=False, residual=None, partials=None, num_batches_tracked=None):
+               relu=False, residual=None, partials=None, num_batches_tracked=None,
+               lazy_residual_grad=False):
     """Drop-in for F.batch_norm on NCHW feature maps (+ optional fused residual add / ReLU).
     `partials`: the per-tile sums the producing conv2d(..., bn_stats=True) emitted for x.
     `num_batches_tracked`: the module's int64 counter; the statistics epilogue adds 1 to it."""
     return _BatchNormFn.apply(x, residual, gamma, beta, running_mean, running_var, bool(training),
                               float(momentum), float(eps), bool(relu),
                               partials if training else None,
-                              num_batches_tracked if training else None)
+                              num_batches_tracked if training else None, bool(lazy_residual_grad))
 
 
 # ----------------------------------------------------------------------------- element-wise

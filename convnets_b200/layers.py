@@ -237,7 +237,7 @@ class BatchNorm2d(nn.BatchNorm2d):
     fuse_relu = False
 
     def forward(self, x: torch.Tensor, residual: torch.Tensor | None = None,
-                relu: bool | None = None) -> torch.Tensor:
+                relu: bool | None = None, lazy_residual_grad: bool = False) -> torch.Tensor:
         self._check_input_dim(x)
         training = self.training or (self.running_mean is None and self.running_var is None)
         if not training and getattr(x, "_cnb_bn_folded", None) is self:
@@ -262,7 +262,8 @@ class BatchNorm2d(nn.BatchNorm2d):
         partials = getattr(x, "_cnb_bn_partials", None) if training else None
         return F_.batch_norm(x, self.weight, self.bias, rm, rv, training, momentum, self.eps,
                              relu=self.fuse_relu if relu is None else relu, residual=residual,
-                             partials=partials, num_batches_tracked=nbt)
+                             partials=partials, num_batches_tracked=nbt,
+                             lazy_residual_grad=lazy_residual_grad and F_._LAZY_SKIP)
 
 
 class ReLU(nn.ReLU):

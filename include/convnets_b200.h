@@ -122,10 +122,14 @@ int cnb_conv2d_dgrad(const cnb_conv_desc* d, const void* dy, const void* w, cons
 /* dx = conv_transpose(dy, w) + addend[N,H,W,C]: the sum autograd forms where a residual block's
  * input feeds both the first conv and the identity shortcut (reference src/resnet.py:139-156,
  * 176-196), folded into the data-grad epilogue.  Stride-1 convolutions on the tensor-core path only
- * (anything else is CNB_ERR_UNSUPPORTED); dx may alias addend. */
+ * (anything else is CNB_ERR_UNSUPPORTED); dx may alias addend.
+ * addend_mask (may be NULL; needs C % 32 == 0): 1 bit per addend element, bit j of byte (m*C + c)/8
+ * for element (m, c + j) — the ReLU mask cnb_bn_fwd_train wrote for the block output.  With it the
+ * addend is the block-output gradient ITSELF and the epilogue zeroes the elements whose ReLU was
+ * inactive, so BatchNorm backward does not have to write the skip gradient as a tensor. */
 int cnb_conv2d_dgrad_add(const cnb_conv_desc* d, const void* dy, const void* w, const void* w_t,
-                         const void* addend, void* dx, void* workspace, size_t workspace_bytes,
-                         void* stream);
+                         const void* addend, const void* addend_mask, void* dx, void* workspace,
+                         size_t workspace_bytes, void* stream);
 /* dw[K,R,S,C/g] (fp32) = x (*) dy ; dbias[K] (fp32, may be NULL) = sum over N,P,Q of dy */
 int cnb_conv2d_wgrad(const cnb_conv_desc* d, const void* x, const void* dy, float* dw, float* dbias,
                      void* workspace, size_t workspace_bytes, void* stream);

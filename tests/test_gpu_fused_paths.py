@@ -61,7 +61,7 @@ def test_dgrad_add_epilogue(n, c, h, k, r, pad):
     dx0, dx1 = torch.empty_like(sk), torch.empty_like(sk)
     L.check(lib.cnb_conv2d_dgrad(C.byref(d), _p(dyd), _p(wb), _p(wt), _p(dx0), _p(ws), ws.numel(), _st()),
             "dgrad")
-    L.check(lib.cnb_conv2d_dgrad_add(C.byref(d), _p(dyd), _p(wb), _p(wt), _p(sk), _p(dx1), _p(ws),
+    L.check(lib.cnb_conv2d_dgrad_add(C.byref(d), _p(dyd), _p(wb), _p(wt), _p(sk), None, _p(dx1), _p(ws),
                                      ws.numel(), _st()), "dgrad_add")
     torch.cuda.synchronize()
     # the fp32 accumulator is not observable: the fused result (ONE rounding of acc + skip) must lie
@@ -75,10 +75,23 @@ def test_dgrad_add_epilogue(n, c, h, k, r, pad):
     assert O.rel_l2(dx1, dx_ref.double() + skip.double()) <= 1e-2
     # in-place form (dx aliases the addend) is what autograd uses
     inpl = sk.clone()
-    L.check(lib.cnb_conv2d_dgrad_add(C.byref(d), _p(dyd), _p(wb), _p(wt), _p(inpl), _p(inpl), _p(ws),
+    L.check(lib.cnb_conv2d_dgrad_add(C.byref(d), _p(dyd), _p(wb), _p(wt), _p(inpl), None, _p(inpl), _p(ws),
                                      ws.numel(), _st()), "dgrad_add(in place)")
     torch.cuda.synchronize()
     assert torch.equal(inpl, dx1)
+    # masked addend (the lazy skip gradient): bit for bit the plain call on the pre-masked tensor
+    if c % 32 == 0:
+        bits = torch.rand(n, h, h, c) < 0.6                       # NHWC order, like the ReLU mask
+        packed = (bits.view(-1, 8).to(torch.uint8) << torch.arange(8, dtype=torch.uint8)).sum(1).to(torch.uint8)
+        pre = (skip.float() * bits.permute(0, 3, 1, 2).float()).bfloat16().cuda().contiguous(memory_format=CL)
+        dx2, dx3 = torch.empty_like(sk), torch.empty_like(sk)
+        L.check(lib.cnb_conv2d_dgrad_add(C.byref(d), _p(dyd), _p(wb), _p(wt), _p(pre), None, _p(dx2), _p(ws),
+                                         ws.numel(), _st()), "dgrad_add(pre-masked)")
+        L.check(lib.cnb_conv2d_dgrad_add(C.byref(d), _p(dyd), _p(wb), _p(wt), _p(sk), _p(packed.cuda()), _p(dx3),
+                                         _p(ws), ws.numel(), _st()), "dgrad_add(mask)")
+        torch.cuda.synchronize()
+        assert torch.equal(dx2, dx3)
+        assert torch.equal(F_.mask_apply(sk, packed.cuda()), pre)
 
 
 @pytest.mark.parametrize("family,kind", [("ResNet", "18"), ("ResNet", "50"), ("DenseNet", "121"),
