@@ -68,17 +68,33 @@ def _can_fold_skip(blocks, x) -> bool:
             and conv.padding_mode == "zeros" and not isinstance(conv.padding, str))
 
 
+def _is_conv_block(m) -> bool:
+    return isinstance(m, L.Conv2d) or (isinstance(m, nn.Sequential)
+                                       and isinstance(next(iter(m.children()), None), L.Conv2d))
+
+
+def _sole(t, consumer):
+    """Mark `t` as read by `consumer` only — true for the tensors handed from one child of a block body
+    to the next — when that consumer is a plain convolution (block): its data-grad may then form the
+    backward sums of the BatchNorm that produced t (functional._dgrad_with_bn_sums)."""
+    if _is_conv_block(consumer) and hasattr(t, "_cnb_bn_holder"):
+        t._cnb_sole = True
+    return t
+
+
 def _residual_forward_folded(self, blocks, x):
     first = list(blocks[0].children())
-    out, identity = first[0](x, with_skip=True)
+    # x reaches this block only (the parent Sequential hands it over) and is read through the
+    # two-output convolution below, whose data-grad forms the COMPLETE gradient of x
+    out, identity = first[0](_sole(x, first[0]), with_skip=True)
     for m in first[1:]:
         out = m(out)
     last = blocks[-1]
     if isinstance(last, nn.Sequential) and isinstance(next(iter(last.children()), None), nn.Conv2d):
         for blk in blocks[1:-1]:
-            out = blk(out)
+            out = blk(_sole(out, blk))
         conv, bn = _tail(last)
-        out = conv(out)
+        out = conv(_sole(out, conv))
         if bn is not None:
             # `identity` is the alias _Conv2dSkipFn handed out and nothing else reads it: its
             # gradient can stay implicit (block-output gradient + the ReLU bit mask)
@@ -102,10 +118,10 @@ def _residual_forward(self, x):
     last = blocks[-1]
     if isinstance(last, nn.Sequential) and isinstance(next(iter(last.children()), None), nn.Conv2d):
         out = x
-        for blk in blocks[:-1]:
-            out = blk(out)
+        for i, blk in enumerate(blocks[:-1]):
+            out = blk(out if i == 0 else _sole(out, blk))   # x itself also feeds the shortcut
         conv, bn = _tail(last)
-        out = conv(out)
+        out = conv(_sole(out, conv) if len(blocks) > 1 else out)
         if bn is not None:
             return bn(out, residual=identity, relu=True)
         return F_.add_relu(out, identity)

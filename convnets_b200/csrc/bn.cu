@@ -1120,6 +1120,76 @@ static int validate_bn(const cnb_bn_desc* d, const char* who) {
 
 using namespace cnb;
 
+// second half of BatchNorm backward: dx (+ d_residual) from the per-channel coefficients c1..c3
+static int launch_bn_bwd_dx(const cnb_bn_desc* d, const void* x, const void* y, const uint8_t* mask,
+                            const void* dy, const float* save_mean, const float* c1, const float* c2,
+                            const float* c3, void* dx, void* d_residual, int v, bool hot, int variant,
+                            int mode, bool three, cudaStream_t st) {
+  const int C = d->C;
+  const int64_t M = d->M;
+  BnGeom ga = bn_geom(M, C, v, three ? 6 : kStreamWaves);
+  dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
+  const int64_t arows = ga.rows_per_split;
+#define DX_ARGS (const T*)x, (const T*)y, mask, (const T*)dy, save_mean, c1, c2, c3, (T*)dx, \
+                (T*)d_residual, M, C, arows
+#define DX(R, D) \
+  CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_dx_k<T, V, R, D, 2, 2><<<agrid, ablock, 0, st>>>(DX_ARGS)))
+#define DX_HOT(UU, MB)                                                                            \
+  do {                                                                                            \
+    using T = bf16;                                                                               \
+    if (mode == 2 && d_residual) bn_bwd_dx_k<T, 8, 2, true, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS); \
+    else if (mode == 2) bn_bwd_dx_k<T, 8, 2, false, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS);   \
+    else if (mode == 1 && d_residual) bn_bwd_dx_k<T, 8, 1, true, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS); \
+    else if (mode == 1) bn_bwd_dx_k<T, 8, 1, false, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS);   \
+    else if (d_residual) bn_bwd_dx_k<T, 8, 0, true, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS);   \
+    else bn_bwd_dx_k<T, 8, 0, false, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS);                  \
+  } while (0)
+  if (hot && variant == 1) DX_HOT(2, 3);
+  else if (hot && variant == 2) DX_HOT(4, 2);
+  else if (hot && variant == 3) DX_HOT(3, 2);
+  else if (hot && variant == 4) DX_HOT(4, 3);
+  else if (mode == 2 && d_residual) DX(2, true);
+  else if (mode == 2) DX(2, false);
+  else if (mode == 1 && d_residual) DX(1, true);
+  else if (mode == 1) DX(1, false);
+  else if (d_residual) DX(0, true);
+  else DX(0, false);
+#undef DX_HOT
+#undef DX
+#undef DX_ARGS
+  return check_launch("bn_bwd_dx");
+}
+
+// Backward reduction from per-CTA partial rows written by the epilogue of the data-grad that
+// produced dy (conv_tc.cu, bn_x != nullptr): rows[n][2][C] = (sum dy', sum dy' * (x - mean)).  Same
+// fixed-order merge as bn_partials_k, finish of bn_bwd_reduce_k.
+__global__ void __launch_bounds__(kBnThreads)
+bn_bwd_partials_k(const float* __restrict__ rows, float* __restrict__ part, int64_t nrows, int64_t M,
+                  int C, int64_t rows_per_split, int splits, int* __restrict__ counter, BnBwdFin f) {
+  extern __shared__ __align__(16) float red[];
+  const int c0 = blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t r0 = blockIdx.y * rows_per_split;
+  int64_t r1 = r0 + rows_per_split;
+  if (r1 > nrows) r1 = nrows;
+  float s[1] = {0.f}, q[1] = {0.f};
+  if (c0 < C) {
+    for (int64_t r = r0 + threadIdx.y; r < r1; r += blockDim.y) {
+      s[0] += __ldg(rows + (r * 2 + 0) * C + c0);
+      q[0] += __ldg(rows + (r * 2 + 1) * C + c0);
+    }
+  }
+  int c;
+  double S, Q;
+  if (!bn_block_merge<1>(s, q, red, part, C, splits, counter, c, S, Q)) return;
+  const float rs = f.rstd[c];
+  const float g = f.gamma ? f.gamma[c] : 1.f;
+  if (f.dbeta) f.dbeta[c] = (float)S;
+  if (f.dgamma) f.dgamma[c] = (float)(Q * (double)rs);
+  f.c1[c] = g * rs;
+  f.c2[c] = (float)(S / (double)M);
+  f.c3[c] = (float)(Q * (double)rs * (double)rs / (double)M);
+}
+
 extern "C" {
 
 size_t cnb_bn_workspace_bytes(const cnb_bn_desc* d) {
@@ -1478,37 +1548,56 @@ int cnb_bn_bwd(const cnb_bn_desc* d, const void* x, const void* y, const void* r
 #undef RED_ARGS
     CNB_TRY(check_launch("bn_bwd_reduce"));
   }
-  BnGeom ga = bn_geom(M, C, v, three ? 6 : kStreamWaves);
-  dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
-  const int64_t arows = ga.rows_per_split;
-#define DX_ARGS (const T*)x, (const T*)y, mask, (const T*)dy, save_mean, c1, c2, c3, (T*)dx, \
-                (T*)d_residual, M, C, arows
-#define DX(R, D) \
-  CNB_DISPATCH_TV(d->dtype, v, (bn_bwd_dx_k<T, V, R, D, 2, 2><<<agrid, ablock, 0, st>>>(DX_ARGS)))
-#define DX_HOT(UU, MB)                                                                            \
-  do {                                                                                            \
-    using T = bf16;                                                                               \
-    if (mode == 2 && d_residual) bn_bwd_dx_k<T, 8, 2, true, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS); \
-    else if (mode == 2) bn_bwd_dx_k<T, 8, 2, false, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS);   \
-    else if (mode == 1 && d_residual) bn_bwd_dx_k<T, 8, 1, true, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS); \
-    else if (mode == 1) bn_bwd_dx_k<T, 8, 1, false, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS);   \
-    else if (d_residual) bn_bwd_dx_k<T, 8, 0, true, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS);   \
-    else bn_bwd_dx_k<T, 8, 0, false, UU, MB><<<agrid, ablock, 0, st>>>(DX_ARGS);                  \
-  } while (0)
-  if (hot && variant == 1) DX_HOT(2, 3);
-  else if (hot && variant == 2) DX_HOT(4, 2);
-  else if (hot && variant == 3) DX_HOT(3, 2);
-  else if (hot && variant == 4) DX_HOT(4, 3);
-  else if (mode == 2 && d_residual) DX(2, true);
-  else if (mode == 2) DX(2, false);
-  else if (mode == 1 && d_residual) DX(1, true);
-  else if (mode == 1) DX(1, false);
-  else if (d_residual) DX(0, true);
-  else DX(0, false);
-#undef DX_HOT
-#undef DX
-#undef DX_ARGS
-  return check_launch("bn_bwd_dx");
+  return launch_bn_bwd_dx(d, x, y, mask, dy, save_mean, c1, c2, c3, dx, d_residual, v, hot, variant, mode, three, st);
 }
 
+int cnb_bn_bwd_from_partials(const cnb_bn_desc* d, const void* x, const void* relu_mask, const void* dy,
+                             const float* gamma, const float* save_mean, const float* save_rstd,
+                             const float* partials, int32_t n_partials, void* dx, void* d_residual,
+                             float* dgamma, float* dbeta, void* workspace, size_t workspace_bytes,
+                             void* stream) {
+  CNB_TRY(validate_bn(d, "cnb_bn_bwd_from_partials"));
+  CNB_REQUIRE(x && dy && save_mean && save_rstd && dx && workspace && partials && n_partials > 0,
+              CNB_ERR_INVALID, "cnb_bn_bwd_from_partials: null pointer / no rows");
+  const bool relu = d->flags & CNB_BN_RELU;
+  CNB_REQUIRE(relu && relu_mask && d->dtype == CNB_BF16 && d->C % 8 == 0, CNB_ERR_UNSUPPORTED,
+              "cnb_bn_bwd_from_partials: bf16 BatchNorm + ReLU with the 1-bit mask only (C=%d)", d->C);
+  CNB_REQUIRE(workspace_bytes >= bn_ws_bytes(d->C), CNB_ERR_WORKSPACE,
+              "cnb_bn_bwd_from_partials: workspace %zu < %zu", workspace_bytes, bn_ws_bytes(d->C));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int C = d->C;
+  const uint8_t* mask = (const uint8_t*)relu_mask;
+  int v = pick_vec(C, dtype_size(d->dtype), x, dy, dx);
+  if (d_residual)
+    while (v > 1 && (uintptr_t)d_residual % (v * dtype_size(d->dtype)) != 0) v >>= 1;
+  CNB_REQUIRE(v == 8, CNB_ERR_INVALID, "cnb_bn_bwd_from_partials: tensors must be 16-byte aligned");
+  const int variant = bn_bwd_variant();
+  const bool three = variant == 1 || variant == 4;
+  float* part = (float*)workspace;
+  BnGeom g;
+  g.V = 1; g.cx = n_partials <= 512 ? 16 : 64; g.ry = kBnThreads / g.cx;
+  g.cblocks = (int)ceil_div(C, g.cx);
+  g.splits = 1;
+  g.rows_per_split = n_partials;
+  if (n_partials > 512) {
+    int64_t splits = ceil_div((int64_t)sm_count() * 2, g.cblocks);
+    int64_t max_splits = ceil_div((int64_t)n_partials, (int64_t)g.ry * 4);
+    if (splits > max_splits) splits = max_splits;
+    if (splits < 1) splits = 1;
+    g.rows_per_split = ceil_div((int64_t)n_partials, splits);
+    g.splits = (int)ceil_div((int64_t)n_partials, g.rows_per_split);
+  }
+  float* c1 = part + (size_t)2 * C * g.splits;
+  float* c2 = c1 + C;
+  float* c3 = c2 + C;
+  int* counter = bn_counters(g.cblocks);
+  CNB_REQUIRE(counter, CNB_ERR_CUDA, "cnb_bn_bwd_from_partials: cannot allocate the arrival counters");
+  BnBwdFin fin{gamma, save_rstd, dgamma, dbeta, c1, c2, c3};
+  dim3 grid(g.cblocks, g.splits), block(g.cx, g.ry);
+  bn_bwd_partials_k<<<grid, block, 4096, st>>>(partials, part, n_partials, d->M, C, g.rows_per_split, g.splits,
+                                               counter, fin);
+  CNB_TRY(check_launch("bn_bwd_partials"));
+  return launch_bn_bwd_dx(d, x, nullptr, mask, dy, save_mean, c1, c2, c3, dx, d_residual, 8, true, variant, 2, three,
+                          st);
+}
 }  // extern "C"

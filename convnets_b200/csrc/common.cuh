@@ -171,7 +171,9 @@ int conv_tc_fwd(const cnb_conv_desc& d, const void* x, const void* w, const floa
 int conv_tc_stats_rows(const cnb_conv_desc& d);
 int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const void* w_t, void* dx,
                   void* ws, size_t ws_bytes, cudaStream_t st, const void* addend = nullptr,
-                  const void* addend_mask = nullptr);
+                  const void* addend_mask = nullptr, const void* bn_x = nullptr, const void* bn_mask = nullptr,
+                  const float* bn_mean = nullptr, float* bn_partials = nullptr);
+int conv_tc_dgrad_stats_rows(const cnb_conv_desc& d);
 int conv_tc_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* dw, void* ws,
                   size_t ws_bytes, cudaStream_t st);
 

@@ -141,6 +141,37 @@ int cnb_conv2d_dgrad_add(const cnb_conv_desc* d, const void* dy, const void* w, 
   return conv_tc_dgrad(*d, dy, w, w_t, dx, workspace, workspace_bytes, (cudaStream_t)stream, addend, addend_mask);
 }
 
+int cnb_conv2d_dgrad_partial_rows(const cnb_conv_desc* d) {
+  CNB_TRY(validate_conv(d, "cnb_conv2d_dgrad_partial_rows"));
+  const char* why = "";
+  if (is_depthwise(*d) || d->stride_h != 1 || d->stride_w != 1 || d->algo == CNB_ALGO_SIMT ||
+      !conv_tc_supported(*d, CNB_DGRAD, &why))
+    return 0;
+  return conv_tc_dgrad_stats_rows(*d);
+}
+
+int cnb_conv2d_dgrad_bn(const cnb_conv_desc* d, const void* dy, const void* w, const void* w_t,
+                        const void* addend, const void* addend_mask, const void* bn_x,
+                        const void* bn_relu_mask, const float* bn_mean, float* bn_partials, void* dx,
+                        void* workspace, size_t workspace_bytes, void* stream) {
+  CNB_TRY(validate_conv(d, "cnb_conv2d_dgrad_bn"));
+  CNB_REQUIRE(dy && w && dx && bn_x && bn_relu_mask && bn_mean && bn_partials, CNB_ERR_INVALID,
+              "cnb_conv2d_dgrad_bn: null tensor pointer");
+  CNB_REQUIRE(!is_depthwise(*d) && d->stride_h == 1 && d->stride_w == 1, CNB_ERR_UNSUPPORTED,
+              "cnb_conv2d_dgrad_bn: stride-1 tensor-core data-grad only (stride %dx%d, groups %d)",
+              d->stride_h, d->stride_w, d->groups);
+  const char* why = "";
+  CNB_REQUIRE(d->algo != CNB_ALGO_SIMT && conv_tc_supported(*d, CNB_DGRAD, &why), CNB_ERR_UNSUPPORTED,
+              "cnb_conv2d_dgrad_bn: no tensor-core path: %s", why);
+  CNB_REQUIRE(((uintptr_t)dy | (uintptr_t)w | (uintptr_t)dx | (uintptr_t)addend | (uintptr_t)bn_x) % 16 == 0,
+              CNB_ERR_INVALID, "cnb_conv2d_dgrad_bn: tensor pointers must be 16-byte aligned");
+  CNB_REQUIRE(!w_t || (uintptr_t)w_t % 16 == 0, CNB_ERR_INVALID, "cnb_conv2d_dgrad_bn: w_t must be 16-byte aligned");
+  CNB_REQUIRE(!addend_mask || (addend && d->C % 32 == 0), CNB_ERR_UNSUPPORTED,
+              "cnb_conv2d_dgrad_bn: a masked addend needs the addend and C %% 32 == 0 (C=%d)", d->C);
+  return conv_tc_dgrad(*d, dy, w, w_t, dx, workspace, workspace_bytes, (cudaStream_t)stream, addend, addend_mask,
+                       bn_x, bn_relu_mask, bn_mean, bn_partials);
+}
+
 int cnb_conv2d_wgrad(const cnb_conv_desc* d, const void* x, const void* dy, float* dw, float* dbias,
                      void* workspace, size_t workspace_bytes, void* stream) {
   CNB_TRY(validate_conv(d, "cnb_conv2d_wgrad"));

@@ -127,6 +127,13 @@ struct FpropParams {
   const float* bias;
   const bf16* addend;  // optional [M][Kout]: added to the accumulator before the bf16 rounding (kConvAccum)
   const uint8_t* addend_mask;  // EPI == 4: bit (m * Kout + c) selects which addend elements count (1-bit ReLU mask)
+  // data-grad whose output is the gradient of a BatchNorm2d + ReLU output: `stats` then receives that
+  // BatchNorm's BACKWARD sums per CTA row — (sum dy', sum dy' * (x - mean)) with dy' = the stored
+  // output of this kernel where the ReLU bit is set — from bn_x (the BatchNorm's input, [M][Kout]),
+  // bn_mask (its 1-bit ReLU mask) and bn_mean
+  const bf16* bn_x;
+  const uint8_t* bn_mask;
+  const float* bn_mean;
   float* stats;     // optional [persistent CTAs / n_tiles][2][Kout] column sums / sums of squares of the stored output
   int M;            // output pixels in this launch
   int outP, outQ;   // output grid per image (pixel index -> (n, i, j))
@@ -165,7 +172,11 @@ struct FpropParams {
 //           3x3 layer re-fetched 8 KB of filter next to every 16 KB activation tile — a third of
 //           the L2 -> SM traffic that bounds these layers (~50 B / clk / SM, ncu r02c).
 constexpr int kBresIters = 9;
-template <int BLOCK_N, int STAGES, bool IM2COL, int EPI, bool BRES = false>
+//   BNRED : data-grad into a BatchNorm + ReLU output: the column-sum pass forms that BatchNorm's
+//           backward sums (see FpropParams::bn_x) instead of forward statistics.  A template
+//           parameter, not a run-time branch: the extra live values cost the N = 256 variants their
+//           last registers (168-register cap at 320 threads), which the forward kernels must not pay.
+template <int BLOCK_N, int STAGES, bool IM2COL, int EPI, bool BRES = false, bool BNRED = false>
 __global__ void __launch_bounds__(kPersistThreads, 1)
 conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
   // EPI: 0 = bias / ReLU by flags, 1 = plain store, 2 = plain + addend (data-grad + skip gradient),
@@ -345,6 +356,9 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
     for (int i = 0; i < 8; ++i) soff[i] = i * 128 + ((((sc % 64) / 8) ^ i) << 4);  // RPG % 8 == 0
     float as0 = 0.f, as1 = 0.f, aq0 = 0.f, aq1 = 0.f;
     const bool want_stats = p.stats != nullptr;
+    const bool col_ok = n0 + sc < p.Kout;
+    const float mu0 = (BNRED && col_ok) ? p.bn_mean[n0 + sc] : 0.f;
+    const float mu1 = (BNRED && col_ok) ? p.bn_mean[n0 + sc + 1] : 0.f;
 
     uint32_t lt = 0;
     for (int mt = m_first; mt < p.m_tiles; mt += m_step, ++lt) {
@@ -473,7 +487,38 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
         }
         __syncwarp();
       }
-      if (want_stats) {
+      if (BNRED) {
+        // backward sums of the BatchNorm whose output gradient this tile is: the staged (stored) dy,
+        // the ReLU bit and the BatchNorm input x of the same element.  8 rows of x / mask are
+        // requested before they are used.
+        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+        const int rows_left = p.M - m0 - rg * RPG;
+        if (col_ok) {
+          const int64_t e0 = ((int64_t)m0 + rg * RPG) * p.Kout + n0 + sc;
+          const int sh = sc & 7;
+#pragma unroll
+          for (int r8 = 0; r8 < RPG / 8; ++r8) {
+            uint32_t xv[8], mb[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const bool ok = r8 * 8 + i < rows_left;
+              const int64_t e = e0 + (int64_t)(r8 * 8 + i) * p.Kout;
+              xv[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(p.bn_x + e)) : 0u;
+              mb[i] = ok ? (uint32_t)__ldg(p.bn_mask + (e >> 3)) : 0u;
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const uint32_t w2 = lds_u32(col_addr + r8 * 1024 + soff[i]);
+              const uint32_t bits = mb[i] >> sh;
+              const float ga = (bits & 1u) ? __uint_as_float(w2 << 16) : 0.f;
+              const float gb = (bits & 2u) ? __uint_as_float(w2 & 0xffff0000u) : 0.f;
+              s0 += ga; q0 = fmaf(ga, __uint_as_float(xv[i] << 16) - mu0, q0);
+              s1 += gb; q1 = fmaf(gb, __uint_as_float(xv[i] & 0xffff0000u) - mu1, q1);
+            }
+          }
+        }
+        as0 += s0; as1 += s1; aq0 += q0; aq1 += q1;
+      } else if (want_stats) {
         // BatchNorm statistics of this tile from the staged (bf16-rounded, i.e. as stored) values.
         // Rows past the end of the tensor are zero (TMA zero-fill x weights) unless a bias was
         // added, so only the generic variant needs the row bound.
@@ -849,6 +894,9 @@ struct FpropLaunch {
   const float* bias;
   const void* addend;            // optional [M][Kout] bf16 summed into the output (data-grad + skip gradient)
   const void* addend_mask;       // optional 1-bit mask over the addend (M*Kout/8 bytes, Kout % 32 == 0)
+  const void* bn_x;              // data-grad into a BatchNorm + ReLU output: that layer's input, mask, mean
+  const void* bn_mask;
+  const float* bn_mean;
   float* stats;                  // optional BatchNorm partials (forward only)
   int flags;
   bool tiled2d;                  // pure GEMM: A is the [M, C] matrix itself
@@ -871,14 +919,14 @@ static int fprop_block_n(int Kout, bool grouped) {
   return Kout <= 64 ? 64 : (Kout <= 128 ? 128 : 256);
 }
 
-template <int BLOCK_N, int STAGES, bool IM2COL, int EPI, bool BRES = false>
+template <int BLOCK_N, int STAGES, bool IM2COL, int EPI, bool BRES = false, bool BNRED = false>
 static int launch_fprop_persist_inst(const FpropParams& prm, cudaStream_t st) {
   constexpr int STAGE_BYTES = BRES ? A_TILE_BYTES : A_TILE_BYTES + BLOCK_N * TILE_K * 2;
   constexpr size_t smem = (size_t)STAGES * STAGE_BYTES + (BRES ? (size_t)kBresIters * BLOCK_N * TILE_K * 2 : 0) +
                           (size_t)TILE_M * BLOCK_N * 2 + (2 * STAGES + 5) * 8 + 16 + 1024;
   static_assert(smem <= 232448, "exceeds the 227 KB dynamic shared memory limit");
   static bool attr_done = false;
-  auto kern = conv_fprop_tc_persist_k<BLOCK_N, STAGES, IM2COL, EPI, BRES>;
+  auto kern = conv_fprop_tc_persist_k<BLOCK_N, STAGES, IM2COL, EPI, BRES, BNRED>;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cudaFuncSetAttribute(fprop persistent): %s",
@@ -900,13 +948,13 @@ static bool bres_enabled() {
   return v == 1;
 }
 
-template <bool IM2COL, int EPI>
+template <bool IM2COL, int EPI, bool BNRED = false>
 static int launch_fprop_bn(const FpropParams& prm, int BLOCK_N, cudaStream_t st) {
   if (BLOCK_N == 64 && prm.num_taps * prm.num_cblk <= kBresIters && bres_enabled())
-    return launch_fprop_persist_inst<64, 8, IM2COL, EPI, true>(prm, st);
-  if (BLOCK_N == 64) return launch_fprop_persist_inst<64, 8, IM2COL, EPI>(prm, st);
-  if (BLOCK_N == 128) return launch_fprop_persist_inst<128, 5, IM2COL, EPI>(prm, st);
-  return launch_fprop_persist_inst<256, 3, IM2COL, EPI>(prm, st);
+    return launch_fprop_persist_inst<64, 8, IM2COL, EPI, true, BNRED>(prm, st);
+  if (BLOCK_N == 64) return launch_fprop_persist_inst<64, 8, IM2COL, EPI, false, BNRED>(prm, st);
+  if (BLOCK_N == 128) return launch_fprop_persist_inst<128, 5, IM2COL, EPI, false, BNRED>(prm, st);
+  return launch_fprop_persist_inst<256, 3, IM2COL, EPI, false, BNRED>(prm, st);
 }
 
 static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
@@ -961,6 +1009,11 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
   prm.flags = L.flags & ((L.bias ? CNB_CONV_BIAS : 0) | CNB_CONV_RELU);
   prm.addend = reinterpret_cast<const bf16*>(L.addend);
   prm.addend_mask = reinterpret_cast<const uint8_t*>(L.addend_mask);
+  prm.bn_x = reinterpret_cast<const bf16*>(L.bn_x);
+  prm.bn_mask = reinterpret_cast<const uint8_t*>(L.bn_mask);
+  prm.bn_mean = L.bn_mean;
+  CNB_REQUIRE(!L.bn_x || (L.stats && L.bn_mask && L.bn_mean && L.Kout % 8 == 0), CNB_ERR_INVALID,
+              "conv_tc: BatchNorm backward sums need the partial table, the bit mask and the mean");
   if (L.addend) prm.flags |= kConvAccum;
   CNB_REQUIRE(!L.addend_mask || (L.addend && L.Kout % 32 == 0), CNB_ERR_UNSUPPORTED,
               "conv_tc: a masked addend needs the addend and Kout %% 32 == 0 (Kout=%d)", L.Kout);
@@ -977,6 +1030,17 @@ static int launch_fprop(const FpropLaunch& L, cudaStream_t st) {
     CNB_REQUIRE(epi == 1 && !L.tiled2d && !L.stats, CNB_ERR_UNSUPPORTED,
                 "conv_tc: the scattering epilogue is a plain im2col store");
     return launch_fprop_bn<true, 3>(prm, BLOCK_N, st);
+  }
+  if (prm.bn_x) {   // data-grad + BatchNorm backward sums
+    CNB_REQUIRE(epi != 0, CNB_ERR_UNSUPPORTED, "conv_tc: BatchNorm backward sums do not combine with bias / ReLU");
+    if (L.tiled2d) {
+      if (epi == 1) return launch_fprop_bn<false, 1, true>(prm, BLOCK_N, st);
+      if (L.addend_mask) return launch_fprop_bn<false, 4, true>(prm, BLOCK_N, st);
+      return launch_fprop_bn<false, 2, true>(prm, BLOCK_N, st);
+    }
+    if (epi == 1) return launch_fprop_bn<true, 1, true>(prm, BLOCK_N, st);
+    if (L.addend_mask) return launch_fprop_bn<true, 4, true>(prm, BLOCK_N, st);
+    return launch_fprop_bn<true, 2, true>(prm, BLOCK_N, st);
   }
   if (L.tiled2d) {
     if (epi == 1) return launch_fprop_bn<false, 1>(prm, BLOCK_N, st);
@@ -1190,6 +1254,13 @@ int conv_tc_stats_rows(const cnb_conv_desc& d) {
   return persist_grid(ceil_div((int64_t)d.N * P * Q, TILE_M), n_tiles) / n_tiles;
 }
 
+// rows of the table a stride-1 data-grad writes when it also forms BatchNorm backward sums
+int conv_tc_dgrad_stats_rows(const cnb_conv_desc& d) {
+  const int BLOCK_N = fprop_block_n(d.C, d.groups > 1);
+  const int n_tiles = (d.C + BLOCK_N - 1) / BLOCK_N;
+  return persist_grid(ceil_div((int64_t)d.N * d.H * d.W, TILE_M), n_tiles) / n_tiles;
+}
+
 int conv_tc_fwd(const cnb_conv_desc& d, const void* x, const void* w, const float* bias, void* y,
                 float* stats, void* ws, size_t ws_bytes, cudaStream_t st) {
   FpropLaunch L;
@@ -1232,7 +1303,8 @@ int conv_tc_fwd(const cnb_conv_desc& d, const void* x, const void* w, const floa
 }
 
 int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const void* w_t, void* dx,
-                  void* ws, size_t ws_bytes, cudaStream_t st, const void* addend, const void* addend_mask) {
+                  void* ws, size_t ws_bytes, cudaStream_t st, const void* addend, const void* addend_mask,
+                  const void* bn_x, const void* bn_mask, const float* bn_mean, float* bn_partials) {
   CNB_REQUIRE(!addend || (d.stride_h == 1 && d.stride_w == 1), CNB_ERR_UNSUPPORTED,
               "conv_tc_dgrad: the accumulating epilogue exists for stride-1 data-grad only");
   CNB_REQUIRE(ws && ws_bytes >= conv_tc_workspace(d, CNB_DGRAD), CNB_ERR_WORKSPACE,
@@ -1286,13 +1358,16 @@ int conv_tc_dgrad(const cnb_conv_desc& d, const void* dy, const void* w, const v
     L.out = dx; L.bias = nullptr; L.flags = 0;
     L.addend = addend;
     L.addend_mask = addend_mask;
+    L.bn_x = bn_x; L.bn_mask = bn_mask; L.bn_mean = bn_mean;
+    L.stats = bn_x ? bn_partials : nullptr;
     L.tiled2d = (RS == 1 && d.pad_h == 0 && d.pad_w == 0);
     return launch_fprop(L, st);
   }
 
   // ---- strided: one stride-1 sub-convolution per output parity class (a, b), each writing its
   // pixels of dx directly; classes without a tap are zero-filled by one small kernel
-  CNB_REQUIRE(!addend, CNB_ERR_UNSUPPORTED, "conv_tc_dgrad: the addend epilogue is stride-1 only");
+  CNB_REQUIRE(!addend && !bn_x, CNB_ERR_UNSUPPORTED,
+              "conv_tc_dgrad: the addend / BatchNorm-sum epilogues are stride-1 only");
   uint32_t zero_mask = 0;
   for (int a = 0; a < d.stride_h; ++a)
     for (int b = 0; b < d.stride_w; ++b) {

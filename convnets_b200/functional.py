@@ -185,7 +185,8 @@ def _conv_desc(x_shape, w_shape, stride, padding, dilation, groups, dtype_code, 
 class _Conv2dFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, wpack, stride, padding, dilation, groups, algo, want_stats,
-                wpack_t=None, relu=False):
+                wpack_t=None, relu=False, bn_holder=None):
+        ctx.bn_holder = bn_holder
         _cuda(x, wpack, bias)
         lib = _L.load()
         x = _nhwc(x)
@@ -229,8 +230,9 @@ class _Conv2dFn(torch.autograd.Function):
             dx = torch.empty_like(x, memory_format=_CL)
             nws = lib.cnb_conv2d_workspace_bytes(C.byref(d), _L.CNB_DGRAD)
             ws = _workspace(nws, x.device)
-            _L.check(lib.cnb_conv2d_dgrad(C.byref(d), _p(dy), _p(wpack), _p(wpack_t), _p(dx), _p(ws),
-                                          ws.numel(), _stream()), "cnb_conv2d_dgrad")
+            if not _dgrad_with_bn_sums(ctx, lib, d, dy, wpack, wpack_t, None, None, dx, ws):
+                _L.check(lib.cnb_conv2d_dgrad(C.byref(d), _p(dy), _p(wpack), _p(wpack_t), _p(dx), _p(ws),
+                                              ws.numel(), _stream()), "cnb_conv2d_dgrad")
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
             dw = torch.empty(tuple(wpack.shape), dtype=torch.float32, device=x.device,
                              memory_format=_CL)
@@ -242,11 +244,40 @@ class _Conv2dFn(torch.autograd.Function):
                                           ws.numel(), _stream()), "cnb_conv2d_wgrad")
             if tuple(dw.shape) != ctx.wshape:  # zero-padded input channels (RGB stem)
                 dw = dw[:, :ctx.wshape[1]].contiguous(memory_format=_CL)
-        return dx, dw, db, None, None, None, None, None, None, None, None, None
+        return dx, dw, db, None, None, None, None, None, None, None, None, None, None
+
+
+# BatchNorm backward sums from the data-grad epilogue (cnb_conv2d_dgrad_bn): a conv whose input x is
+# the output of a BatchNorm2d + ReLU, AND is that output's only consumer, computes dx — which is that
+# BatchNorm's dy — and can form sum dy', sum dy' * (x_bn - mean) from the tile it just stored.  The
+# BatchNorm layer hands a `holder` (its input, bit mask and batch mean) forward on its output tensor;
+# the block forwards of convert.py mark tensors they know to be single-use (`_cnb_sole`); the conv
+# leaves the partial table in the holder, keyed by dx's address, and BatchNorm backward skips its
+# reduction pass when the gradient that arrives is that very tensor.  CNB_BN_BWD_SUMS=0 turns it off.
+_BN_BWD_SUMS = __import__("os").environ.get("CNB_BN_BWD_SUMS", "1") == "1"
+
+
+def _dgrad_with_bn_sums(ctx, lib, d, dy, wpack, wpack_t, addend, amask, dx, ws) -> bool:
+    h = getattr(ctx, "bn_holder", None)
+    if not (_BN_BWD_SUMS and h and "x" in h and d.stride_h == 1 and d.stride_w == 1
+            and d.algo != _L.CNB_ALGO_SIMT and dx.dtype == torch.bfloat16):
+        return False
+    bx = h["x"]
+    if tuple(bx.shape) != tuple(dx.shape) or bx.dtype != dx.dtype or not bx.is_contiguous(memory_format=_CL):
+        return False
+    rows = lib.cnb_conv2d_dgrad_partial_rows(C.byref(d))
+    if rows <= 0:
+        return False
+    part = torch.empty((rows, 2, dx.shape[1]), dtype=torch.float32, device=dx.device)
+    _L.check(lib.cnb_conv2d_dgrad_bn(C.byref(d), _p(dy), _p(wpack), _p(wpack_t), _p(addend), _p(amask),
+                                     _p(bx), _p(h["mask"]), _p(h["mean"]), _p(part), _p(dx), _p(ws),
+                                     ws.numel(), _stream()), "cnb_conv2d_dgrad_bn")
+    h["bwd"] = (part, dx.data_ptr(), dx)
+    return True
 
 
 def conv2d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, wpack=None,
-           algo=_L.CNB_ALGO_AUTO, bn_stats=False, wpack_t=None, relu=False):
+           algo=_L.CNB_ALGO_AUTO, bn_stats=False, wpack_t=None, relu=False, bn_holder=None):
     """Drop-in for F.conv2d as reached from nn.Conv2d (reference src/basemodel.py:974,992).
     `weight` is the fp32 master parameter; `wpack` an optional pre-packed operand copy.
     With `bn_stats` returns (y, partials): the per-tile BatchNorm partial sums emitted by the
@@ -256,7 +287,7 @@ def conv2d(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, wpac
         wpack = pack_weight(weight, x.dtype)
     y, part = _Conv2dFn.apply(x, weight, bias, wpack, _pair(stride), _pair(padding),
                               _pair(dilation), int(groups), int(algo), bool(bn_stats), wpack_t,
-                              bool(relu))
+                              bool(relu), bn_holder)
     if bn_stats:
         return y, (part if part.shape[0] > 0 else None)
     return y
@@ -272,9 +303,9 @@ class _Conv2dSkipFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, weight, bias, wpack, stride, padding, dilation, groups, algo, want_stats,
-                wpack_t=None):
+                wpack_t=None, bn_holder=None):
         y, part = _Conv2dFn.forward(ctx, x, weight, bias, wpack, stride, padding, dilation, groups,
-                                    algo, want_stats, wpack_t)
+                                    algo, want_stats, wpack_t, False, bn_holder)
         return y, part, x.view_as(x)
 
     @staticmethod
@@ -307,7 +338,9 @@ class _Conv2dSkipFn(torch.autograd.Function):
             # cannot mask in the epilogue: materialise the masked gradient after all
             dskip = mask_apply(dskip, amask)
             amask = None
-        if fused:
+        if fused and _dgrad_with_bn_sums(ctx, lib, d, dy, wpack, wpack_t, dskip, amask, dx, ws):
+            pass
+        elif fused:
             _L.check(lib.cnb_conv2d_dgrad_add(C.byref(d), _p(dy), _p(wpack), _p(wpack_t), _p(dskip),
                                               _p(amask), _p(dx), _p(ws), ws.numel(), _stream()),
                      "cnb_conv2d_dgrad_add")
@@ -327,7 +360,7 @@ class _Conv2dSkipFn(torch.autograd.Function):
                                           ws.numel(), _stream()), "cnb_conv2d_wgrad")
             if tuple(dw.shape) != ctx.wshape:
                 dw = dw[:, :ctx.wshape[1]].contiguous(memory_format=_CL)
-        return dx, dw, db, None, None, None, None, None, None, None, None
+        return dx, dw, db, None, None, None, None, None, None, None, None, None
 
 
 def mask_apply(t: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
@@ -340,13 +373,14 @@ def mask_apply(t: torch.Tensor, mask: torch.Tensor) -> torch.Tensor:
 
 
 def conv2d_with_skip(x, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, wpack=None,
-                     algo=_L.CNB_ALGO_AUTO, bn_stats=False, wpack_t=None):
+                     algo=_L.CNB_ALGO_AUTO, bn_stats=False, wpack_t=None, bn_holder=None):
     """conv2d(x, ...) plus an alias of x for the identity shortcut: returns (y, partials-or-None,
     x_skip).  See _Conv2dSkipFn."""
     if wpack is None:
         wpack = pack_weight(weight, x.dtype)
     y, part, xs = _Conv2dSkipFn.apply(x, weight, bias, wpack, _pair(stride), _pair(padding),
-                                      _pair(dilation), int(groups), int(algo), bool(bn_stats), wpack_t)
+                                      _pair(dilation), int(groups), int(algo), bool(bn_stats), wpack_t,
+                                      bn_holder)
     return y, (part if (bn_stats and part.shape[0] > 0) else None), xs
 
 
@@ -489,7 +523,7 @@ _LAZY_SKIP = __import__("os").environ.get("CNB_LAZY_SKIP_GRAD", "1") == "1"
 class _BatchNormFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps,
-                relu, partials, nbt=None, lazy_dres=False):
+                relu, partials, nbt=None, lazy_dres=False, holder=None):
         _cuda(x, residual, gamma, beta)
         lib = _L.load()
         x = _nhwc(x)
@@ -528,6 +562,9 @@ class _BatchNormFn(torch.autograd.Function):
                                           ws.numel(), _stream()), "cnb_bn_fwd_train")
             ctx.save_for_backward(x, (y if mask is None else None) if relu else None, mask, g32,
                                   mean, rstd)
+            if holder is not None and mask is not None:
+                # what a sole consumer's data-grad needs to form this layer's backward sums
+                holder["x"], holder["mask"], holder["mean"] = x, mask, mean
         else:
             _L.check(lib.cnb_bn_fwd_eval(C.byref(d), _p(x), _p(residual), _p(g32), _p(b32),
                                          _p(running_mean), _p(running_var), _p(y), _p(ws), ws.numel(),
@@ -538,6 +575,7 @@ class _BatchNormFn(torch.autograd.Function):
         ctx.has_res = residual is not None
         ctx.affine = gamma is not None
         # lazy residual gradient: see _LAZY_DRES
+        ctx.holder = holder
         ctx.lazy_dres = bool(lazy_dres and training and residual is not None and relu
                              and x.dtype == torch.bfloat16 and c % 32 == 0)
         return y
@@ -562,9 +600,19 @@ class _BatchNormFn(torch.autograd.Function):
         dgamma = torch.empty(c, dtype=torch.float32, device=x.device) if ctx.affine else None
         dbeta = torch.empty(c, dtype=torch.float32, device=x.device) if ctx.affine else None
         ws = _workspace(lib.cnb_bn_workspace_bytes(C.byref(d)), x.device)
-        _L.check(lib.cnb_bn_bwd(C.byref(d), _p(x), _p(y), _p(mask), _p(dy), _p(gamma), _p(mean),
-                                _p(rstd), _p(dx), _p(dres), _p(dgamma), _p(dbeta), _p(ws), ws.numel(),
-                                _stream()), "cnb_bn_bwd")
+        h = getattr(ctx, "holder", None)
+        sums = h.pop("bwd", None) if h else None
+        if sums is not None and mask is not None and sums[1] == dy.data_ptr() and sums[2].shape == dy.shape:
+            # the data-grad that produced dy already formed sum dy', sum dy' * (x - mean) (_dgrad_with_bn_sums)
+            part = sums[0]
+            _L.check(lib.cnb_bn_bwd_from_partials(C.byref(d), _p(x), _p(mask), _p(dy), _p(gamma), _p(mean),
+                                                  _p(rstd), _p(part), part.shape[0], _p(dx), _p(dres),
+                                                  _p(dgamma), _p(dbeta), _p(ws), ws.numel(), _stream()),
+                     "cnb_bn_bwd_from_partials")
+        else:
+            _L.check(lib.cnb_bn_bwd(C.byref(d), _p(x), _p(y), _p(mask), _p(dy), _p(gamma), _p(mean),
+                                    _p(rstd), _p(dx), _p(dres), _p(dgamma), _p(dbeta), _p(ws), ws.numel(),
+                                    _stream()), "cnb_bn_bwd")
         if lazy:
             # d_residual = dy where the output ReLU was active.  Its only consumer is the skip-gradient
             # epilogue of the block's first convolution (_Conv2dSkipFn), which can apply the 1-bit mask
@@ -573,7 +621,7 @@ class _BatchNormFn(torch.autograd.Function):
                 _LAZY_DRES.clear()
             _LAZY_DRES[dy.data_ptr()] = (mask, dy)
             dres = dy
-        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None, None
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None, None, None
 
 
 def batch_norm(x, gamma, beta, running_mean, running_var, training, momentum=0.1, eps=1e-5,
@@ -581,11 +629,16 @@ def batch_norm(x, gamma, beta, running_mean, running_var, training, momentum=0.1
                lazy_residual_grad=False):
     """Drop-in for F.batch_norm on NCHW feature maps (+ optional fused residual add / ReLU).
     `partials`: the per-tile sums the producing conv2d(..., bn_stats=True) emitted for x.
-    `num_batches_tracked`: the module's int64 counter; the statistics epilogue adds 1 to it."""
-    return _BatchNormFn.apply(x, residual, gamma, beta, running_mean, running_var, bool(training),
-                              float(momentum), float(eps), bool(relu),
-                              partials if training else None,
-                              num_batches_tracked if training else None, bool(lazy_residual_grad))
+    `num_batches_tracked`: the module's int64 counter; the statistics epilogue adds 1 to it.
+    In training with a fused ReLU the result carries `_cnb_bn_holder` (see _dgrad_with_bn_sums)."""
+    holder = {} if (training and relu and _BN_BWD_SUMS and torch.is_grad_enabled()) else None
+    y = _BatchNormFn.apply(x, residual, gamma, beta, running_mean, running_var, bool(training),
+                           float(momentum), float(eps), bool(relu),
+                           partials if training else None,
+                           num_batches_tracked if training else None, bool(lazy_residual_grad), holder)
+    if holder:
+        y._cnb_bn_holder = holder
+    return y
 
 
 # ----------------------------------------------------------------------------- element-wise

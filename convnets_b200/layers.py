@@ -191,11 +191,14 @@ class Conv2d(nn.Conv2d):
                 and _FOLD_BN):
             return self._forward_folded(x, bn)
         stats = self.emit_bn_stats and self.training
+        # x is the output of a BatchNorm + ReLU and this conv its only reader (marked by the block
+        # forward): the data-grad epilogue will also form that BatchNorm's backward sums
+        holder = getattr(x, "_cnb_bn_holder", None) if getattr(x, "_cnb_sole", False) else None
         if with_skip:
             wpack, wpack_t = self._packed(x.dtype)
             y, part, xs = F_.conv2d_with_skip(x, self.weight, self.bias, self.stride, self.padding,
                                               self.dilation, self.groups, wpack=wpack, algo=self.algo,
-                                              bn_stats=stats, wpack_t=wpack_t)
+                                              bn_stats=stats, wpack_t=wpack_t, bn_holder=holder)
             return self._tag((y, part)), xs
         if self.cast_input and self.compute_dtype is not None and not x.requires_grad:
             # network entry: fp32 NCHW batch -> compute dtype NHWC.  A stem whose channel count
@@ -209,7 +212,7 @@ class Conv2d(nn.Conv2d):
         wpack, wpack_t = self._packed(x.dtype)
         return self._tag(F_.conv2d(x, self.weight, self.bias, self.stride, self.padding,
                                    self.dilation, self.groups, wpack=wpack, algo=self.algo,
-                                   bn_stats=stats, wpack_t=wpack_t))
+                                   bn_stats=stats, wpack_t=wpack_t, bn_holder=holder))
 
 
     def _forward_folded(self, x: torch.Tensor, bn) -> torch.Tensor:

@@ -66,6 +66,9 @@ SIGNATURES = {
     "cnb_conv2d_fwd": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_conv2d_dgrad": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_conv2d_dgrad_add": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
+    "cnb_conv2d_dgrad_partial_rows": (_I, [C.POINTER(ConvDesc)]),
+    "cnb_conv2d_dgrad_bn": (_I, [C.POINTER(ConvDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
+    "cnb_bn_bwd_from_partials": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _I32, _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_rowim2col_nchw": (_I, [C.POINTER(ConvDesc), _P, _P, _I32, _P]),
     "cnb_pack_filter": (_I, [_P, _P, _P, _I32, _I32, _I32, _P]),
     "cnb_pack_filter_blocks": (_I64, [_I32, _I32, _I32]),

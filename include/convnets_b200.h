@@ -130,6 +130,18 @@ int cnb_conv2d_dgrad(const cnb_conv_desc* d, const void* dy, const void* w, cons
 int cnb_conv2d_dgrad_add(const cnb_conv_desc* d, const void* dy, const void* w, const void* w_t,
                          const void* addend, const void* addend_mask, void* dx, void* workspace,
                          size_t workspace_bytes, void* stream);
+/* Data-grad whose output IS the gradient of a BatchNorm2d + ReLU output (conv -> BN -> ReLU -> conv,
+ * reference src/basemodel.py:1004-1015 inside src/resnet.py:159-196): besides dx (optionally + addend,
+ * as cnb_conv2d_dgrad_add) the epilogue forms that BatchNorm's backward sums from the tile it just
+ * stored — per CTA row of bn_partials[rows][2][C] (fp32): sum dx', sum dx' * (bn_x - bn_mean), dx' =
+ * dx where the ReLU bit is set — so cnb_bn_bwd_from_partials needs no reduction pass over x and dy.
+ * bn_x [N,H,W,C]: the BatchNorm's input; bn_relu_mask: the 1-bit mask cnb_bn_fwd_train wrote; rows =
+ * cnb_conv2d_dgrad_partial_rows(d) (0: this shape has no such path). */
+int cnb_conv2d_dgrad_partial_rows(const cnb_conv_desc* d);
+int cnb_conv2d_dgrad_bn(const cnb_conv_desc* d, const void* dy, const void* w, const void* w_t,
+                        const void* addend, const void* addend_mask, const void* bn_x,
+                        const void* bn_relu_mask, const float* bn_mean, float* bn_partials, void* dx,
+                        void* workspace, size_t workspace_bytes, void* stream);
 /* dw[K,R,S,C/g] (fp32) = x (*) dy ; dbias[K] (fp32, may be NULL) = sum over N,P,Q of dy */
 int cnb_conv2d_wgrad(const cnb_conv_desc* d, const void* x, const void* dy, float* dw, float* dbias,
                      void* workspace, size_t workspace_bytes, void* stream);
@@ -148,6 +160,13 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
                      float* save_mean, float* save_rstd, const float* conv_partials,
                      int32_t n_partials, void* relu_mask, void* workspace, size_t workspace_bytes,
                      void* stream);
+/* backward from the sums a data-grad epilogue already formed (cnb_conv2d_dgrad_bn): finish + dx pass
+ * only.  bf16, CNB_BN_RELU with the 1-bit mask, C % 8 == 0. */
+int cnb_bn_bwd_from_partials(const cnb_bn_desc* d, const void* x, const void* relu_mask, const void* dy,
+                             const float* gamma, const float* save_mean, const float* save_rstd,
+                             const float* partials, int32_t n_partials, void* dx, void* d_residual,
+                             float* dgamma, float* dbeta, void* workspace, size_t workspace_bytes,
+                             void* stream);
 /* ---- concat-aware BatchNorm: DenseNet's BatchNorm2d over torch.cat([x, out], 1) (reference
  * src/densenet.py:117,124,131-140) when the block keeps its feature maps in one [M, C_total] buffer.
  * Layer l normalises the channel prefix [0, C_l) of the buffer: x has a row stride != C.

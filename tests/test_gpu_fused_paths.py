@@ -238,3 +238,50 @@ def test_depthwise_emits_batchnorm_partials(n, c, h, w, stride, dtype):
         a = F.batch_norm(y1, gam, bet, None, None, True, 0.1, 1e-5, relu=True, partials=part)
         b = F.batch_norm(y1, gam, bet, None, None, True, 0.1, 1e-5, relu=True)
         assert O.rel_l2(a, b) <= (1e-2 if dtype == torch.bfloat16 else 1e-5)
+
+
+# ------------------------------------------------------------------ BatchNorm backward sums / lazy skip gradient
+def _one_step_grads(monkeypatch, family, kind, sums, lazy, hw=64, batch=8):
+    import convnets_b200 as cnb
+    from convnets_b200 import functional as F_
+    from convnets_b200 import zoo as M
+    monkeypatch.setattr(F_, "_BN_BWD_SUMS", sums)
+    monkeypatch.setattr(F_, "_LAZY_SKIP", lazy)
+    torch.manual_seed(21)
+    s = M.Settings(kind=kind, input_size=(3, hw, hw), num_classes=10, dropout_rate=0.0)
+    s.device.set_device("cuda:0")
+    model = cnb.convert(M.FAMILIES[family](s))
+    s.device.move(model)
+    model.train()
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(batch, 3, hw, hw, generator=g).cuda()
+    y = torch.randint(0, 10, (batch,), generator=g).cuda()
+    from convnets_b200 import lib as L
+    n0 = L.launch_count()
+    logits = model(x)
+    model.cost_function(logits.float(), y).backward()
+    torch.cuda.synchronize()
+    return logits.detach().float(), {k: p.grad.detach().clone() for k, p in model.named_parameters()}, \
+        L.launch_count() - n0
+
+
+@pytest.mark.parametrize("family,kind,hw", [("ResNet", "18", 64), ("ResNet", "50", 64), ("ResNet", "50", 224),
+                                            ("ResNeXt", "50", 64)])
+def test_bn_backward_sums_and_lazy_skip_gradient_vs_plain(monkeypatch, family, kind, hw):
+    """cnb_conv2d_dgrad_bn + cnb_bn_bwd_from_partials (BatchNorm backward sums formed by the data-grad
+    epilogue) and the masked-addend skip gradient against the plain kernels on the same step: the
+    forward is the same code, so the logits are bit-identical, and the gradients may differ only by
+    the order of fp32 sums and a handful of bf16 roundings downstream of them."""
+    batch = 4 if hw == 224 else 8
+    l0, g0, n0 = _one_step_grads(monkeypatch, family, kind, False, False, hw, batch)
+    for sums, lazy in ((True, False), (False, True), (True, True)):
+        l1, g1, n1 = _one_step_grads(monkeypatch, family, kind, sums, lazy, hw, batch)
+        assert torch.equal(l0, l1)
+        gsum = sum(v.norm().item() for v in g0.values())
+        errs = sorted((O.rel_l2(g1[k], g0[k]), k) for k in g0 if g0[k].norm().item() > 1e-6 * gsum)
+        med, worst = errs[len(errs) // 2], errs[-1]
+        print(f"{family}-{kind} {hw}: sums={sums} lazy={lazy}: launches {n0} -> {n1}, grads vs plain median "
+              f"{med[0]:.2e} max {worst[0]:.2e} ({worst[1]})")
+        if sums:
+            assert n1 < n0, "no BatchNorm reduction kernel was saved"
+        assert med[0] <= 2e-2 and worst[0] <= 2e-1, (med, worst)
