@@ -227,8 +227,12 @@ def call_cost(name, a):
             in_pix = d["N"] * P * Q
         byts = (in_pix * d["C"] + d["N"] * P * Q * d["K"]) * es + \
             d["K"] * (d["C"] // d["groups"]) * d["R"] * d["S"] * es
-        if name == "cnb_conv2d_dgrad_add":
+        nulls = a[-1].get("_nulls", []) if isinstance(a[-1], dict) else []
+        if name == "cnb_conv2d_dgrad_add" or (name == "cnb_conv2d_dgrad_bn" and 4 not in nulls):
             byts += d["N"] * d["H"] * d["W"] * d["C"] * es   # the skip-gradient addend
+        if name == "cnb_conv2d_dgrad_bn":
+            # the BatchNorm input and bit mask the epilogue reads for the backward sums
+            byts += d["N"] * d["H"] * d["W"] * d["C"] * (es + 1.0 / 8)
         if d["groups"] == d["C"] and d["groups"] > 1:
             key = name + "(depthwise)"
     elif name.startswith("cnb_bn_") and a and isinstance(a[0], dict):
@@ -237,15 +241,23 @@ def call_cost(name, a):
         # backward only when no bit mask exists (fp32-IO, or C % 8 != 0).
         d = a[0]
         es = 2 if d["dtype"] == 1 else 4
-        n_t = {"cnb_bn_fwd_train": 2, "cnb_bn_fwd_eval": 2, "cnb_bn_bwd": 3}[name]
-        if d["flags"] & 2:
+        nulls = a[-1].get("_nulls", []) if isinstance(a[-1], dict) else []
+        # position of the d_residual argument: the residual gradient counts only when it is written
+        # (the lazy skip gradient leaves it implicit)
+        dres_at = {"cnb_bn_bwd": 9, "cnb_bn_bwd_from_partials": 10}.get(name)
+        bwd = name in ("cnb_bn_bwd", "cnb_bn_bwd_from_partials", "cnb_bn_bwd_prefix")
+        n_t = {"cnb_bn_fwd_train": 2, "cnb_bn_fwd_eval": 2, "cnb_bn_fwd_train_prefix": 2, "cnb_bn_bwd": 3,
+               "cnb_bn_bwd_from_partials": 3, "cnb_bn_bwd_prefix": 4}.get(name, 0)   # prefix bwd: acc read + write
+        if n_t and d["flags"] & 2 and (dres_at is None or dres_at not in nulls):
             n_t += 1  # residual read (fwd) / residual-gradient write (bwd)
         byts = n_t * d["M"] * d["C"] * es
-        if d["flags"] & 1 and name != "cnb_bn_fwd_eval":
+        if n_t and d["flags"] & 1 and name != "cnb_bn_fwd_eval":
             if d["dtype"] == 1 and d["C"] % 8 == 0:
                 byts += d["M"] * d["C"] / 8          # bit mask written (fwd) / read (bwd)
-            elif name == "cnb_bn_bwd":
+            elif bwd:
                 byts += d["M"] * d["C"] * es         # no mask: backward reads y
+        if n_t:   # the variants of one operation share its family
+            key = "cnb_bn_bwd" if bwd else ("cnb_bn_fwd_train" if name.startswith("cnb_bn_fwd_train") else name)
     return flops, byts, key
 
 

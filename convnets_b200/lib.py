@@ -167,18 +167,23 @@ class _Calls:
 
 _NO_STREAM = {"cnb_version", "cnb_last_error", "cnb_launch_count", "cnb_conv2d_out_dims",
               "cnb_conv2d_uses_tc", "cnb_conv2d_workspace_bytes", "cnb_bn_workspace_bytes",
-              "cnb_conv2d_bn_partial_rows"}
+              "cnb_conv2d_bn_partial_rows", "cnb_conv2d_dgrad_partial_rows", "cnb_adam_item_blocks",
+              "cnb_pack_filter_blocks"}
 
 
 def _describe(args):
     """Plain-Python copy of the scalar arguments / descriptor fields of one call."""
     out = []
-    for a in args:
+    nulls = []
+    for i, a in enumerate(args):
         obj = getattr(a, "_obj", None)  # byref(struct)
         if isinstance(obj, C.Structure):
             out.append({f: getattr(obj, f) for f, _ in obj._fields_})
         elif isinstance(a, (int, float)):
             out.append(a)
+        elif a is None or (isinstance(a, C.c_void_p) and not a.value):
+            nulls.append(i)
+    out.append({"_nulls": nulls})   # positions of the NULL pointer arguments (optional tensors)
     return out
 
 

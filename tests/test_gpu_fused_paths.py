@@ -214,12 +214,13 @@ def test_switches_off_same_result(monkeypatch, family, kind):
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
 @pytest.mark.parametrize("n,c,h,w,stride", [(4, 64, 28, 28, 1), (3, 128, 14, 14, 2), (2, 32, 9, 11, 1),
                                             (2, 68, 7, 7, 2), (8, 512, 4, 4, 1), (2, 1024, 1, 1, 1)])
-def test_depthwise_emits_batchnorm_partials(n, c, h, w, stride, dtype):
+def test_depthwise_emits_batchnorm_partials(n, c, h, w, stride, dtype, monkeypatch):
     """The 3x3 depthwise forward kernels emit the [rows][2][C] table of per-channel sums / sums of
     squares of the STORED output (Conv2dBlockDW, reference src/mobilenet_v1.py:90-125): the table must
     reproduce the sums of y, the output itself must be bit-identical to the plain launch, and
     BatchNorm fed with the table must agree with BatchNorm that reads y."""
     from convnets_b200 import functional as F
+    monkeypatch.setenv("CNB_DW_STATS", "1")      # opt-in path (measured slower on MobileNet-v1, see dwconv.cu)
     g = torch.Generator().manual_seed(c + h)
     x = torch.randn(n, c, h, w, generator=g).to(dtype).cuda().contiguous(memory_format=CL)
     wt = (torch.randn(c, 1, 3, 3, generator=g) * 0.4).cuda()
