@@ -241,11 +241,11 @@ dw3x3_strip_k(const T* __restrict__ in, const T* __restrict__ w, const float* __
   float ss[V], sq[V];
 #pragma unroll
   for (int j = 0; j < V; ++j) ss[j] = sq[j] = 0.f;
-  if (!active) {
-    if (STATS) dw_emit_stats<V>(ss, sq, dw_red, stats, p.C, 0, false);
-    return;
-  }
-  const int c0 = cv * V;
+  // Threads past the last channel vector leave at once — unless the CTA still has the statistics
+  // barrier ahead of it: every thread of a warp must reach the SAME __syncthreads, so with STATS the
+  // idle threads skip the loop (zero trips) and fall through to the one call site below.
+  if (!STATS && !active) return;
+  const int c0 = active ? cv * V : 0;
   float wr[9][V];
 #pragma unroll
   for (int t = 0; t < 9; ++t)
@@ -256,7 +256,8 @@ dw3x3_strip_k(const T* __restrict__ in, const T* __restrict__ w, const float* __
   for (int j = 0; j < V; ++j) bz[j] = (p.flags & CNB_CONV_BIAS) ? bias[c0 + j] : 0.f;
   const bool relu = p.flags & CNB_CONV_RELU;
   const int64_t step = (int64_t)gridDim.y * blockDim.y;
-  for (int64_t sidx = (int64_t)blockIdx.y * blockDim.y + threadIdx.y; sidx < p.total_strips; sidx += step) {
+  const int64_t my_strips = active ? p.total_strips : 0;
+  for (int64_t sidx = (int64_t)blockIdx.y * blockDim.y + threadIdx.y; sidx < my_strips; sidx += step) {
     const int qs = (int)(sidx % p.strips_per_row);
     const int64_t t2 = sidx / p.strips_per_row;
     const int oh = (int)(t2 % p.OH);
@@ -316,7 +317,7 @@ dw3x3_strip_k(const T* __restrict__ in, const T* __restrict__ w, const float* __
       }
     }
   }
-  if (STATS) dw_emit_stats<V>(ss, sq, dw_red, stats, p.C, c0, true);
+  if (STATS) dw_emit_stats<V>(ss, sq, dw_red, stats, p.C, c0, active);
 }
 
 // Stride-1 column walk (bf16): a thread owns 4 channels x 4 output columns and walks kDwRH output
@@ -337,11 +338,8 @@ dw3x3_s1_walk_k(const T* __restrict__ in, const T* __restrict__ w, const float* 
   float ss[V], sq[V];
 #pragma unroll
   for (int j = 0; j < V; ++j) ss[j] = sq[j] = 0.f;
-  if (!active) {
-    if (STATS) dw_emit_stats<V>(ss, sq, dw_red, stats, p.C, 0, false);
-    return;
-  }
-  const int c0 = cv * V;
+  if (!STATS && !active) return;   // with STATS every thread reaches the one barrier below (see the strip kernel)
+  const int c0 = active ? cv * V : 0;
   float wr[9][V];
 #pragma unroll
   for (int t = 0; t < 9; ++t)
@@ -351,7 +349,7 @@ dw3x3_s1_walk_k(const T* __restrict__ in, const T* __restrict__ w, const float* 
 #pragma unroll
   for (int j = 0; j < V; ++j) bz[j] = (p.flags & CNB_CONV_BIAS) ? bias[c0 + j] : 0.f;
   const bool relu = p.flags & CNB_CONV_RELU;
-  const int64_t units = (int64_t)p.N * row_blocks * p.strips_per_row;
+  const int64_t units = active ? (int64_t)p.N * row_blocks * p.strips_per_row : 0;
   const int64_t step = (int64_t)gridDim.y * blockDim.y;
   for (int64_t u = (int64_t)blockIdx.y * blockDim.y + threadIdx.y; u < units; u += step) {
     const int qs = (int)(u % p.strips_per_row);
@@ -422,7 +420,7 @@ dw3x3_s1_walk_k(const T* __restrict__ in, const T* __restrict__ w, const float* 
       }
     }
   }
-  if (STATS) dw_emit_stats<V>(ss, sq, dw_red, stats, p.C, c0, true);
+  if (STATS) dw_emit_stats<V>(ss, sq, dw_red, stats, p.C, c0, active);
 }
 
 // data gradient of the stride-2 / pad-1 3x3 depthwise conv: a strip of 4 dx columns (w0 % 4 == 0)
@@ -698,6 +696,13 @@ int dwconv_stats_rows(const cnb_conv_desc& d) {
   // kernel from 52 to 308 bytes of spills.  Kept, tested, and off until the walk is re-registered.
   const char* e = getenv("CNB_DW_STATS");   // read per call: the tests switch it in-process
   if (!(e && e[0] == '1')) return 0;
+  {
+    // only shapes whose channel vectors fill every CTA column (no idle threads next to working ones)
+    const int cvt = d.C / kDwV;
+    int cx = 1;
+    while (cx * 2 <= cvt && cx * 2 <= 32) cx *= 2;
+    if (cvt % cx != 0) return 0;
+  }
   if (!(d.R == 3 && d.S == 3 && d.pad_h == 1 && d.pad_w == 1 && d.dil_h == 1 && d.dil_w == 1 &&
         d.stride_h == d.stride_w && (d.stride_h == 1 || d.stride_h == 2) && d.C % kDwV == 0))
     return 0;

@@ -226,8 +226,11 @@ def test_depthwise_emits_batchnorm_partials(n, c, h, w, stride, dtype, monkeypat
     wt = (torch.randn(c, 1, 3, 3, generator=g) * 0.4).cuda()
     y0 = F.conv2d(x, wt, None, stride, 1, 1, c)
     y1, part = F.conv2d(x, wt, None, stride, 1, 1, c, bn_stats=True)
-    assert part is not None and part.shape[1:] == (2, c) and part.shape[0] >= 1
     assert torch.equal(y0, y1)
+    if (c // 4) % min(32, 1 << ((c // 4).bit_length() - 1)) != 0:
+        assert part is None        # a partly filled channel block: the kernel keeps to the plain form
+        return
+    assert part is not None and part.shape[1:] == (2, c) and part.shape[0] >= 1
     yd = y1.double()
     s_ref, q_ref = yd.sum(dim=(0, 2, 3)), (yd * yd).sum(dim=(0, 2, 3))
     s, q = part[:, 0].double().sum(0), part[:, 1].double().sum(0)
@@ -258,12 +261,11 @@ def _one_step_grads(monkeypatch, family, kind, sums, lazy, hw=64, batch=8):
     x = torch.randn(batch, 3, hw, hw, generator=g).cuda()
     y = torch.randint(0, 10, (batch,), generator=g).cuda()
     from convnets_b200 import lib as L
-    n0 = L.launch_count()
+    L.trace_begin()
     logits = model(x)
     model.cost_function(logits.float(), y).backward()
-    torch.cuda.synchronize()
-    return logits.detach().float(), {k: p.grad.detach().clone() for k, p in model.named_parameters()}, \
-        L.launch_count() - n0
+    calls = [c[0] for c in L.trace_end()]
+    return logits.detach().float(), {k: p.grad.detach().clone() for k, p in model.named_parameters()}, calls
 
 
 @pytest.mark.parametrize("family,kind,hw", [("ResNet", "18", 64), ("ResNet", "50", 64), ("ResNet", "50", 224),
@@ -281,8 +283,9 @@ def test_bn_backward_sums_and_lazy_skip_gradient_vs_plain(monkeypatch, family, k
         gsum = sum(v.norm().item() for v in g0.values())
         errs = sorted((O.rel_l2(g1[k], g0[k]), k) for k in g0 if g0[k].norm().item() > 1e-6 * gsum)
         med, worst = errs[len(errs) // 2], errs[-1]
-        print(f"{family}-{kind} {hw}: sums={sums} lazy={lazy}: launches {n0} -> {n1}, grads vs plain median "
-              f"{med[0]:.2e} max {worst[0]:.2e} ({worst[1]})")
-        if sums:
-            assert n1 < n0, "no BatchNorm reduction kernel was saved"
+        used = n1.count("cnb_bn_bwd_from_partials")
+        print(f"{family}-{kind} {hw}: sums={sums} lazy={lazy}: {used} of {used + n1.count('cnb_bn_bwd')} BatchNorm "
+              f"backward calls took the data-grad's sums, grads vs plain median {med[0]:.2e} max {worst[0]:.2e} "
+              f"({worst[1]})")
+        assert (used > 0) == sums and "cnb_bn_bwd_from_partials" not in n0
         assert med[0] <= 2e-2 and worst[0] <= 2e-1, (med, worst)
