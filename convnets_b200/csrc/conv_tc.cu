@@ -356,9 +356,9 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
     for (int i = 0; i < 8; ++i) soff[i] = i * 128 + ((((sc % 64) / 8) ^ i) << 4);  // RPG % 8 == 0
     float as0 = 0.f, as1 = 0.f, aq0 = 0.f, aq1 = 0.f;
     const bool want_stats = p.stats != nullptr;
-    const bool col_ok = n0 + sc < p.Kout;
-    const float mu0 = (BNRED && col_ok) ? p.bn_mean[n0 + sc] : 0.f;
-    const float mu1 = (BNRED && col_ok) ? p.bn_mean[n0 + sc + 1] : 0.f;
+    float bsum[BNRED ? 8 : 1], bsq[BNRED ? 8 : 1];   // BNRED: this thread's 8 columns, all its tiles
+#pragma unroll
+    for (int j = 0; j < (BNRED ? 8 : 1); ++j) bsum[j] = bsq[j] = 0.f;
 
     uint32_t lt = 0;
     for (int mt = m_first; mt < p.m_tiles; mt += m_step, ++lt) {
@@ -373,6 +373,18 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
 #pragma unroll
           for (int b = 0; b < (HALF_N * 2 + 127) / 128; ++b)
             if (n0 + chalf * HALF_N + b * 64 < p.Kout) prefetch_l2(ap + b * 64);
+        }
+      }
+      if (BNRED) {
+        // the BatchNorm input rows of this tile come from HBM (written in the forward pass): ask for
+        // their lines now — the column-sum pass below then finds them in L2.  256 threads, one
+        // 128-byte line each per round: line l = (row l / segs, 64-channel segment l % segs).
+        constexpr int SEGS = BLOCK_N / 64;
+#pragma unroll
+        for (int l = et; l < TILE_M * SEGS; l += 256) {
+          const int r = l / SEGS, sg = l % SEGS;
+          if (m0 + r < p.M && n0 + sg * 64 < p.Kout)
+            prefetch_l2(p.bn_x + ((int64_t)m0 + r) * p.Kout + n0 + sg * 64);
         }
       }
       mbar_wait(&tmem_full_bar[buf], (lt >> 1) & 1);
@@ -489,35 +501,48 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
       }
       if (BNRED) {
         // backward sums of the BatchNorm whose output gradient this tile is: the staged (stored) dy,
-        // the ReLU bit and the BatchNorm input x of the same element.  8 rows of x / mask are
-        // requested before they are used.
-        float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
-        const int rows_left = p.M - m0 - rg * RPG;
-        if (col_ok) {
-          const int64_t e0 = ((int64_t)m0 + rg * RPG) * p.Kout + n0 + sc;
-          const int sh = sc & 7;
+        // the ReLU bits and the BatchNorm input x of the same elements.  A thread owns 8 adjacent
+        // columns (one 16-byte vector of x, of the staged tile, one mask byte per row) and every
+        // RGB-th row: 4 rows' loads are in flight together, a warp's lanes read whole rows.
+        constexpr int CG = BLOCK_N / 8;        // column groups: 8, 16, 32
+        constexpr int RGB = 256 / CG;          // row groups:   32, 16, 8
+        constexpr int RPB = TILE_M / RGB;      // rows per thread and tile: 4, 8, 16
+        const int cg = et % CG, rgb = et / CG;
+        const int col8 = n0 + cg * 8;
+        if (col8 < p.Kout) {
+          const float4 mlo = __ldg(reinterpret_cast<const float4*>(p.bn_mean + col8));
+          const float4 mhi = __ldg(reinterpret_cast<const float4*>(p.bn_mean + col8 + 4));
+          const float mu[8] = {mlo.x, mlo.y, mlo.z, mlo.w, mhi.x, mhi.y, mhi.z, mhi.w};
+          const uint32_t sbase = st_base + (uint32_t)(cg / 8) * (TILE_M * 128);
 #pragma unroll
-          for (int r8 = 0; r8 < RPG / 8; ++r8) {
-            uint32_t xv[8], mb[8];
+          for (int b4 = 0; b4 < RPB / 4; ++b4) {
+            uint4 xv[4];
+            uint32_t mb[4];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const bool ok = r8 * 8 + i < rows_left;
-              const int64_t e = e0 + (int64_t)(r8 * 8 + i) * p.Kout;
-              xv[i] = ok ? __ldg(reinterpret_cast<const uint32_t*>(p.bn_x + e)) : 0u;
+            for (int i = 0; i < 4; ++i) {
+              const int r = rgb + RGB * (b4 * 4 + i);
+              const bool ok = m0 + r < p.M;
+              const int64_t e = ((int64_t)m0 + r) * p.Kout + col8;
+              xv[i] = ok ? __ldg(reinterpret_cast<const uint4*>(p.bn_x + e)) : make_uint4(0u, 0u, 0u, 0u);
               mb[i] = ok ? (uint32_t)__ldg(p.bn_mask + (e >> 3)) : 0u;
             }
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const uint32_t w2 = lds_u32(col_addr + r8 * 1024 + soff[i]);
-              const uint32_t bits = mb[i] >> sh;
-              const float ga = (bits & 1u) ? __uint_as_float(w2 << 16) : 0.f;
-              const float gb = (bits & 2u) ? __uint_as_float(w2 & 0xffff0000u) : 0.f;
-              s0 += ga; q0 = fmaf(ga, __uint_as_float(xv[i] << 16) - mu0, q0);
-              s1 += gb; q1 = fmaf(gb, __uint_as_float(xv[i] & 0xffff0000u) - mu1, q1);
+            for (int i = 0; i < 4; ++i) {
+              const int r = rgb + RGB * (b4 * 4 + i);
+              const uint4 dv = lds_v4(sbase + (uint32_t)r * 128 + ((uint32_t)((cg & 7) ^ (r & 7)) << 4));
+              const uint32_t dw[4] = {dv.x, dv.y, dv.z, dv.w}, xw[4] = {xv[i].x, xv[i].y, xv[i].z, xv[i].w};
+#pragma unroll
+              for (int e2 = 0; e2 < 4; ++e2) {
+                const float ga = (mb[i] >> (2 * e2) & 1u) ? __uint_as_float(dw[e2] << 16) : 0.f;
+                const float gb = (mb[i] >> (2 * e2 + 1) & 1u) ? __uint_as_float(dw[e2] & 0xffff0000u) : 0.f;
+                bsum[2 * e2] += ga;
+                bsq[2 * e2] = fmaf(ga, __uint_as_float(xw[e2] << 16) - mu[2 * e2], bsq[2 * e2]);
+                bsum[2 * e2 + 1] += gb;
+                bsq[2 * e2 + 1] = fmaf(gb, __uint_as_float(xw[e2] & 0xffff0000u) - mu[2 * e2 + 1], bsq[2 * e2 + 1]);
+              }
             }
           }
         }
-        as0 += s0; as1 += s1; aq0 += q0; aq1 += q1;
       } else if (want_stats) {
         // BatchNorm statistics of this tile from the staged (bf16-rounded, i.e. as stored) values.
         // Rows past the end of the tensor are zero (TMA zero-fill x weights) unless a bias was
@@ -543,7 +568,34 @@ conv_fprop_tc_persist_k(const __grid_constant__ FpropParams p) {
       if (elect_one()) tma_store_wait0();
       __syncwarp();
     }
-    if (want_stats) {
+    if (BNRED) {
+      // [RGB][2][BLOCK_N] floats in the staging buffer (16 KB), then one thread per column sums the
+      // row groups in fixed order
+      constexpr int CG = BLOCK_N / 8, RGB = 256 / CG;
+      const int cg = et % CG, rgb = et / CG;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      const uint32_t red = st_base;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        sts_f32(red + ((rgb * 2 + 0) * BLOCK_N + cg * 8 + j) * 4, bsum[j]);
+        sts_f32(red + ((rgb * 2 + 1) * BLOCK_N + cg * 8 + j) * 4, bsq[j]);
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (et < BLOCK_N) {
+        float S = 0.f, Qs = 0.f;
+#pragma unroll
+        for (int g = 0; g < RGB; ++g) {
+          S += lds_f32(red + ((g * 2 + 0) * BLOCK_N + et) * 4);
+          Qs += lds_f32(red + ((g * 2 + 1) * BLOCK_N + et) * 4);
+        }
+        const int col = n0 + et;
+        if (col < p.Kout) {
+          float* dst = p.stats + (size_t)m_first * 2 * p.Kout;
+          dst[col] = S;
+          dst[p.Kout + col] = Qs;
+        }
+      }
+    } else if (want_stats) {
       // combine the row groups in fixed order and write this CTA's partial row
       asm volatile("bar.sync 1, 256;" ::: "memory");  // staging is idle (last store completed)
       const uint32_t red = st_base;                    // [RG][2][BLOCK_N] floats

@@ -29,6 +29,8 @@ CASES = [
     ("ResNeXt", "50", 224, 2),         # C4: grouped 3x3 (32 x 4d)
     ("DenseNet", "121", 224, 2),       # C5: concat-heavy blocks
     ("SKNet", "50", 224, 2),           # C5: dilated grouped paths
+    ("ShuffleNetV1", "g4", 32, 8),     # 68 / 136 / 272-channel groups: mixed tensor-core / CUDA-core directions
+    ("ShuffleNetV1", "g4", 64, 8),
 ]
 
 

@@ -37,7 +37,10 @@ CASES = [
     ("DenseNet", "121", 64, 8),
     ("MobileNetV1", "", 64, 8),
     ("ShuffleNetV1", "g3", 64, 8),
-    ("ShuffleNetV1", "g4", 32, 8),     # 68 / 136 / 272 channels per group: no 16-byte aligned channel slices
+    ("ShuffleNetV1", "g4", 64, 8),     # 68 / 136 / 272 channels per group: no 16-byte aligned channel slices
+    # (at 32 x 32 the last stage is 1 x 1: BatchNorm over 8 values per channel, where two bf16 executions
+    # of the reference graph itself differ by O(0.1) on the logits; every layer of that case is held to
+    # the oracle on identical inputs by tests/test_gpu_layers_in_network.py)
     ("SEResNet", "50", 64, 8),
     ("SENet", "26", 64, 8),
     ("SKResNet", "26", 64, 8),
