@@ -11,6 +11,8 @@
 // The merges sum in a fixed order (no floating-point atomics): results are bit-reproducible.
 #include <string.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace cnb {
@@ -1599,5 +1601,134 @@ int cnb_bn_bwd_from_partials(const cnb_bn_desc* d, const void* x, const void* re
   CNB_TRY(check_launch("bn_bwd_partials"));
   return launch_bn_bwd_dx(d, x, nullptr, mask, dy, save_mean, c1, c2, c3, dx, d_residual, 8, true, variant, 2, three,
                           st);
+}
+
+// ---------------------------------------------------------------- allocation-free BatchNorm forward
+// cnb_bn_fwd_train_static: the training forward of cnb_bn_fwd_train (statistics from x) for callers
+// that may not allocate — under CUDA-graph capture, in a tight serving loop, in a harness that
+// forbids cudaMalloc.  No counterpart in the reference.
+// The scratch the two-kernel form needs (per-CTA partial sums, the per-channel scale / shift, the
+// arrival counters of the "last CTA merges" step) lives in ONE file-scope device array that every
+// GPU loading the library holds until exit:
+//   [0, kStaticScratchBytes)            partials [splits][2][C] floats, then scale[C], shift[C]
+//   [kStaticScratchBytes, + 4 KiB)      arrival counters (kCountersPerSlot ints)
+// In host code the array's NAME is a host-side stand-in, not a device address: its device address is
+// looked up once per device with cudaGetSymbolAddress (that device current) and passed to the
+// kernels.  Every call shares the array and finds the previous call's contents in it: the counters
+// are cleared on the caller's stream before the statistics kernel; partials and coefficients are
+// fully rewritten before they are read.  Two calls that overlap on the GPU (different streams, no
+// ordering between them) race on it.
+constexpr size_t kStaticScratchBytes = (size_t)1 << 20;
+constexpr int kStaticMaxChannels = 16384;
+constexpr size_t kStaticTotalBytes = kStaticScratchBytes + (size_t)kCountersPerSlot * sizeof(int);
+static __device__ __align__(256) unsigned char g_bn_static_scratch[kStaticTotalBytes];
+
+static int bn_static_scratch_ptr(unsigned char** out) {
+  static std::mutex mu;
+  static unsigned char* addr[64] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  CNB_REQUIRE(e == cudaSuccess && dev >= 0 && dev < 64, CNB_ERR_CUDA,
+              "cnb_bn_fwd_train_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    unsigned char* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_bn_static_scratch);
+    CNB_REQUIRE(e == cudaSuccess && p != nullptr, CNB_ERR_CUDA,
+                "cnb_bn_fwd_train_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return CNB_OK;
+}
+
+size_t cnb_bn_static_scratch_bytes(void) { return kStaticScratchBytes; }
+
+int cnb_bn_fwd_train_static(const cnb_bn_desc* d, const void* x, const void* residual, const float* gamma,
+                            const float* beta, float* running_mean, float* running_var, void* y,
+                            float* save_mean, float* save_rstd, void* relu_mask, void* stream) {
+  CNB_TRY(validate_bn(d, "cnb_bn_fwd_train_static"));
+  CNB_REQUIRE(!relu_mask || ((d->flags & CNB_BN_RELU) && d->dtype == CNB_BF16 && d->C % 8 == 0),
+              CNB_ERR_INVALID,
+              "cnb_bn_fwd_train_static: relu_mask needs CNB_BN_RELU, bf16 and C %% 8 == 0 (C=%d)", d->C);
+  CNB_REQUIRE(x && y && save_mean && save_rstd, CNB_ERR_INVALID, "cnb_bn_fwd_train_static: null pointer");
+  const bool add = d->flags & CNB_BN_ADD, relu = d->flags & CNB_BN_RELU;
+  CNB_REQUIRE(!add || residual, CNB_ERR_INVALID, "cnb_bn_fwd_train_static: CNB_BN_ADD without residual");
+  CNB_REQUIRE(d->M > 1, CNB_ERR_INVALID,
+              "cnb_bn_fwd_train_static: expected more than 1 value per channel when training (M=%lld)",
+              (long long)d->M);
+  CNB_REQUIRE(d->C <= kStaticMaxChannels, CNB_ERR_WORKSPACE,
+              "cnb_bn_fwd_train_static: C=%d exceeds the %d channels the built-in scratch is sized for "
+              "(use cnb_bn_fwd_train with a caller workspace)", d->C, kStaticMaxChannels);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int C = d->C;
+  const int64_t M = d->M;
+  int v = pick_vec(C, dtype_size(d->dtype), x, y, add ? residual : nullptr);
+  CNB_REQUIRE(!relu_mask || v == 8, CNB_ERR_INVALID,
+              "cnb_bn_fwd_train_static: relu_mask needs 16-byte aligned tensors");
+  // same kernels and launch geometry as cnb_bn_fwd_train => the same bits
+  const int svariant = (d->dtype == CNB_BF16 && v == 8) ? bn_stats_variant() : 0;
+  BnGeom g = bn_geom(M, C, v, svariant == 2 ? 3 : kReduceWaves, kReduceCx);
+  const size_t need = ((size_t)2 * C * g.splits + (size_t)2 * C) * sizeof(float);
+  CNB_REQUIRE(need <= kStaticScratchBytes && g.cblocks <= kCountersPerSlot, CNB_ERR_WORKSPACE,
+              "cnb_bn_fwd_train_static: needs %zu bytes of scratch (C=%d, %d row splits), the built-in "
+              "scratch holds %zu (use cnb_bn_fwd_train with a caller workspace)", need, C, g.splits,
+              kStaticScratchBytes);
+  unsigned char* base = nullptr;
+  CNB_TRY(bn_static_scratch_ptr(&base));
+  float* part = reinterpret_cast<float*>(base);
+  int* counter = reinterpret_cast<int*>(base + kStaticScratchBytes);
+  float* scale = part + (size_t)2 * C * g.splits;
+  float* shift = scale + C;
+  BnFwdFin fin{gamma, beta, running_mean, running_var, save_mean, save_rstd, scale, shift,
+               d->eps, d->momentum, (long long*)d->num_batches_tracked};
+  cudaError_t e = cudaMemsetAsync(counter, 0, (size_t)g.cblocks * sizeof(int), st);
+  CNB_REQUIRE(e == cudaSuccess, CNB_ERR_CUDA, "cnb_bn_fwd_train_static: clearing the counters: %s",
+              cudaGetErrorString(e));
+  {
+    dim3 grid(g.cblocks, g.splits), block(g.cx, g.ry);
+    size_t smem = (size_t)g.ry * 2 * g.cx * v * sizeof(float);
+    if (smem < 4096) smem = 4096;  // the merge step re-uses it for 256 x 2 doubles
+    if (svariant == 1)
+      bn_stats_walk_k<bf16, 8, 4, 4><<<grid, block, smem, st>>>((const bf16*)x, part, M, C, g.rows_per_split,
+                                                                g.splits, counter, fin);
+    else if (svariant == 2)
+      bn_stats_walk_k<bf16, 8, 8, 3><<<grid, block, smem, st>>>((const bf16*)x, part, M, C, g.rows_per_split,
+                                                                g.splits, counter, fin);
+    else
+      CNB_DISPATCH_TV(d->dtype, v, (bn_stats_k<T, V><<<grid, block, smem, st>>>(
+                                       (const T*)x, part, M, C, g.rows_per_split, g.splits, counter,
+                                       fin)));
+    CNB_TRY(check_launch("bn_stats(static)"));
+  }
+  const float* mean_ptr = save_mean;
+  uint8_t* mask = (uint8_t*)relu_mask;
+  const bool ahot = d->dtype == CNB_BF16 && v == 8;
+  const int avariant = bn_fwd_variant();
+  BnGeom ga = bn_geom(M, C, v, apply_waves(ahot, avariant));
+  dim3 agrid(ga.cblocks, ga.splits), ablock(ga.cx, ga.ry);
+  const int64_t arows = ga.rows_per_split;
+#define SAPPLY_ARGS (const T*)x, (const T*)residual, scale, shift, mean_ptr, (T*)y, mask, M, C, arows
+#define SAPPLY(R, A) \
+  CNB_DISPATCH_TV(d->dtype, v, (bn_apply_k<T, V, R, A, 4, 2><<<agrid, ablock, 0, st>>>(SAPPLY_ARGS)))
+#define SAPPLY_HOT(UU, MB)                                                                          \
+  do {                                                                                              \
+    using T = bf16;                                                                                 \
+    if (relu && add) bn_apply_k<T, 8, true, true, UU, MB><<<agrid, ablock, 0, st>>>(SAPPLY_ARGS);   \
+    else if (relu) bn_apply_k<T, 8, true, false, UU, MB><<<agrid, ablock, 0, st>>>(SAPPLY_ARGS);    \
+    else if (add) bn_apply_k<T, 8, false, true, UU, MB><<<agrid, ablock, 0, st>>>(SAPPLY_ARGS);     \
+    else bn_apply_k<T, 8, false, false, UU, MB><<<agrid, ablock, 0, st>>>(SAPPLY_ARGS);             \
+  } while (0)
+  if (ahot && avariant == 1) SAPPLY_HOT(2, 3);
+  else if (ahot && avariant == 2) SAPPLY_HOT(4, 3);
+  else if (ahot && avariant == 3) SAPPLY_HOT(2, 4);
+  else if (relu && add) SAPPLY(true, true);
+  else if (relu) SAPPLY(true, false);
+  else if (add) SAPPLY(false, true);
+  else SAPPLY(false, false);
+#undef SAPPLY_HOT
+#undef SAPPLY
+#undef SAPPLY_ARGS
+  return check_launch("bn_apply(static)");
 }
 }  // extern "C"

@@ -77,6 +77,8 @@ SIGNATURES = {
     "cnb_bn_workspace_bytes": (_SZ, [C.POINTER(BnDesc)]),
     "cnb_bn_fwd_train": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I32, _P, _P,
                               _SZ, _P]),
+    "cnb_bn_static_scratch_bytes": (_SZ, []),
+    "cnb_bn_fwd_train_static": (_I, [C.POINTER(BnDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "cnb_bn_stats_from_partials": (_I, [C.POINTER(BnDesc), _P, _I32, _P, _P, _P, _SZ, _P]),
     "cnb_bn_fwd_train_prefix": (_I, [C.POINTER(BnDesc), _P, _I64, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P]),
     "cnb_bn_bwd_prefix": (_I, [C.POINTER(BnDesc), _P, _I64, _P, _P, _P, _P, _P, _P, _P, _I64, _P, _P, _P, _SZ, _P]),
@@ -167,6 +169,7 @@ class _Calls:
 
 _NO_STREAM = {"cnb_version", "cnb_last_error", "cnb_launch_count", "cnb_conv2d_out_dims",
               "cnb_conv2d_uses_tc", "cnb_conv2d_workspace_bytes", "cnb_bn_workspace_bytes",
+              "cnb_bn_static_scratch_bytes",
               "cnb_conv2d_bn_partial_rows", "cnb_conv2d_dgrad_partial_rows", "cnb_adam_item_blocks",
               "cnb_pack_filter_blocks"}
 

@@ -18,7 +18,8 @@
  *     immediately; no implicit device synchronisation.
  *   - return value: 0 = ok, negative = cnb_status error; cnb_last_error() gives a thread-local
  *     message.  There is NO silent fallback: an unsupported shape is an error.
- *   - scratch memory comes from the caller, sized by the *_workspace_bytes query.
+ *   - scratch memory comes from the caller, sized by the *_workspace_bytes query (one exception:
+ *     cnb_bn_fwd_train_static, whose scratch is a static device array inside the library).
  */
 #ifndef CONVNETS_B200_H
 #define CONVNETS_B200_H
@@ -160,6 +161,22 @@ int cnb_bn_fwd_train(const cnb_bn_desc* d, const void* x, const void* residual, 
                      float* save_mean, float* save_rstd, const float* conv_partials,
                      int32_t n_partials, void* relu_mask, void* workspace, size_t workspace_bytes,
                      void* stream);
+/* Allocation-free training forward.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, kernels, launch geometry and results as
+ * cnb_bn_fwd_train with conv_partials = NULL, but the scratch (per-CTA partial sums, scale / shift,
+ * arrival counters) is a 1 MiB + 4 KiB static __device__ array inside the library — held by every
+ * GPU that loads it until exit — instead of a caller workspace; the call makes no cudaMalloc /
+ * cudaFree and calls no allocating routine.  Limits: C <= 16384 and 8*C*(splits+1) bytes <=
+ * cnb_bn_static_scratch_bytes() and at most 1024 channel blocks (on a 148-SM B200 the scratch need
+ * peaks at ~434 KB: every C <= 16384 with C % 8 == 0 in bf16 / C % 4 == 0 in fp32 fits, unvectorised
+ * rows up to C = 8192); beyond them it returns CNB_ERR_WORKSPACE with a message and launches nothing.  All calls share the array: calls that
+ * overlap on the GPU (different streams without an ordering between them) race on it — serialise
+ * them, or use cnb_bn_fwd_train with one workspace per stream. */
+size_t cnb_bn_static_scratch_bytes(void);
+int cnb_bn_fwd_train_static(const cnb_bn_desc* d, const void* x, const void* residual, const float* gamma,
+                            const float* beta, float* running_mean, float* running_var, void* y,
+                            float* save_mean, float* save_rstd, void* relu_mask, void* stream);
 /* backward from the sums a data-grad epilogue already formed (cnb_conv2d_dgrad_bn): finish + dx pass
  * only.  bf16, CNB_BN_RELU with the 1-bit mask, C % 8 == 0. */
 int cnb_bn_bwd_from_partials(const cnb_bn_desc* d, const void* x, const void* relu_mask, const void* dy,
