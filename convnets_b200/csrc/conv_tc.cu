@@ -69,6 +69,23 @@ static int load_driver_fns() {
   return CNB_OK;
 }
 
+// The encode calls are DRIVER API: they need a context current on the calling thread.  A thread that
+// has only ever made calls that do not bind one (the autograd engine's device thread can reach a
+// convolution that way) gets CUDA_ERROR_INVALID_CONTEXT; a runtime call that needs the device binds
+// the primary context, after which the encode is retried once.  Never taken on a thread that has
+// launched anything.
+template <typename F>
+static CUresult encode_with_context(const void* base, F&& encode) {
+  CUresult r = encode();
+  if (r == CUDA_ERROR_INVALID_CONTEXT) {
+    cudaPointerAttributes a;   // the device that owns the operand, not whatever device 0 is
+    if (cudaPointerGetAttributes(&a, base) == cudaSuccess && a.type == cudaMemoryTypeDevice)
+      cudaSetDevice(a.device);
+    if (cudaFree(nullptr) == cudaSuccess) r = encode();
+  }
+  return r;
+}
+
 // 2-D / 3-D tiled bf16 map with 128B swizzle; dims/box innermost first; OOB reads give zeros.
 static int make_tiled_map(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
                           const uint64_t* strides_bytes /* rank-1 */, const uint32_t* box,
@@ -81,10 +98,12 @@ static int make_tiled_map(CUtensorMap* m, const void* base, int rank, const uint
     es[i] = 1;
   }
   for (int i = 0; i < rank - 1; ++i) gstr[i] = strides_bytes[i];
-  CUresult r = g_encodeTiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank,
-                             const_cast<void*>(base), gdim, gstr, b, es,
-                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = encode_with_context(base, [&] {
+    return g_encodeTiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank,
+                         const_cast<void*>(base), gdim, gstr, b, es,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  });
   CNB_REQUIRE(r == CUDA_SUCCESS, CNB_ERR_CUDA, "cuTensorMapEncodeTiled(%s) failed: CUresult %d", what,
               (int)r);
   return CNB_OK;
@@ -99,10 +118,12 @@ static int make_im2col_map(CUtensorMap* m, const void* base, int N, int H, int W
   int lower[2] = {lower_w, lower_h};
   int upper[2] = {upper_w, upper_h};
   cuuint32_t es[4] = {1, (cuuint32_t)trav_w, (cuuint32_t)trav_h, 1};
-  CUresult r = g_encodeIm2col(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim,
-                              gstr, lower, upper, (cuuint32_t)TILE_K, (cuuint32_t)pixels, es,
-                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r = encode_with_context(base, [&] {
+    return g_encodeIm2col(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim,
+                          gstr, lower, upper, (cuuint32_t)TILE_K, (cuuint32_t)pixels, es,
+                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  });
   CNB_REQUIRE(r == CUDA_SUCCESS, CNB_ERR_CUDA,
               "cuTensorMapEncodeIm2col(%s) failed: CUresult %d (N=%d H=%d W=%d C=%d lower=%d,%d "
               "upper=%d,%d trav=%d,%d)",
@@ -1547,9 +1568,11 @@ int conv_tc_wgrad(const cnb_conv_desc& d, const void* x, const void* dy, float* 
     cuuint64_t gstr[3] = {(cuuint64_t)CW * 4, (cuuint64_t)RS * CW * 4, (cuuint64_t)wsz * 4};
     cuuint32_t box[4] = {32, 1, (cuuint32_t)TILE_M, 1};
     cuuint32_t es[4] = {1, 1, 1, 1};
-    CUresult r = g_encodeTiled(&prm.tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, part, gdim, gstr, box, es,
-                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    CUresult r = encode_with_context(part, [&] {
+      return g_encodeTiled(&prm.tmOut, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, part, gdim, gstr, box, es,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    });
     CNB_REQUIRE(r == CUDA_SUCCESS, CNB_ERR_CUDA, "cuTensorMapEncodeTiled(wgrad out) failed: CUresult %d",
                 (int)r);
   }

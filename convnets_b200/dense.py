@@ -47,6 +47,9 @@ class _Ctx:
     def mark_non_differentiable(self, *ts):
         pass
 
+    def set_materialize_grads(self, value):
+        pass
+
 
 def _p(t):
     return None if t is None else C.c_void_p(t.data_ptr())

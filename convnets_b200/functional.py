@@ -182,10 +182,20 @@ def _conv_desc(x_shape, w_shape, stride, padding, dilation, groups, dtype_code, 
     return d
 
 
+# Autograd hands a Function one gradient per OUTPUT and, by default, materialises zeros for the ones
+# nobody differentiated — here the partial-sum tables the conv functions return as non-differentiable
+# second outputs: one `fill` launch per conv per step (~170 in a ResNet-50 step).  With
+# CNB_SKIP_ZERO_GRADS=1 the conv functions take `None` instead (set_materialize_grads(False)) and
+# return no gradient when their main output was not used at all, as torch's own convolution does.
+_SKIP_ZERO_GRADS = __import__("os").environ.get("CNB_SKIP_ZERO_GRADS", "0") == "1"
+
+
 class _Conv2dFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, bias, wpack, stride, padding, dilation, groups, algo, want_stats,
                 wpack_t=None, relu=False, bn_holder=None):
+        if _SKIP_ZERO_GRADS:
+            ctx.set_materialize_grads(False)
         ctx.bn_holder = bn_holder
         _cuda(x, wpack, bias)
         lib = _L.load()
@@ -219,6 +229,8 @@ class _Conv2dFn(torch.autograd.Function):
             raise NotImplementedError(
                 "conv2d(relu=True) is the inference epilogue (BatchNorm folded into the filter, "
                 "reference valid_model runs under no_grad, src/basemodel.py:304); no backward")
+        if dy is None:       # only with CNB_SKIP_ZERO_GRADS: the output was not used
+            return (None,) * 13
         lib = _L.load()
         x, wpack, wpack_t = ctx.saved_tensors
         d = ctx.desc
@@ -313,6 +325,14 @@ class _Conv2dSkipFn(torch.autograd.Function):
         # a lazy skip gradient (see _LAZY_DRES) is taken off the table whatever happens next: the
         # entry keeps dy alive, so no other tensor can sit at its address while it is registered
         lazy = _LAZY_DRES.pop(dskip.data_ptr(), None) if dskip is not None else None
+        if dy is None and dskip is not None:
+            # only with CNB_SKIP_ZERO_GRADS: the conv output was not used, the identity path was
+            if not ctx.needs_input_grad[0]:
+                return (None,) * 12
+            dskip = _nhwc(dskip)
+            if lazy is not None:
+                dskip = mask_apply(dskip, lazy[0])
+            return (dskip,) + (None,) * 11
         if dskip is None or not ctx.needs_input_grad[0]:
             return _Conv2dFn.backward(ctx, dy, _dpart)
         lib = _L.load()
@@ -391,6 +411,8 @@ class _InputConvFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, weight, bias, stride, padding, dilation, dtype, want_stats, relu=False):
+        if _SKIP_ZERO_GRADS:
+            ctx.set_materialize_grads(False)
         _cuda(x, weight, bias)
         lib = _L.load()
         if x.dtype != torch.float32 or not x.is_contiguous():
@@ -435,6 +457,8 @@ class _InputConvFn(torch.autograd.Function):
     def backward(ctx, dy, _dpart=None):
         if ctx.relu:
             raise NotImplementedError("conv2d_input(relu=True) is the inference epilogue; no backward")
+        if dy is None:
+            return (None,) * 9
         lib = _L.load()
         (col,) = ctx.saved_tensors
         d = ctx.desc

@@ -289,3 +289,38 @@ def test_bn_backward_sums_and_lazy_skip_gradient_vs_plain(monkeypatch, family, k
               f"({worst[1]})")
         assert (used > 0) == sums and "cnb_bn_bwd_from_partials" not in n0
         assert med[0] <= 2e-2 and worst[0] <= 2e-1, (med, worst)
+
+
+def test_tensor_core_conv_from_a_thread_that_never_touched_cuda():
+    """The tensor-map encodes are driver-API calls and need a context current on the calling thread.
+    A thread whose FIRST CUDA-related call is cnb_conv2d_fwd (a C-ABI caller's worker thread; the
+    autograd device thread when no gradient had to be materialised before a convolution's backward)
+    used to get CUDA_ERROR_INVALID_CONTEXT from cuTensorMapEncodeTiled; the library now binds the
+    primary context of the operand's device and retries."""
+    import threading
+    from convnets_b200 import lib as L
+    lib = L.load()
+    n, h, w, c, k = 2, 16, 16, 64, 128
+    g = torch.Generator(device="cuda").manual_seed(5)
+    x = torch.randn(n, h, w, c, device="cuda", generator=g).bfloat16()
+    wt = (torch.randn(k, c, device="cuda", generator=g) / c ** 0.5).bfloat16()
+    y = torch.zeros(n, h, w, k, device="cuda", dtype=torch.bfloat16)
+    d = L.ConvDesc(n, h, w, c, k, 1, 1, 1, 1, 0, 0, 1, 1, 1, L.CNB_BF16, 0, L.CNB_ALGO_TC)
+    ws = torch.empty(max(1, lib.cnb_conv2d_workspace_bytes(C.byref(d), L.CNB_FWD)), dtype=torch.uint8, device="cuda")
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    out = {}
+
+    def worker():
+        out["status"] = lib.cnb_conv2d_fwd(C.byref(d), C.c_void_p(x.data_ptr()), C.c_void_p(wt.data_ptr()), None,
+                                           C.c_void_p(y.data_ptr()), None, C.c_void_p(ws.data_ptr()), ws.numel(),
+                                           stream)
+        out["error"] = L.last_error()     # thread-local message
+
+    t = threading.Thread(target=worker)
+    t.start()
+    t.join()
+    torch.cuda.synchronize()
+    assert out["status"] == 0, out["error"]
+    ref = (x.float().view(-1, c) @ wt.float().t()).view(n, h, w, k)
+    assert O.rel_l2(y.float(), ref) < 1e-2
