@@ -186,9 +186,6 @@ class EvalGraph:
             self.graph, self.key, self.epoch = g, key, L._WEIGHT_EPOCH[0]
         if x.data_ptr() != self.x.data_ptr():
             self.x.copy_(x, non_blocking=True)
-        opt = self.model.optimizer
-        if hasattr(opt, "sync_hyperparams"):
-            opt.sync_hyperparams()      # a learning rate changed by the scheduler reaches the replay
         self.graph.replay()
         return self.out
 
