@@ -49,6 +49,21 @@ def test_library_is_sm100a_only(lib):
     assert archs == {"sm_100a"}, archs
 
 
+def test_convolution_object_code_is_tcgen05_and_tma(lib):
+    """The dense convolution kernels are Blackwell-native in the OBJECT code: tcgen05.mma (UTCHMMA) with
+    TMEM read-back (LDTM), TMA loads in tiled and im2col mode (UTMALDG[.IM2COL]), TMA stores (UTMASTG),
+    mbarrier waits (SYNCS) — and no legacy mma.sync (HMMA) contraction."""
+    from convnets_b200 import build
+    obj = os.path.join(build.BUILD, "conv_tc.o")
+    sass = subprocess.run(["cuobjdump", "-sass", obj], capture_output=True, text=True, check=True).stdout
+    ops = re.findall(r"/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", sass)
+    count = lambda prefix: sum(1 for o in ops if o.startswith(prefix))
+    assert count("UTCHMMA") >= 100 and count("LDTM") >= 20
+    assert count("UTMALDG") >= 100 and sum(1 for o in ops if o.startswith("UTMALDG") and "IM2COL" in o) >= 20
+    assert count("UTMASTG") >= 20 and count("SYNCS") >= 100
+    assert count("HMMA") == 0
+
+
 def test_descriptor_validation_without_a_gpu(lib):
     h = lib.load()
     d = lib.ConvDesc(2, 56, 56, 64, 128, 3, 3, 2, 2, 1, 1, 1, 1, 1, lib.CNB_BF16, 0, lib.CNB_ALGO_AUTO)
