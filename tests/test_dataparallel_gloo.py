@@ -88,3 +88,62 @@ def test_gradsync_matches_dp_oracle(bucket_bytes):
     assert nb0 == nb1 and n0 == n1 == nb0      # one all-reduce per bucket per step
     if bucket_bytes == 1 << 20:
         assert nb0 > 5
+
+
+def _worker_slots(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.set_num_threads(2)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from convnets_b200.dataparallel import GradSync
+        torch.manual_seed(7 + rank)
+        net = torch.nn.Sequential(torch.nn.Conv2d(3, 8, 3, padding=1), torch.nn.BatchNorm2d(8), torch.nn.ReLU(),
+                                  torch.nn.Conv2d(8, 16, 3, padding=1), torch.nn.AdaptiveAvgPool2d(1),
+                                  torch.nn.Flatten(), torch.nn.Linear(16, 10))
+        net = net.to(memory_format=torch.channels_last)      # conv filters KRSC, as convert() leaves them
+        sync = GradSync(net, bucket_bytes=2048)
+        opt = torch.optim.Adam(net.parameters(), lr=1e-2)
+        g = torch.Generator().manual_seed(50 + rank)
+        ptrs, ok = None, True
+        for _ in range(3):
+            # StepGraph's step: gradients dropped (not zeroed) before every backward
+            opt.zero_grad(set_to_none=True)
+            x = torch.randn(4, 3, 8, 8, generator=g)
+            y = torch.randint(0, 10, (4,), generator=g)
+            torch.nn.functional.cross_entropy(net(x), y, reduction="sum").backward()
+            cur = []
+            for p in net.parameters():
+                bi, off = sync._slot[p]
+                slot = sync._view(sync.buckets[bi], p, off)
+                # what optim.FusedAdam's item table needs: the gradient IS the bucket slot, at a fixed
+                # address, dense in the parameter's own physical order
+                ok &= p.grad.data_ptr() == slot.data_ptr() and p.grad.stride() == p.stride()
+                cur.append(p.grad.data_ptr())
+            ok &= ptrs is None or ptrs == cur
+            ptrs = cur
+            opt.step()
+        digest = float(sum(p.detach().double().sum() for p in net.parameters()))
+        q.put((rank, bool(ok), digest, len(sync.buckets), sync.launched))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gradients_live_in_fixed_bucket_slots_across_steps():
+    """The multi-tensor Adam caches one table of (parameter, gradient) addresses per group and a CUDA
+    graph replays it: with GradSync every `.grad` must be the same bucket slot on every step even
+    though the step drops the gradients (set_to_none) before each backward."""
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker_slots, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=300) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    (_, ok0, d0, nb0, n0), (_, ok1, d1, nb1, n1) = res
+    assert ok0 and ok1
+    assert d0 == d1                              # replicas bit-identical after 3 steps
+    assert nb0 == nb1 > 1 and n0 == n1 == 3 * nb0
